@@ -1,0 +1,120 @@
+// ORACLE (test infrastructure).  Thin C-ABI driver around the UNMODIFIED reference headers
+// (/root/reference/include + patched-files, compiled where they lie) against oracle/shim.
+// Built once per tau (-DREF_TAU=...) into oracle/_ref/libref_tau<tau>.so, because the reference makes
+// tau a template parameter (lz77_sss.hpp:176-186) and its misc/utils.hpp defines non-inline
+// functions (one translation unit per library).
+#include <lz77_sss/lz77_sss.hpp>
+#include <omp.h>
+#include <cstdint>
+#include <cstring>
+#include <random>
+#include <vector>
+
+#ifndef REF_TAU
+#error "compile with -DREF_TAU=<tau>"
+#endif
+
+namespace {
+
+struct sink_t {
+    uint64_t* src;
+    uint64_t* len;
+    uint64_t cap;
+    uint64_t z;
+};
+
+template <typename pos_t, uint64_t tau>
+int64_t run_approximate(const uint8_t* text, uint64_t n, int phr_mode, int fact_mode,
+                        int num_threads, sink_t& sink, double* seconds) {
+    // every reference driver pads the input with zero bytes (cli/lz77_sss_3_aprx.cpp:66,
+    // bench/lz77_sss_bench_tau.cpp:72)
+    std::vector<char> buf(n + 4 * 4096, 0);
+    std::memcpy(buf.data(), text, n);
+    auto out = [&](typename lz77_sss<pos_t>::factor f) {
+        if (sink.z < sink.cap) {
+            sink.src[sink.z] = f.src;
+            sink.len[sink.z] = f.len;
+        }
+        sink.z++;
+    };
+    parameters prm { .num_threads = (uint16_t)num_threads, .log = false };
+    char* T = buf.data();
+    pos_t N = (pos_t)n;
+    using L = lz77_sss<pos_t>;
+    auto t0 = std::chrono::steady_clock::now();   // timed like lz77_sss.hpp:314-353: around the call only
+#define RUN(FM, PM) L::template factorize_approximate<FM, PM, tau>(T, N, out, prm)
+    if (fact_mode == greedy) {
+        switch (phr_mode) {
+            case lpf_naive: RUN(greedy, lpf_naive); break;
+            case lpf_lnf_naive: RUN(greedy, lpf_lnf_naive); break;
+            case lpf_opt: RUN(greedy, lpf_opt); break;
+            case lpf_lnf_opt: RUN(greedy, lpf_lnf_opt); break;
+            default: return -1;
+        }
+    } else if (fact_mode == greedy_naive && phr_mode == lpf_opt) {
+        RUN(greedy_naive, lpf_opt);
+    } else {
+        return -1;
+    }
+#undef RUN
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return (int64_t)sink.z;
+}
+
+// Mirror of the generator inside rk_prime<107>::random64 (rolling_hash.hpp:127-130): a
+// function-local static mt19937_64 seeded once from (the pinned) std::random_device, one draw
+// from uniform_int_distribution<uint64_t>(257, 2^20-1) per rk_prime constructed with base 0.
+// rolling_hash_index_107 constructs num_patt_lens = 5 of them per factorization
+// (rolling_hash_index_107.hpp:72-75), in order of pattern-length index.
+std::mt19937_64& mirror() {
+    static std::mt19937_64 g(ORACLE_PINNED_SEED);
+    return g;
+}
+uint64_t draw(std::mt19937_64& g) {
+    return std::uniform_int_distribution<uint64_t>(257, (uint64_t(1) << 20) - 1)(g);
+}
+}  // namespace
+
+extern "C" {
+
+uint64_t refdrv_tau() { return REF_TAU; }
+int refdrv_max_threads() { return omp_get_max_threads(); }
+uint64_t refdrv_sizeof_rk_prime() { return sizeof(lce::rolling_hash::rk_prime<107>); }
+
+void refdrv_set_sss_params(uint32_t base, uint32_t qmax) {
+    oracle::g_sss_base = base;
+    oracle::g_sss_qmax = qmax;
+}
+
+// The 5 gap-index bases the NEXT refdrv_factorize_approximate call of this library will use.
+void refdrv_peek_next_bases(uint64_t out[5]) {
+    std::mt19937_64 g = mirror();
+    for (int i = 0; i < 5; i++) out[i] = draw(g);
+}
+
+// phr_mode / fact_mode: the reference's enum values (lz77_sss.hpp:47-58).  pos_t = uint32_t iff
+// n <= UINT32_MAX, as the reference CLIs choose (cli/lz77_sss_3_aprx.cpp:73).
+// Returns z (number of factors; may exceed cap, then only the first cap are stored) or <0.
+int64_t refdrv_factorize_approximate(const uint8_t* text, uint64_t n, int phr_mode, int fact_mode,
+                                     int num_threads, uint64_t* src, uint64_t* len, uint64_t cap,
+                                     double* seconds) {
+    if (n == 0) return -2;
+    sink_t s { src, len, cap, 0 };
+    int64_t z;
+    if (n <= 0xFFFFFFFFull) z = run_approximate<uint32_t, REF_TAU>(text, n, phr_mode, fact_mode, num_threads, s, seconds);
+    else z = run_approximate<uint64_t, REF_TAU>(text, n, phr_mode, fact_mode, num_threads, s, seconds);
+    if (z >= 0 && fact_mode == greedy) {
+        int builds = (phr_mode == lpf_lnf_naive || phr_mode == lpf_lnf_opt) ? 1 : 1;
+        for (int i = 0; i < 5 * builds; i++) draw(mirror());   // advance past the bases that run consumed
+    }
+    return z;
+}
+
+// lz77_sss<>::decode (algorithms/common.cpp:33-54)
+int refdrv_decode(const uint64_t* src, const uint64_t* len, uint64_t z, uint8_t* out, uint64_t n) {
+    std::vector<lz77_sss<uint64_t>::factor> f(z);
+    for (uint64_t i = 0; i < z; i++) f[i] = { src[i], len[i] };
+    lz77_sss<uint64_t>::decode(f.begin(), reinterpret_cast<char*>(out), n);
+    return 0;
+}
+}

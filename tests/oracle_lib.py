@@ -1,0 +1,211 @@
+"""ctypes bindings of the ORACLE libraries (test infrastructure; never imported by the product).
+
+liboracle.so : oracle/restate/lz77_sss_restate.cpp — standalone CPU restatement (travels to the GPU box)
+libref_tau*.so: oracle/ref/ref_driver.cpp — the reference's own headers + oracle/shim (built only
+                where /root/reference exists; the prebuilt files travel in oracle/_ref/)
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+DEFAULT_SSS_BASE = 0x9E3779B1
+DEFAULT_QMAX = 32
+LPF_NAIVE, LPF_LNF_NAIVE, LPF_OPT, LPF_LNF_OPT = 0, 1, 2, 3      # lz77_sss.hpp:47-52
+GREEDY_NAIVE, GREEDY, SKIP_PHRASES = 0, 1, 2                      # lz77_sss.hpp:54-58
+
+_u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+_u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+
+
+class OracleStats(C.Structure):
+    _fields_ = [("size_sss", C.c_uint64), ("num_lpf", C.c_uint64), ("len_lpf_phr", C.c_uint64),
+                ("num_gaps", C.c_uint64), ("patt_lens", C.c_uint64 * 5), ("roll_threshold", C.c_uint64),
+                ("table_entries", C.c_uint64), ("has_runs", C.c_uint64)]
+
+
+def build_core():
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR, "core"], check=True)
+
+
+def build_ref():
+    if os.path.isdir("/root/reference/include"):
+        subprocess.run(["make", "-s", "-j8", "-C", ORACLE_DIR, "ref"], check=True)
+
+
+_core = None
+
+
+def core():
+    global _core
+    if _core is None:
+        path = os.path.join(ORACLE_DIR, "_build", "liboracle.so")
+        if not os.path.exists(path):
+            build_core()
+        L = C.CDLL(path)
+        L.oracle_sss.restype = C.c_int64
+        L.oracle_sss.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, _u64p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.oracle_q_bruteforce.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_uint32, _u8p]
+        L.oracle_q_anchored.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_uint32, _u8p]
+        L.oracle_window_ids.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, _u32p]
+        L.oracle_sa_s.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_uint32, _u64p, C.c_uint64, _u32p, C.c_int]
+        L.oracle_lcp_s.argtypes = [_u8p, C.c_uint64, _u64p, _u32p, C.c_uint64, _u64p]
+        L.oracle_lce_batch.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, _u64p, _u64p, C.c_uint64, _u64p, _u64p]
+        L.oracle_lpf_opt.restype = C.c_int64
+        L.oracle_lpf_opt.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, _u64p, _u64p, _u64p, _u32p, C.c_uint64]
+        L.oracle_factorize_approximate.restype = C.c_int64
+        L.oracle_factorize_approximate.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, _u64p, C.c_int, C.c_int,
+                                                   _u64p, _u64p, C.c_uint64, C.POINTER(OracleStats)]
+        L.oracle_decode.restype = C.c_int
+        L.oracle_decode.argtypes = [_u64p, _u64p, C.c_uint64, _u8p, C.c_uint64]
+        _core = L
+    return _core
+
+
+def _text(t) -> np.ndarray:
+    if isinstance(t, (bytes, bytearray)):
+        t = np.frombuffer(bytes(t), dtype=np.uint8)
+    return np.ascontiguousarray(t, dtype=np.uint8)
+
+
+def _pad1(a):  # ctypes ndpointer dislikes zero-size arrays on some numpy versions
+    return a if a.size else np.zeros(1, dtype=a.dtype)
+
+
+def sss(text, tau, base=DEFAULT_SSS_BASE, qmax=DEFAULT_QMAX):
+    t = _text(text)
+    n = t.size
+    cap = max(1, n)
+    S = np.zeros(cap, dtype=np.uint64)
+    nq = C.c_uint64(0)
+    s = core().oracle_sss(_pad1(t), n, tau, base, qmax, S, cap, C.byref(nq))
+    return S[:s].copy(), int(nq.value)
+
+
+def q_bruteforce(text, tau, qmax=DEFAULT_QMAX):
+    t = _text(text)
+    q = np.zeros(max(1, t.size), dtype=np.uint8)
+    core().oracle_q_bruteforce(_pad1(t), t.size, tau, qmax, q)
+    return q[:max(0, t.size - tau + 1)]
+
+
+def q_anchored(text, tau, qmax=DEFAULT_QMAX):
+    t = _text(text)
+    q = np.zeros(max(1, t.size), dtype=np.uint8)
+    core().oracle_q_anchored(_pad1(t), t.size, tau, qmax, q)
+    return q[:max(0, t.size - tau + 1)]
+
+
+def window_ids(text, tau, base=DEFAULT_SSS_BASE, qmax=DEFAULT_QMAX):
+    t = _text(text)
+    ids = np.zeros(t.size + 2, dtype=np.uint32)
+    core().oracle_window_ids(_pad1(t), t.size, tau, base, qmax, ids)
+    return ids[:max(0, t.size - tau + 2)]
+
+
+def sa_s(text, tau, S, qmax=DEFAULT_QMAX, naive=False):
+    t = _text(text)
+    S = np.ascontiguousarray(S, dtype=np.uint64)
+    sa = np.zeros(max(1, S.size), dtype=np.uint32)
+    core().oracle_sa_s(_pad1(t), t.size, tau, qmax, _pad1(S), S.size, sa, int(naive))
+    return sa[:S.size]
+
+
+def lcp_s(text, S, sa):
+    t = _text(text)
+    S = np.ascontiguousarray(S, dtype=np.uint64)
+    sa = np.ascontiguousarray(sa, dtype=np.uint32)
+    out = np.zeros(max(1, S.size), dtype=np.uint64)
+    core().oracle_lcp_s(_pad1(t), t.size, _pad1(S), _pad1(sa), S.size, out)
+    return out[:S.size]
+
+
+def lce_batch(text, tau, qi, qj, base=DEFAULT_SSS_BASE, qmax=DEFAULT_QMAX):
+    t = _text(text)
+    qi = np.ascontiguousarray(qi, dtype=np.uint64)
+    qj = np.ascontiguousarray(qj, dtype=np.uint64)
+    a = np.zeros(qi.size, dtype=np.uint64)
+    b = np.zeros(qi.size, dtype=np.uint64)
+    core().oracle_lce_batch(t, t.size, tau, base, qmax, qi, qj, qi.size, a, b)
+    return a, b
+
+
+def lpf_opt(text, tau, p_ref=1, base=DEFAULT_SSS_BASE, qmax=DEFAULT_QMAX):
+    t = _text(text)
+    cap = t.size + 1
+    beg = np.zeros(cap, dtype=np.uint64); end = np.zeros(cap, dtype=np.uint64)
+    src = np.zeros(cap, dtype=np.uint64); blk = np.zeros(cap, dtype=np.uint32)
+    k = core().oracle_lpf_opt(_pad1(t), t.size, tau, base, qmax, p_ref, beg, end, src, blk, cap)
+    return beg[:k].copy(), end[:k].copy(), src[:k].copy(), blk[:k].copy()
+
+
+def factorize(text, tau, bases, p_ref=1, pos_bits=32, sss_base=DEFAULT_SSS_BASE, qmax=DEFAULT_QMAX):
+    """CPU restatement of factorize_approximate<greedy, lpf_opt, tau>. Returns (src, len, stats)."""
+    t = _text(text)
+    cap = t.size + 1
+    src = np.zeros(cap, dtype=np.uint64); ln = np.zeros(cap, dtype=np.uint64)
+    st = OracleStats()
+    b = np.ascontiguousarray(bases, dtype=np.uint64)
+    z = core().oracle_factorize_approximate(_pad1(t), t.size, tau, sss_base, qmax, b, p_ref, pos_bits, src, ln, cap, C.byref(st))
+    assert 0 <= z <= cap
+    return src[:z].copy(), ln[:z].copy(), st
+
+
+def decode(src, ln, n):
+    src = np.ascontiguousarray(src, dtype=np.uint64)
+    ln = np.ascontiguousarray(ln, dtype=np.uint64)
+    out = np.zeros(max(1, n), dtype=np.uint8)
+    rc = core().oracle_decode(_pad1(src), _pad1(ln), src.size, out, n)
+    assert rc == 0, rc
+    return out[:n]
+
+
+_ref = {}
+
+
+def ref_available(tau=512):
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", f"libref_tau{tau}.so"))
+
+
+def ref(tau):
+    if tau not in _ref:
+        path = os.path.join(ORACLE_DIR, "_ref", f"libref_tau{tau}.so")
+        L = C.CDLL(path)
+        L.refdrv_tau.restype = C.c_uint64
+        L.refdrv_sizeof_rk_prime.restype = C.c_uint64
+        L.refdrv_set_sss_params.argtypes = [C.c_uint32, C.c_uint32]
+        L.refdrv_peek_next_bases.argtypes = [_u64p]
+        L.refdrv_factorize_approximate.restype = C.c_int64
+        L.refdrv_factorize_approximate.argtypes = [_u8p, C.c_uint64, C.c_int, C.c_int, C.c_int, _u64p, _u64p, C.c_uint64,
+                                                   C.POINTER(C.c_double)]
+        L.refdrv_decode.argtypes = [_u64p, _u64p, C.c_uint64, _u8p, C.c_uint64]
+        assert L.refdrv_tau() == tau
+        _ref[tau] = L
+    return _ref[tau]
+
+
+def ref_factorize(text, tau, p=1, phr_mode=LPF_OPT, fact_mode=GREEDY, sss_base=DEFAULT_SSS_BASE, qmax=DEFAULT_QMAX):
+    """The reference's own factorize_approximate. Returns (src, len, bases_used, seconds)."""
+    t = _text(text)
+    L = ref(tau)
+    L.refdrv_set_sss_params(sss_base, qmax)
+    bases = np.zeros(5, dtype=np.uint64)
+    L.refdrv_peek_next_bases(bases)
+    cap = t.size + 1
+    src = np.zeros(cap, dtype=np.uint64); ln = np.zeros(cap, dtype=np.uint64)
+    sec = C.c_double(0)
+    z = L.refdrv_factorize_approximate(t, t.size, phr_mode, fact_mode, p, src, ln, cap, C.byref(sec))
+    assert 0 <= z <= cap, z
+    return src[:z].copy(), ln[:z].copy(), bases, sec.value
+
+
+def ref_decode(src, ln, n, tau=512):
+    out = np.zeros(max(1, n), dtype=np.uint8)
+    ref(tau).refdrv_decode(np.ascontiguousarray(src, dtype=np.uint64), np.ascontiguousarray(ln, dtype=np.uint64), len(src), out, n)
+    return out[:n]
