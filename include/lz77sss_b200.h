@@ -1,0 +1,128 @@
+/* lz77sss_b200.h — C ABI of the B200-native lz77-sss hot path (liblz77sss_b200.so).
+ *
+ * The reference (LukasNalbach/lz77-sss) has no FFI layer: its boundary is the header-only template API
+ *   lz77_sss<pos_t>::factorize_approximate<fact_mode, phr_mode, tau>(input, n, output, {num_threads, log})
+ *   lz77_sss<pos_t>::factorize_exact<...>(...)      lz77_sss<pos_t>::decode(fact_it, out_it, n)
+ * (/root/reference/include/lz77_sss/lz77_sss.hpp:176-203).  lz77_sss_b200/include/lz77_sss/lz77_sss.hpp keeps those
+ * templates and forwards to the entry points below; INTEGRATION.md shows the reference-side binding.
+ *
+ * Plain C types only; no CUDA or torch types.  All functions return 0 on success or a negative
+ * LZ77SSS_E_* code; lz77sss_last_error() gives the message.  There is no CPU fallback: without a
+ * CUDA device every compute call fails with LZ77SSS_E_CUDA.
+ */
+#ifndef LZ77SSS_B200_H
+#define LZ77SSS_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LZ77SSS_OK 0
+#define LZ77SSS_E_ARG (-1)       /* invalid argument (tau not a power of two in [4,4096], n == 0, ...) */
+#define LZ77SSS_E_CUDA (-2)      /* CUDA runtime error / no device */
+#define LZ77SSS_E_UNSUPPORTED (-3) /* mode not built yet (see DESIGN.md scope table) */
+#define LZ77SSS_E_INTERNAL (-4)  /* an internal invariant failed; the result must not be used */
+#define LZ77SSS_E_STATE (-5)     /* introspection call without a preceding factorization */
+
+/* enum values of the reference: lz77_sss.hpp:47-58 */
+#define LZ77SSS_PHR_LPF_NAIVE 0
+#define LZ77SSS_PHR_LPF_LNF_NAIVE 1
+#define LZ77SSS_PHR_LPF_OPT 2
+#define LZ77SSS_PHR_LPF_LNF_OPT 3
+#define LZ77SSS_FACT_GREEDY_NAIVE 0
+#define LZ77SSS_FACT_GREEDY 1
+#define LZ77SSS_FACT_SKIP_PHRASES 2
+
+typedef struct lz77sss_handle lz77sss_handle;
+
+/* Everything the factor stream is a function of.  The reference draws its
+ * rolling-hash bases from std::random_device (rolling_hash.hpp:30-39,127-130); here they are explicit. */
+typedef struct lz77sss_config {
+    uint32_t struct_size;   /* = sizeof(lz77sss_config) */
+    uint32_t tau;           /* template parameter tau (lz77_sss.hpp:179); power of two, 4..4096 */
+    uint32_t num_threads;   /* parameters::num_threads (lz77_sss.hpp:67-70): the LOGICAL partition count p of
+                               build_LPF_opt (lpf_opt.cpp:50-56); it changes the factor stream, so it is kept as a
+                               parameter and is independent of the number of GPUs.  0 -> 1 */
+    uint32_t pos_bits;      /* 32 or 64: sizeof(pos_t)*8 of the replaced lz77_sss<pos_t> (gap table sizing,
+                               rolling_hash_index_107.hpp:59-67); 0 -> 32 iff n <= UINT32_MAX (cli/lz77_sss_3_aprx.cpp:73) */
+    uint32_t phr_mode;      /* LZ77SSS_PHR_* ; only LPF_OPT is implemented so far */
+    uint32_t fact_mode;     /* LZ77SSS_FACT_* ; only GREEDY is implemented so far */
+    uint32_t sss_base;      /* multiplier of the window fingerprint of the synchronizing set; 0 -> 0x9E3779B1 */
+    uint32_t sss_qmax;      /* period bound cap of the low-period set Q; 0xFFFFFFFF -> 32 */
+    uint64_t gap_bases[5];  /* bases of the five rk_prime<107> of the gap index (rolling_hash_index_107.hpp:72-75),
+                               each in [257, 2^20-1] (rolling_hash.hpp:31-36) */
+    int32_t device;         /* CUDA device ordinal */
+    uint32_t log;           /* parameters::log: print phase times to stdout */
+} lz77sss_config;
+
+/* phase times of the last factorization, nanoseconds, keyed like the reference's log_phase names
+ *  plus the copies. */
+typedef struct lz77sss_stats {
+    uint64_t n, size_sss, num_q, num_factors;
+    uint64_t num_lpf, len_lpf_phr, num_gaps, patt_lens[5], roll_threshold, table_entries;
+    uint64_t ctx_levels, doubling_rounds, gap_positions_hashed;
+    uint64_t t_h2d_ns, t_sss_ns, t_sort_ns, t_lce_ns, t_lpf_ns, t_d2h_ns, t_chain_ns, t_gap_hash_ns, t_emit_ns, t_total_ns;
+    uint64_t kernel_launches;
+} lz77sss_stats;
+
+/* factor callback: lz77_sss<pos_t>::factor {src,len} by value, in text order, on the calling thread
+ * (lz77_sss.hpp:129-131; len == 0 means a literal whose byte is src). */
+typedef void (*lz77sss_emit_fn)(void* ctx, uint64_t src, uint64_t len);
+
+/* Ready-made callback for callers that just want the factors in two arrays (bindings from languages where a
+ * per-factor callback is expensive): pass lz77sss_sink_emit as emit and a lz77sss_factor_sink* as ctx.
+ * count keeps counting past cap; only the first cap factors are stored. */
+typedef struct lz77sss_factor_sink {
+    uint64_t* src;
+    uint64_t* len;
+    uint64_t cap;
+    uint64_t count;
+} lz77sss_factor_sink;
+void lz77sss_sink_emit(void* ctx, uint64_t src, uint64_t len);
+
+const char* lz77sss_last_error(void);
+const char* lz77sss_version(void);
+int lz77sss_device_count(void);
+
+int lz77sss_create(const lz77sss_config* cfg, lz77sss_handle** out);
+void lz77sss_destroy(lz77sss_handle* h);
+
+/* lz77_sss<pos_t>::factorize_approximate<greedy, lpf_opt, tau> (lz77_sss.hpp:176-186).
+ * text: HOST pointer to n bytes (no padding required); copied to the device inside the call. */
+int lz77sss_factorize_approximate(lz77sss_handle* h, const uint8_t* text, uint64_t n, lz77sss_emit_fn emit, void* ctx);
+
+/* Same, with the text already resident in device memory: d_text is a DEVICE pointer to a buffer obtained from
+ * lz77sss_device_text_alloc (which provides the zero padding the kernels rely on).  host_text must hold the
+ * same n bytes: the sequential greedy emission runs on the host and reads the text there. */
+int lz77sss_device_text_alloc(lz77sss_handle* h, uint64_t n, uint8_t** d_text);
+int lz77sss_device_text_upload(lz77sss_handle* h, uint8_t* d_text, const uint8_t* host_text, uint64_t n);
+int lz77sss_device_text_free(lz77sss_handle* h, uint8_t* d_text);
+int lz77sss_factorize_approximate_device(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n,
+                                         lz77sss_emit_fn emit, void* ctx);
+
+/* lz77_sss<pos_t>::decode (algorithms/common.cpp:33-54): z factors -> n bytes into the HOST buffer out. */
+int lz77sss_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, uint64_t z, uint8_t* out, uint64_t n);
+
+/* ---- stage-level entry points (used by the parity tests and by bench.py's kernel timing) ---- */
+/* Only the synchronizing set of a host text (stage K1+K2). count_out = |S|; S_out may be NULL. */
+int lz77sss_build_sss(lz77sss_handle* h, const uint8_t* text, uint64_t n, uint64_t* S_out, uint64_t cap, uint64_t* count_out,
+                      uint64_t* num_q_out);
+/* Re-run the K1+K2 kernel `iters` times on a device-resident text and return the mean kernel time (CUDA events). */
+int lz77sss_time_sss_kernel(lz77sss_handle* h, const uint8_t* d_text, uint64_t n, int iters, double* ms_out,
+                            uint64_t* count_out);
+/* Introspection of the last factorization on this handle (arrays of |S| entries unless noted). */
+int lz77sss_get_stats(lz77sss_handle* h, lz77sss_stats* out);
+int lz77sss_get_sss(lz77sss_handle* h, uint64_t* out, uint64_t cap, uint64_t* count);
+int lz77sss_get_sa_s(lz77sss_handle* h, uint32_t* out, uint64_t cap, uint64_t* count);
+int lz77sss_get_lcp_s(lz77sss_handle* h, uint64_t* out, uint64_t cap, uint64_t* count);
+/* LPF phrases of build_LPF_opt, concatenated over the logical blocks; blk_out[k] = block index */
+int lz77sss_get_lpf(lz77sss_handle* h, uint64_t* beg, uint64_t* end, uint64_t* src, uint32_t* blk_out, uint64_t cap,
+                    uint64_t* count);
+/* batched exact LCE_R on the text of the last factorization (lce_sss.hpp:102-177) */
+int lz77sss_lce_batch(lz77sss_handle* h, const uint64_t* qi, const uint64_t* qj, uint64_t nq, uint64_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,244 @@
+"""ctypes binding of the C ABI in include/lz77sss_b200.h (liblz77sss_b200.so).
+
+This is harness plumbing for tests/ and bench.py: the product is the shared library and the C++
+header lz77_sss_b200/include/lz77_sss/lz77_sss.hpp.  Nothing here computes; there is no fallback:
+if the library is missing or no CUDA device is present the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liblz77sss_b200.so")
+
+PHR_LPF_NAIVE, PHR_LPF_LNF_NAIVE, PHR_LPF_OPT, PHR_LPF_LNF_OPT = 0, 1, 2, 3
+FACT_GREEDY_NAIVE, FACT_GREEDY, FACT_SKIP_PHRASES = 0, 1, 2
+DEFAULT_SSS_BASE = 0x9E3779B1
+DEFAULT_GAP_BASES = (65599, 131071, 262147, 524309, 1048573)
+
+EXPORTS = [
+    "lz77sss_last_error", "lz77sss_version", "lz77sss_device_count", "lz77sss_create", "lz77sss_destroy",
+    "lz77sss_factorize_approximate", "lz77sss_device_text_alloc", "lz77sss_device_text_upload",
+    "lz77sss_device_text_free", "lz77sss_factorize_approximate_device", "lz77sss_decode", "lz77sss_build_sss",
+    "lz77sss_time_sss_kernel", "lz77sss_get_stats", "lz77sss_get_sss", "lz77sss_get_sa_s", "lz77sss_get_lcp_s",
+    "lz77sss_get_lpf", "lz77sss_lce_batch", "lz77sss_sink_emit",
+]
+
+
+class Config(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("tau", C.c_uint32), ("num_threads", C.c_uint32), ("pos_bits", C.c_uint32),
+                ("phr_mode", C.c_uint32), ("fact_mode", C.c_uint32), ("sss_base", C.c_uint32), ("sss_qmax", C.c_uint32),
+                ("gap_bases", C.c_uint64 * 5), ("device", C.c_int32), ("log", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("n", "size_sss", "num_q", "num_factors", "num_lpf", "len_lpf_phr", "num_gaps")] + \
+               [("patt_lens", C.c_uint64 * 5)] + \
+               [(k, C.c_uint64) for k in ("roll_threshold", "table_entries", "ctx_levels", "doubling_rounds",
+                                          "gap_positions_hashed", "t_h2d_ns", "t_sss_ns", "t_sort_ns", "t_lce_ns",
+                                          "t_lpf_ns", "t_d2h_ns", "t_chain_ns", "t_gap_hash_ns", "t_emit_ns", "t_total_ns",
+                                          "kernel_launches")]
+
+    def as_dict(self):
+        d = {}
+        for k, _ in self._fields_:
+            v = getattr(self, k)
+            d[k] = list(v) if k == "patt_lens" else int(v)
+        return d
+
+
+class Sink(C.Structure):
+    _fields_ = [("src", C.POINTER(C.c_uint64)), ("len", C.POINTER(C.c_uint64)), ("cap", C.c_uint64), ("count", C.c_uint64)]
+
+
+class Lz77SssError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"lz77sss error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                    "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.lz77sss_last_error.restype = C.c_char_p
+        L.lz77sss_version.restype = C.c_char_p
+        L.lz77sss_create.argtypes = [C.POINTER(Config), C.POINTER(C.c_void_p)]
+        L.lz77sss_destroy.argtypes = [C.c_void_p]
+        L.lz77sss_destroy.restype = None
+        L.lz77sss_factorize_approximate.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+        L.lz77sss_device_text_alloc.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]
+        L.lz77sss_device_text_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+        L.lz77sss_device_text_free.argtypes = [C.c_void_p, C.c_void_p]
+        L.lz77sss_factorize_approximate_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+        L.lz77sss_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]
+        L.lz77sss_build_sss.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.lz77sss_time_sss_kernel.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+        L.lz77sss_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+        L.lz77sss_get_sss.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_get_sa_s.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_get_lcp_s.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_get_lpf.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_lce_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise Lz77SssError(rc, lib().lz77sss_last_error().decode())
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+def _u8(text) -> np.ndarray:
+    if isinstance(text, (bytes, bytearray, memoryview)):
+        text = np.frombuffer(bytes(text), dtype=np.uint8)
+    return np.ascontiguousarray(text, dtype=np.uint8)
+
+
+class Factorizer:
+    """One lz77sss_handle: factorize_approximate<greedy, lpf_opt, tau> with every parameter explicit."""
+
+    def __init__(self, tau=512, num_threads=1, gap_bases=DEFAULT_GAP_BASES, pos_bits=0, sss_base=DEFAULT_SSS_BASE,
+                 sss_qmax=32, device=0, phr_mode=PHR_LPF_OPT, fact_mode=FACT_GREEDY, log=False):
+        cfg = Config()
+        cfg.struct_size = C.sizeof(Config)
+        cfg.tau, cfg.num_threads, cfg.pos_bits = tau, num_threads, pos_bits
+        cfg.phr_mode, cfg.fact_mode = phr_mode, fact_mode
+        cfg.sss_base, cfg.sss_qmax = sss_base, sss_qmax
+        for i in range(5):
+            cfg.gap_bases[i] = int(gap_bases[i])
+        cfg.device, cfg.log = device, int(log)
+        self._h = C.c_void_p()
+        _check(lib().lz77sss_create(C.byref(cfg), C.byref(self._h)))
+        self.tau = tau
+
+    def close(self):
+        if self._h:
+            lib().lz77sss_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # --- the public path -------------------------------------------------------------------------
+    def _sink(self, cap):
+        src = np.empty(cap, dtype=np.uint64)
+        ln = np.empty(cap, dtype=np.uint64)
+        s = Sink(src.ctypes.data_as(C.POINTER(C.c_uint64)), ln.ctypes.data_as(C.POINTER(C.c_uint64)), cap, 0)
+        return src, ln, s
+
+    def factorize(self, text, cap=None):
+        """Host text -> (src, len) arrays (len == 0: literal byte in src)."""
+        t = _u8(text)
+        cap = cap if cap is not None else t.size + 1
+        src, ln, s = self._sink(cap)
+        emit = C.cast(lib().lz77sss_sink_emit, C.c_void_p)
+        _check(lib().lz77sss_factorize_approximate(self._h, _ptr(t), t.size, emit, C.byref(s)))
+        z = int(s.count)
+        if z > cap:
+            raise RuntimeError(f"factor sink too small: {z} > {cap}")
+        return src[:z], ln[:z]
+
+    def factorize_into(self, text_ptr, n, sink, src_keepalive=None):
+        """Zero-copy variant for bench.py: text_ptr is a host address (e.g. pinned), sink a prepared Sink."""
+        emit = C.cast(lib().lz77sss_sink_emit, C.c_void_p)
+        sink.count = 0
+        _check(lib().lz77sss_factorize_approximate(self._h, C.c_void_p(text_ptr), n, emit, C.byref(sink)))
+        return int(sink.count)
+
+    def device_text(self, text):
+        t = _u8(text)
+        d = C.c_void_p()
+        _check(lib().lz77sss_device_text_alloc(self._h, t.size, C.byref(d)))
+        _check(lib().lz77sss_device_text_upload(self._h, d, _ptr(t), t.size))
+        return d
+
+    def free_device_text(self, d):
+        _check(lib().lz77sss_device_text_free(self._h, d))
+
+    def factorize_device_into(self, d_text, host_ptr, n, sink):
+        emit = C.cast(lib().lz77sss_sink_emit, C.c_void_p)
+        sink.count = 0
+        _check(lib().lz77sss_factorize_approximate_device(self._h, d_text, C.c_void_p(host_ptr), n, emit, C.byref(sink)))
+        return int(sink.count)
+
+    def decode(self, src, ln, n):
+        src = np.ascontiguousarray(src, dtype=np.uint64)
+        ln = np.ascontiguousarray(ln, dtype=np.uint64)
+        out = np.empty(n, dtype=np.uint8)
+        _check(lib().lz77sss_decode(self._h, _ptr(src), _ptr(ln), src.size, _ptr(out), n))
+        return out
+
+    # --- stage-level -----------------------------------------------------------------------------
+    def build_sss(self, text):
+        t = _u8(text)
+        cap = max(1, t.size)
+        S = np.empty(cap, dtype=np.uint64)
+        cnt, nq = C.c_uint64(0), C.c_uint64(0)
+        _check(lib().lz77sss_build_sss(self._h, _ptr(t), t.size, _ptr(S), cap, C.byref(cnt), C.byref(nq)))
+        return S[:cnt.value].copy(), int(nq.value)
+
+    def time_sss_kernel(self, d_text, n, iters=5):
+        ms, cnt = C.c_double(0), C.c_uint64(0)
+        _check(lib().lz77sss_time_sss_kernel(self._h, d_text, n, iters, C.byref(ms), C.byref(cnt)))
+        return ms.value, int(cnt.value)
+
+    def stats(self):
+        st = Stats()
+        _check(lib().lz77sss_get_stats(self._h, C.byref(st)))
+        return st.as_dict()
+
+    def _get(self, fn, dtype):
+        cnt = C.c_uint64(0)
+        _check(fn(self._h, None, 0, C.byref(cnt)))
+        out = np.empty(max(1, cnt.value), dtype=dtype)
+        _check(fn(self._h, _ptr(out), cnt.value, C.byref(cnt)))
+        return out[:cnt.value]
+
+    def sss(self):
+        return self._get(lib().lz77sss_get_sss, np.uint64)
+
+    def sa_s(self):
+        return self._get(lib().lz77sss_get_sa_s, np.uint32)
+
+    def lcp_s(self):
+        return self._get(lib().lz77sss_get_lcp_s, np.uint64)
+
+    def lpf(self):
+        cnt = C.c_uint64(0)
+        _check(lib().lz77sss_get_lpf(self._h, None, None, None, None, 0, C.byref(cnt)))
+        k = max(1, cnt.value)
+        beg = np.empty(k, dtype=np.uint64); end = np.empty(k, dtype=np.uint64)
+        src = np.empty(k, dtype=np.uint64); blk = np.empty(k, dtype=np.uint32)
+        _check(lib().lz77sss_get_lpf(self._h, _ptr(beg), _ptr(end), _ptr(src), _ptr(blk), cnt.value, C.byref(cnt)))
+        k = cnt.value
+        return beg[:k], end[:k], src[:k], blk[:k]
+
+    def lce_batch(self, qi, qj):
+        qi = np.ascontiguousarray(qi, dtype=np.uint64)
+        qj = np.ascontiguousarray(qj, dtype=np.uint64)
+        out = np.empty(max(1, qi.size), dtype=np.uint64)
+        _check(lib().lz77sss_lce_batch(self._h, _ptr(qi), _ptr(qj), qi.size, _ptr(out)))
+        return out[:qi.size]

@@ -1,0 +1,912 @@
+// C-ABI (include/lz77sss_b200.h) and host orchestration of the device pipeline.
+//
+// Mirrors lz77_sss<pos_t>::factorizer::compute_approximation<greedy, lpf_opt>
+// (/root/reference/include/lz77_sss/lz77_sss.hpp:374-491):
+//   build_lce           -> K1+K2 (sss.cu), K3 (suffix.cu), range-min/successor structures (lpf.cu)
+//   build_LPF_opt       -> lpf_candidates kernel (all LCE probes, data-parallel) + the coverage chain on the
+//                          host (lpf_opt.cpp:58-63,87-89: each step depends on the previous phrase end)
+//   get_phrase_info / pattern lengths / table size -> host scalars, same double arithmetic (lz77_sss.hpp:112-122,425-461)
+//   gap index           -> K5 (gap_hash.cu) computes every bucket id; the host keeps only the table of last writers
+//   factorize_greedy    -> thin sequential pass on the host (greedy.cpp:34-140), calls the factor callback
+// The host never computes a fingerprint, never sorts and never builds an index: it consumes device results.
+#include <algorithm>
+#include <array>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/lz77sss_b200.h"
+#include "common.cuh"
+#include "stages.cuh"
+
+namespace lz77sss {
+unsigned long long g_kernel_launches = 0;
+}
+
+using namespace lz77sss;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+struct lpf_t { uint64_t beg, end, src; };
+
+using clk = std::chrono::steady_clock;
+inline uint64_t ns_since(clk::time_point t0) {
+    return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - t0).count();
+}
+
+// pinned host buffer, grow-only
+template <typename T>
+struct hbuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    ~hbuf() { if (p) cudaFreeHost(p); }
+    void reserve(size_t n) {
+        if (n <= cap) return;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        size_t want = n + n / 8 + 64;
+        CUDA_CHECK(cudaMallocHost(&p, want * sizeof(T)));
+        cap = want;
+    }
+    T& operator[](size_t i) { return p[i]; }
+    const T& operator[](size_t i) const { return p[i]; }
+};
+
+constexpr uint64_t FRONT_PAD = 256;   // readable zero bytes before T[0] (leftward LCE loads)
+
+template <typename pos_t>
+struct pipeline {
+    dbuf<pos_t> S;
+    sss_scratch sss;
+    suffix_state<pos_t> suf;
+    lce_state<pos_t> lce;
+    hbuf<pos_t> hS, h_plce, h_nlce, h_plcel, h_nlcel;
+    hbuf<uint32_t> h_pidx, h_nidx;
+    uint64_t s = 0;
+};
+
+}  // namespace
+
+struct lz77sss_handle {
+    lz77sss_config cfg;
+    cudaStream_t st = nullptr;
+    dbuf<uint8_t> text_buf;           // FRONT_PAD + n + TEXT_PAD
+    const uint8_t* d_text = nullptr;  // text of the last factorization (device)
+    uint64_t n = 0;
+    int pos_bytes = 0;                // internal position width of the last factorization
+    pipeline<uint32_t> p32;
+    pipeline<uint64_t> p64;
+    lz77sss_stats stats;
+    bool have_result = false;
+    std::vector<std::vector<lpf_t>> LPF;   // per logical block, without the sentinel
+    // gap bucket ids
+    dbuf<uint64_t> d_rng;
+    dbuf<uint32_t> d_ids;
+    hbuf<uint32_t> h_ids;
+    hbuf<uint64_t> h_rng;
+    std::vector<uint8_t*> user_texts;
+};
+
+namespace {
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+template <typename F>
+int guarded(F f) {
+    try {
+        return f();
+    } catch (const cuda_error& e) {
+        return fail(LZ77SSS_E_CUDA, e.what());
+    } catch (const std::invalid_argument& e) {
+        return fail(LZ77SSS_E_ARG, e.what());
+    } catch (const std::exception& e) {
+        return fail(LZ77SSS_E_INTERNAL, e.what());
+    }
+}
+
+bool valid_tau(uint32_t tau) { return tau >= 4 && tau <= 4096 && (tau & (tau - 1)) == 0; }
+
+uint8_t* alloc_text(dbuf<uint8_t>& buf, uint64_t n, cudaStream_t st) {
+    uint64_t total = FRONT_PAD + n + TEXT_PAD;
+    buf.reserve(total);
+    CUDA_CHECK(cudaMemsetAsync(buf.get(), 0, FRONT_PAD, st));
+    CUDA_CHECK(cudaMemsetAsync(buf.get() + FRONT_PAD + n, 0, TEXT_PAD, st));
+    return buf.get() + FRONT_PAD;
+}
+
+template <typename pos_t>
+pipeline<pos_t>& pipe(lz77sss_handle* h);
+template <> pipeline<uint32_t>& pipe<uint32_t>(lz77sss_handle* h) { return h->p32; }
+template <> pipeline<uint64_t>& pipe<uint64_t>(lz77sss_handle* h) { return h->p64; }
+
+// ---- host side of build_LPF_opt: the coverage chain (lpf_opt.cpp:46-145) over the device-computed candidates ----
+template <typename pos_t>
+void lpf_chain(lz77sss_handle* h, pipeline<pos_t>& P) {
+    const uint64_t n = h->n, s = P.s;
+    const uint32_t p = h->cfg.num_threads;
+    h->LPF.assign(p, {});
+    const pos_t* S = P.hS.p;
+    for (uint32_t i_p = 0; i_p < p; i_p++) {
+        const uint64_t b = (uint64_t)i_p * (n / p);
+        const uint64_t e = i_p == p - 1 ? n : (uint64_t)(i_p + 1) * (n / p);
+        const uint64_t i_min = std::lower_bound(S, S + s, (pos_t)b) - S;
+        const uint64_t i_max = std::lower_bound(S, S + s, (pos_t)e) - S;
+        uint64_t max_end = b;
+        auto& out = h->LPF[i_p];
+        for (uint64_t i = i_min; i < i_max; i++) {
+            while (i + 1 < i_max && (uint64_t)S[i + 1] <= max_end) i++;
+            const uint64_t lst_end = max_end, pos = S[i];
+            lpf_t phr{0, 0, 0};
+            auto candidate = [&](uint32_t sidx, uint64_t lce, uint64_t lcel_max, bool is_psv) {
+                uint64_t src = S[sidx];
+                const uint64_t end = pos + lce;
+                if (end <= lst_end) return;
+                uint64_t beg = pos;
+                if (pos > lst_end && src != 0 && pos != 0) {
+                    const uint64_t cap = pos - lst_end;
+                    // the kernel extended left up to pos - max(block start, S[i-1]); a visit can never ask for more
+                    uint64_t kcap;
+                    {
+                        uint64_t prevpos = b;
+                        if (i >= 2 && (uint64_t)S[i - 1] >= b) prevpos = S[i - 1];
+                        kcap = std::min<uint64_t>(pos - prevpos, src);
+                    }
+                    if (std::min<uint64_t>(cap, src) > kcap) throw std::logic_error("lpf_chain: left-extension cap exceeded");
+                    const uint64_t l = std::min<uint64_t>(lcel_max, cap);
+                    beg -= l;
+                    src -= l;
+                }
+                if (beg < lst_end) {
+                    const uint64_t exc = lst_end - beg;
+                    beg += exc;
+                    src += exc;
+                }
+                if (end > max_end) max_end = end;
+                if (is_psv) {
+                    if (end - beg > 1) phr = {beg, end, src};
+                } else if (end - beg > phr.end - phr.beg) {
+                    phr = {beg, end, src};
+                }
+            };
+            if (P.h_pidx[i] != NONE32) candidate(P.h_pidx[i], P.h_plce[i], P.h_plcel[i], true);
+            if (P.h_nidx[i] != NONE32) {
+                candidate(P.h_nidx[i], P.h_nlce[i], P.h_nlcel[i], false);
+                if (phr.end - phr.beg > 1) out.push_back(phr);     // pushed only inside the NSV branch (lpf_opt.cpp:141-143)
+            }
+        }
+    }
+}
+
+// get_phrase_info (approximate/common.cpp:100-157)
+void phrase_info(lz77sss_handle* h) {
+    auto& st = h->stats;
+    const uint64_t n = h->n;
+    const uint32_t p = h->cfg.num_threads;
+    st.num_gaps = st.num_lpf = st.len_lpf_phr = 0;
+    for (uint32_t i_p = 0; i_p < p; i_p++) {
+        uint64_t gaps = 0, len = 0, cnt = 0;
+        uint64_t b = (uint64_t)i_p * (n / p);
+        uint64_t e = i_p == p - 1 ? n : (uint64_t)(i_p + 1) * (n / p);
+        auto& L = h->LPF[i_p];
+        if (!L.empty()) e = std::max(e, L.back().end);
+        for (uint32_t j = 0; j < i_p; j++)
+            if (!h->LPF[j].empty()) b = std::max(b, h->LPF[j].back().end);
+        size_t i = 0;
+        while (i < L.size() && L[i].end <= b) i++;
+        cnt = L.size() - i;
+        if (cnt > 0) {
+            len += L[i].end - std::max(L[i].beg, b);
+            if (L[i].beg > b) gaps = 1;
+            for (i++; i < L.size(); i++) {
+                len += L[i].end - L[i].beg;
+                if (L[i].beg > L[i - 1].end) gaps++;
+            }
+            if (L.back().end < e) gaps++;
+        } else {
+            gaps = 1;
+        }
+        st.num_gaps += gaps;
+        st.num_lpf += cnt;
+        st.len_lpf_phr += len;
+    }
+}
+
+struct gap_params {
+    std::array<uint64_t, 5> patt_lens{};
+    uint64_t roll_threshold = 0, table_entries = 0;
+};
+
+// pattern lengths and table size (lz77_sss.hpp:99-122,425-461; rolling_hash_index_107.hpp:59-67), malloc_count == 0
+gap_params choose_gap_params(lz77sss_handle* h) {
+    using entry_t = std::pair<double, std::array<uint64_t, 5>>;
+    static const double infty = std::numeric_limits<double>::max();
+    static const std::array<entry_t, 10> table{{{6, {2, 3, 4, 5, 6}}, {8, {2, 3, 4, 6, 8}}, {12, {2, 3, 4, 8, 12}},
+        {16, {2, 4, 6, 9, 16}}, {32, {2, 4, 6, 10, 20}}, {64, {2, 4, 7, 12, 28}}, {128, {2, 4, 8, 16, 36}},
+        {256, {2, 5, 10, 20, 42}}, {1024, {2, 6, 12, 24, 48}}, {infty, {2, 8, 16, 32, 64}}}};
+    auto& st = h->stats;
+    const uint64_t n = h->n;
+    const unsigned sizeof_pos = h->cfg.pos_bits / 8;
+    gap_params g;
+    uint64_t len_gaps = n - st.len_lpf_phr;
+    if (sizeof_pos == 4) len_gaps = (uint32_t)len_gaps;
+    const double rel_len_gaps = len_gaps / (double)n;
+    const double avg_gap_len = len_gaps / (double)st.num_gaps;
+    const double avg_lpf_phr_len = st.len_lpf_phr / (double)st.num_lpf;
+    const uint64_t target = std::min<uint64_t>(uint64_t(1) << 30,
+        std::max<uint64_t>({uint64_t(1) << 20, uint64_t(0), (uint64_t)((n / 3.0) * rel_len_gaps)}));
+    const double guess = std::min<double>({avg_gap_len, avg_lpf_phr_len, 8.0 * std::pow(128, 1.0 - rel_len_gaps)});
+    for (auto& [threshold, lens] : table)
+        if (guess <= threshold) { g.patt_lens = lens; break; }
+    for (int j = 0; j < 5; j++) g.roll_threshold += g.patt_lens[j];
+    g.roll_threshold /= 5;
+    // sizeof(rk_prime<107>) = 80 on x86-64 libstdc++ (checked against the reference build in tests)
+    const int64_t rolling_hash_size = (80 + 16 * 256 * 256) * 5;
+    uint64_t a = 1 << 20, bb;
+    if (sizeof_pos == 4) bb = (uint32_t)(n * 0.1);
+    else bb = (uint64_t)(n * 0.1);
+    const int64_t min_index = std::max<uint64_t>(a, bb) / sizeof_pos;
+    const int64_t max_index = (int64_t)(1 << 30) / sizeof_pos;
+    const int64_t tgt_index = std::max<int64_t>(0, (int64_t)target - rolling_hash_size) / sizeof_pos;
+    const uint64_t size_h = std::min<int64_t>(max_index, std::max<int64_t>(min_index, tgt_index));
+    const uint8_t lg = std::round(std::log2(size_h));
+    g.table_entries = uint64_t(1) << lg;
+    return g;
+}
+
+// Bucket ids of the gap index for the text ranges the emission can touch, fetched from the device.
+struct bucket_provider {
+    lz77sss_handle* h;
+    gap_hash_params gp;
+    std::vector<uint64_t> beg, end, off;   // main ranges
+    size_t cur = 0;
+    // on-demand range
+    uint64_t t_beg = 0, t_end = 0;
+    std::vector<uint32_t> t_ids;
+    uint64_t hashed = 0;
+
+    void fetch_main() {
+        const uint64_t nr = beg.size();
+        uint64_t total = 0;
+        off.resize(nr);
+        for (uint64_t k = 0; k < nr; k++) { off[k] = total; total += end[k] - beg[k]; }
+        hashed += total;
+        if (!total) return;
+        h->h_rng.reserve(3 * nr);
+        std::memcpy(h->h_rng.p, beg.data(), nr * 8);
+        std::memcpy(h->h_rng.p + nr, end.data(), nr * 8);
+        std::memcpy(h->h_rng.p + 2 * nr, off.data(), nr * 8);
+        h->d_rng.reserve(3 * nr);
+        h->d_ids.reserve(5 * total);
+        h->h_ids.reserve(5 * total);
+        CUDA_CHECK(cudaMemcpyAsync(h->d_rng.get(), h->h_rng.p, 3 * nr * 8, cudaMemcpyHostToDevice, h->st));
+        gap_bucket_ids(h->d_text, h->n, gp, h->d_rng.get(), h->d_rng.get() + nr, h->d_rng.get() + 2 * nr, nr, total,
+                       h->d_ids.get(), h->st);
+        CUDA_CHECK(cudaMemcpyAsync(h->h_ids.p, h->d_ids.get(), 5 * total * 4, cudaMemcpyDeviceToHost, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+    }
+    void fetch_temp(uint64_t pos) {
+        // position outside the precomputed ranges (a gap factor ran over whole LPF phrases, greedy.cpp:68-77,
+        // or the stale-fingerprint window at n - patt_len): hash a fresh stretch on the device
+        t_beg = pos;
+        t_end = std::min<uint64_t>(h->n, pos + 8192);
+        const uint64_t total = t_end - t_beg;
+        hashed += total;
+        dbuf<uint64_t> rng;
+        dbuf<uint32_t> ids;
+        rng.reserve(3);
+        ids.reserve(5 * total);
+        uint64_t hr[3] = {t_beg, t_end, 0};
+        CUDA_CHECK(cudaMemcpyAsync(rng.get(), hr, 24, cudaMemcpyHostToDevice, h->st));
+        gap_bucket_ids(h->d_text, h->n, gp, rng.get(), rng.get() + 1, rng.get() + 2, 1, total, ids.get(), h->st);
+        t_ids.resize(5 * total);
+        CUDA_CHECK(cudaMemcpyAsync(t_ids.data(), ids.get(), 5 * total * 4, cudaMemcpyDeviceToHost, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+    }
+    // bucket of the window of pattern x starting at pos (pos + patt_len[x] <= n)
+    uint32_t get(uint64_t pos, int x) {
+        if (pos >= t_beg && pos < t_end) return t_ids[5 * (pos - t_beg) + x];
+        if (!beg.empty()) {
+            if (cur >= beg.size() || pos < beg[cur] || pos >= end[cur]) {
+                // ranges are sorted and disjoint
+                size_t k = std::upper_bound(beg.begin(), beg.end(), pos) - beg.begin();
+                if (k > 0 && pos < end[k - 1]) cur = k - 1;
+                else { fetch_temp(pos); return t_ids[x]; }
+            }
+            return h->h_ids[5 * (off[cur] + (pos - beg[cur])) + x];
+        }
+        fetch_temp(pos);
+        return t_ids[x];
+    }
+};
+
+// rolling_hash_index_107 without the fingerprints: cur_pos, the table of last writers, and the rule for stale
+// fingerprints at the end of the text (rolling_hash_index_107.hpp:80-150)
+template <typename ent_t>
+struct gap_index {
+    bucket_provider& bp;
+    uint64_t n;
+    std::array<uint64_t, 5> L;
+    std::vector<ent_t> H;
+    uint64_t cur_pos = 0;
+    bool zero[5];   // fingerprint x was reset at a position where the window no longer fits: it stays 0
+    gap_index(bucket_provider& bp_, uint64_t n_, const gap_params& g) : bp(bp_), n(n_), L(g.patt_lens) {
+        H.assign(g.table_entries, (ent_t)~(ent_t)0);
+        reinit(0);
+    }
+    void reinit(uint64_t pos) {
+        cur_pos = pos;
+        for (int x = 0; x < 5; x++) zero[x] = !(pos + L[x] < n);
+    }
+    void roll() { cur_pos++; }
+    uint32_t bucket(int x) {
+        if (cur_pos + L[x] < n) return bp.get(cur_pos, x);
+        if (zero[x]) return 0;
+        return bp.get(n - L[x], x);     // stale: the last fingerprint that was rolled in
+    }
+    void advance() {
+        for (int x = 0; x < 5; x++)
+            if (cur_pos + L[x] < n) H[bp.get(cur_pos, x)] = (ent_t)cur_pos;
+        cur_pos++;
+    }
+    void advance_i(int x) {
+        if (cur_pos + L[x] < n) H[bp.get(cur_pos, x)] = (ent_t)cur_pos;
+    }
+    uint64_t advance_and_get_occ(int x) {
+        const uint32_t b = bucket(x);
+        const ent_t occ = H[b];
+        H[b] = (ent_t)cur_pos;
+        return occ == (ent_t)~(ent_t)0 ? ~0ull : (uint64_t)occ;
+    }
+};
+
+inline uint64_t host_lce(const uint8_t* T, uint64_t n, uint64_t src, uint64_t pos) {   // src < pos
+    const uint64_t lim = n - pos;
+    uint64_t k = 0;
+    while (k + 8 <= lim) {
+        uint64_t a, b;
+        std::memcpy(&a, T + src + k, 8);
+        std::memcpy(&b, T + pos + k, 8);
+        if (a != b) return k + (__builtin_ctzll(a ^ b) >> 3);
+        k += 8;
+    }
+    while (k < lim && T[src + k] == T[pos + k]) k++;
+    return k;
+}
+
+// factorize + next_lpf (approximate/factorize/common.cpp:66-111) and factorize_greedy (greedy.cpp:34-140)
+template <typename ent_t>
+uint64_t greedy_emit(lz77sss_handle* h, const uint8_t* T, const gap_params& g, bucket_provider& bp,
+                     lz77sss_emit_fn emit, void* ctx) {
+    const uint64_t n = h->n;
+    const uint32_t p = h->cfg.num_threads;
+    auto& LPF = h->LPF;
+    LPF[p - 1].push_back(lpf_t{n, n + 1, 0});       // sentinel (lz77_sss.hpp:418,423)
+    gap_index<ent_t> idx(bp, n, g);
+    uint64_t num_fact = 0;
+    uint32_t i_p = 0;
+    size_t li = 0;
+    while (LPF[i_p].empty()) i_p++;
+    auto next_lpf = [&]() {
+        lpf_t phr = LPF[i_p][li++];
+        if (li == LPF[i_p].size()) {
+            if (i_p < p - 1 && p > 1) {
+                do {
+                    i_p++;
+                    li = 0;
+                    auto& V = LPF[i_p];
+                    while (li < V.size() && V[li].end <= phr.end) li++;
+                    if (li < V.size() && V[li].beg < phr.end) {
+                        const uint64_t offs = phr.end - V[li].beg;
+                        V[li].beg += offs;
+                        V[li].src += offs;
+                    }
+                } while (li == LPF[i_p].size() && i_p < p - 1);
+            } else {
+                li--;
+            }
+        }
+        return phr;
+    };
+    auto longest_prev_occ = [&](uint64_t pos, uint64_t& f_src, uint64_t& f_len) {   // factorize/common.cpp:33-61
+        f_src = T[pos];
+        f_len = 0;
+        for (int x = 4; x >= 0; x--) {
+            if (f_len == 0) {
+                const uint64_t src = idx.advance_and_get_occ(x);
+                if (src < pos && T[src] == T[pos]) {
+                    f_len = host_lce(T, n, src, pos);
+                    f_src = src;
+                }
+            } else {
+                idx.advance_i(x);
+            }
+        }
+        idx.cur_pos++;
+    };
+    lpf_t ph = next_lpf();
+    for (uint64_t i = 0;;) {
+        uint64_t gap_end = ph.beg;
+        if (i < gap_end) {
+            if (idx.cur_pos < i) {
+                if (i - idx.cur_pos <= g.roll_threshold) {
+                    do { idx.roll(); } while (idx.cur_pos < i);
+                } else {
+                    idx.reinit(i);
+                }
+            }
+            do {
+                uint64_t fs, fl;
+                longest_prev_occ(i, fs, fl);
+                i += std::max<uint64_t>(1, fl);
+                if (i > gap_end) {
+                    if (i <= ph.end) {
+                        fl -= i - gap_end;
+                        i = gap_end;
+                    } else {
+                        do { ph = next_lpf(); } while (ph.end <= i);
+                        while (idx.cur_pos < gap_end) idx.advance();
+                        gap_end = ph.beg;
+                    }
+                }
+                emit(ctx, fs, fl);
+                num_fact++;
+                while (idx.cur_pos < i) idx.advance();
+            } while (i < gap_end);
+        }
+        if (i == n) break;
+        const uint64_t exc = i - gap_end;
+        uint64_t ls = ph.src + exc, ll = (ph.end - ph.beg) - exc;
+        if (idx.cur_pos == i) {
+            uint64_t fs, fl;
+            longest_prev_occ(i, fs, fl);
+            if (fl > ll) { ls = fs; ll = fl; }
+        }
+        emit(ctx, ls, ll);
+        num_fact++;
+        i += ll;
+        while (ph.end <= i) ph = next_lpf();
+    }
+    LPF[p - 1].pop_back();   // keep the introspection view free of the sentinel
+    return num_fact;
+}
+
+template <typename pos_t>
+int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n,
+                   lz77sss_emit_fn emit, void* ctx) {
+    auto& P = pipe<pos_t>(h);
+    auto& st = h->stats;
+    const uint32_t tau = h->cfg.tau;
+    cudaStream_t s = h->st;
+    h->d_text = d_text;
+    h->n = n;
+    h->pos_bytes = sizeof(pos_t);
+    st.n = n;
+
+    // K1+K2
+    auto t0 = clk::now();
+    uint64_t s_cap = n / 2 + 1024;                 // |S| <= number of candidate positions; typical 2n/tau
+    if (tau >= 16) s_cap = std::min<uint64_t>(n, 8 * (n / tau) + 65536);
+    P.S.reserve(s_cap);
+    uint64_t size_s = 0, numq = 0;
+    sss_build(d_text, n, tau, h->cfg.sss_base, h->cfg.sss_qmax, P.S.get(), sizeof(pos_t), s_cap, P.sss, s, &size_s, &numq);
+    if (size_s > s_cap) {                          // rare: denser than expected, redo with the exact size
+        s_cap = size_s;
+        P.S.reserve(s_cap);
+        sss_build(d_text, n, tau, h->cfg.sss_base, h->cfg.sss_qmax, P.S.get(), sizeof(pos_t), s_cap, P.sss, s, &size_s, &numq);
+    }
+    P.s = size_s;
+    st.size_sss = size_s;
+    st.num_q = numq;
+    st.t_sss_ns = ns_since(t0);
+
+    // K3
+    t0 = clk::now();
+    suffix_sort_sync<pos_t>(d_text, n, tau, h->cfg.sss_qmax, P.S.get(), size_s, P.suf, s);
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    st.ctx_levels = P.suf.ctx_levels;
+    st.doubling_rounds = P.suf.doubling_rounds;
+    st.t_sort_ns = ns_since(t0);
+
+    // range-min / nearest-smaller / successor structures, LPF candidates
+    t0 = clk::now();
+    build_lce_structures<pos_t>(d_text, n, tau, P.S.get(), size_s, P.suf, P.lce, s);
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    st.t_lce_ns = ns_since(t0);
+    t0 = clk::now();
+    lpf_candidates<pos_t>(d_text, n, tau, P.S.get(), size_s, h->cfg.num_threads, P.suf, P.lce, s);
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    st.t_lpf_ns = ns_since(t0);
+
+    // candidates to the host
+    t0 = clk::now();
+    if (size_s) {
+        P.hS.reserve(size_s); P.h_pidx.reserve(size_s); P.h_nidx.reserve(size_s);
+        P.h_plce.reserve(size_s); P.h_nlce.reserve(size_s); P.h_plcel.reserve(size_s); P.h_nlcel.reserve(size_s);
+        CUDA_CHECK(cudaMemcpyAsync(P.hS.p, P.S.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(P.h_pidx.p, P.lce.psv_idx.get(), size_s * 4, cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(P.h_nidx.p, P.lce.nsv_idx.get(), size_s * 4, cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(P.h_plce.p, P.lce.psv_lce.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(P.h_nlce.p, P.lce.nsv_lce.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(P.h_plcel.p, P.lce.psv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(P.h_nlcel.p, P.lce.nsv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+    }
+    st.t_d2h_ns = ns_since(t0);
+
+    // coverage chain, statistics, gap parameters (host scalars)
+    t0 = clk::now();
+    lpf_chain<pos_t>(h, P);
+    phrase_info(h);
+    gap_params g = choose_gap_params(h);
+    for (int x = 0; x < 5; x++) st.patt_lens[x] = g.patt_lens[x];
+    st.roll_threshold = g.roll_threshold;
+    st.table_entries = g.table_entries;
+    st.t_chain_ns = ns_since(t0);
+    h->have_result = true;
+    if (g.patt_lens[0] == 0) return fail(LZ77SSS_E_UNSUPPORTED, "degenerate phrase statistics (no LPF phrase or no gap): pattern lengths undefined in the reference (SURVEY.md A7)");
+
+    // K5: bucket ids of every position the emission can insert or probe
+    t0 = clk::now();
+    bucket_provider bp;
+    bp.h = h;
+    for (int x = 0; x < 5; x++) { bp.gp.patt_len[x] = g.patt_lens[x]; bp.gp.base[x] = h->cfg.gap_bases[x]; }
+    bp.gp.mask = g.table_entries - 1;
+    {
+        uint64_t cur = 0;
+        for (auto& V : h->LPF)
+            for (auto& ph : V) {
+                if (ph.end <= cur) continue;
+                const uint64_t b = std::max(ph.beg, cur);
+                bp.beg.push_back(cur);
+                bp.end.push_back(b + 1);
+                cur = ph.end;
+            }
+        if (cur < n) { bp.beg.push_back(cur); bp.end.push_back(n); }
+        // the windows whose fingerprints go stale at the end of the text (n - patt_len) are fetched on demand
+    }
+    bp.fetch_main();
+    st.t_gap_hash_ns = ns_since(t0);
+
+    // greedy emission
+    t0 = clk::now();
+    uint64_t z;
+    if (h->cfg.pos_bits == 32) z = greedy_emit<uint32_t>(h, host_text, g, bp, emit, ctx);
+    else z = greedy_emit<uint64_t>(h, host_text, g, bp, emit, ctx);
+    st.num_factors = z;
+    st.gap_positions_hashed = bp.hashed;
+    st.t_emit_ns = ns_since(t0);
+    return LZ77SSS_OK;
+}
+
+int factorize_dispatch(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n,
+                       lz77sss_emit_fn emit, void* ctx) {
+    if (!h || !host_text || !emit) return fail(LZ77SSS_E_ARG, "null argument");
+    if (n == 0) return fail(LZ77SSS_E_ARG, "empty input");
+    if (h->cfg.phr_mode != LZ77SSS_PHR_LPF_OPT || h->cfg.fact_mode != LZ77SSS_FACT_GREEDY)
+        return fail(LZ77SSS_E_UNSUPPORTED, "only factorize_approximate<greedy, lpf_opt> is implemented");
+    if (h->cfg.num_threads > n) return fail(LZ77SSS_E_ARG, "num_threads > n");
+    if (h->cfg.pos_bits == 32 && n > 0xFFFFFFFFull) return fail(LZ77SSS_E_ARG, "pos_bits == 32 but n > UINT32_MAX");
+    std::memset(&h->stats, 0, sizeof h->stats);
+    h->have_result = false;
+    const unsigned long long l0 = g_kernel_launches;
+    auto t0 = clk::now();
+    int rc;
+    if (n < 0xFFFF0000ull) rc = factorize_impl<uint32_t>(h, d_text, host_text, n, emit, ctx);
+    else rc = factorize_impl<uint64_t>(h, d_text, host_text, n, emit, ctx);
+    h->stats.t_total_ns += ns_since(t0);
+    h->stats.kernel_launches = g_kernel_launches - l0;
+    if (h->cfg.log) {
+        auto& s = h->stats;
+        printf("lz77sss_b200: n=%llu |S|=%llu z=%llu  h2d=%.3f sss=%.3f sort=%.3f lce=%.3f lpf=%.3f d2h=%.3f chain=%.3f gap_hash=%.3f emit=%.3f total=%.3f ms\n",
+               (unsigned long long)s.n, (unsigned long long)s.size_sss, (unsigned long long)s.num_factors, s.t_h2d_ns / 1e6,
+               s.t_sss_ns / 1e6, s.t_sort_ns / 1e6, s.t_lce_ns / 1e6, s.t_lpf_ns / 1e6, s.t_d2h_ns / 1e6, s.t_chain_ns / 1e6,
+               s.t_gap_hash_ns / 1e6, s.t_emit_ns / 1e6, s.t_total_ns / 1e6);
+    }
+    return rc;
+}
+
+template <typename pos_t, typename out_t>
+int copy_out(const pos_t* d, uint64_t cnt, out_t* out, uint64_t cap, uint64_t* count, cudaStream_t st) {
+    if (count) *count = cnt;
+    if (!out) return LZ77SSS_OK;
+    uint64_t m = std::min(cnt, cap);
+    std::vector<pos_t> tmp(m);
+    if (m) {
+        CUDA_CHECK(cudaMemcpyAsync(tmp.data(), d, m * sizeof(pos_t), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+    }
+    for (uint64_t i = 0; i < m; i++) out[i] = (out_t)tmp[i];
+    return LZ77SSS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+#pragma GCC visibility push(default)
+
+void lz77sss_sink_emit(void* ctx, uint64_t src, uint64_t len) {
+    auto* s = static_cast<lz77sss_factor_sink*>(ctx);
+    if (s->count < s->cap) {
+        s->src[s->count] = src;
+        s->len[s->count] = len;
+    }
+    s->count++;
+}
+
+const char* lz77sss_last_error(void) { return g_last_error.c_str(); }
+const char* lz77sss_version(void) { return "lz77sss_b200 0.1 (sm_100a)"; }
+
+int lz77sss_device_count(void) {
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return c;
+}
+
+int lz77sss_create(const lz77sss_config* cfg, lz77sss_handle** out) {
+    if (!cfg || !out) return fail(LZ77SSS_E_ARG, "null argument");
+    if (cfg->struct_size != sizeof(lz77sss_config)) return fail(LZ77SSS_E_ARG, "lz77sss_config.struct_size mismatch");
+    if (!valid_tau(cfg->tau)) return fail(LZ77SSS_E_ARG, "tau must be a power of two in [4, 4096]");
+    if (cfg->pos_bits != 0 && cfg->pos_bits != 32 && cfg->pos_bits != 64) return fail(LZ77SSS_E_ARG, "pos_bits must be 0, 32 or 64");
+    for (int x = 0; x < 5; x++)
+        if (cfg->gap_bases[x] < 257 || cfg->gap_bases[x] >= (1ull << 20))
+            return fail(LZ77SSS_E_ARG, "gap_bases must lie in [257, 2^20-1] (rolling_hash.hpp:31-36)");
+    return guarded([&]() {
+        int ndev = 0;
+        CUDA_CHECK(cudaGetDeviceCount(&ndev));
+        if (cfg->device < 0 || cfg->device >= ndev) return fail(LZ77SSS_E_CUDA, "no such CUDA device (there is no CPU fallback)");
+        CUDA_CHECK(cudaSetDevice(cfg->device));
+        auto h = std::make_unique<lz77sss_handle>();
+        h->cfg = *cfg;
+        if (h->cfg.num_threads == 0) h->cfg.num_threads = 1;
+        if (h->cfg.sss_base == 0) h->cfg.sss_base = 0x9E3779B1u;
+        if (h->cfg.sss_qmax == 0xFFFFFFFFu) h->cfg.sss_qmax = 32;
+        if ((h->cfg.sss_base & 1) == 0) return fail(LZ77SSS_E_ARG, "sss_base must be odd");
+        std::memset(&h->stats, 0, sizeof h->stats);
+        CUDA_CHECK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+        *out = h.release();
+        return LZ77SSS_OK;
+    });
+}
+
+void lz77sss_destroy(lz77sss_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    for (auto* p : h->user_texts) cudaFree(p - FRONT_PAD);
+    if (h->st) cudaStreamDestroy(h->st);
+    delete h;
+}
+
+int lz77sss_factorize_approximate(lz77sss_handle* h, const uint8_t* text, uint64_t n, lz77sss_emit_fn emit, void* ctx) {
+    if (!h || !text) return fail(LZ77SSS_E_ARG, "null argument");
+    if (n == 0) return fail(LZ77SSS_E_ARG, "empty input");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        lz77sss_config saved = h->cfg;
+        if (h->cfg.pos_bits == 0) h->cfg.pos_bits = n <= 0xFFFFFFFFull ? 32 : 64;
+        auto t0 = clk::now();
+        uint8_t* d = alloc_text(h->text_buf, n, h->st);
+        CUDA_CHECK(cudaMemcpyAsync(d, text, n, cudaMemcpyHostToDevice, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        uint64_t t_h2d = ns_since(t0);
+        int rc = factorize_dispatch(h, d, text, n, emit, ctx);
+        h->stats.t_h2d_ns = t_h2d;
+        h->stats.t_total_ns += t_h2d;
+        h->cfg.pos_bits = saved.pos_bits == 0 ? 0 : h->cfg.pos_bits;
+        return rc;
+    });
+}
+
+int lz77sss_device_text_alloc(lz77sss_handle* h, uint64_t n, uint8_t** d_text) {
+    if (!h || !d_text) return fail(LZ77SSS_E_ARG, "null argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        uint8_t* p = nullptr;
+        CUDA_CHECK(cudaMalloc(&p, FRONT_PAD + n + TEXT_PAD));
+        CUDA_CHECK(cudaMemsetAsync(p, 0, FRONT_PAD, h->st));
+        CUDA_CHECK(cudaMemsetAsync(p + FRONT_PAD + n, 0, TEXT_PAD, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        h->user_texts.push_back(p + FRONT_PAD);
+        *d_text = p + FRONT_PAD;
+        return LZ77SSS_OK;
+    });
+}
+
+int lz77sss_device_text_upload(lz77sss_handle* h, uint8_t* d_text, const uint8_t* host_text, uint64_t n) {
+    if (!h || !d_text || !host_text) return fail(LZ77SSS_E_ARG, "null argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        CUDA_CHECK(cudaMemcpyAsync(d_text, host_text, n, cudaMemcpyHostToDevice, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        return LZ77SSS_OK;
+    });
+}
+
+int lz77sss_device_text_free(lz77sss_handle* h, uint8_t* d_text) {
+    if (!h || !d_text) return fail(LZ77SSS_E_ARG, "null argument");
+    auto it = std::find(h->user_texts.begin(), h->user_texts.end(), d_text);
+    if (it == h->user_texts.end()) return fail(LZ77SSS_E_ARG, "not a buffer of this handle");
+    h->user_texts.erase(it);
+    cudaSetDevice(h->cfg.device);
+    cudaFree(d_text - FRONT_PAD);
+    return LZ77SSS_OK;
+}
+
+int lz77sss_factorize_approximate_device(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n,
+                                         lz77sss_emit_fn emit, void* ctx) {
+    if (!h || !d_text) return fail(LZ77SSS_E_ARG, "null argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        lz77sss_config saved = h->cfg;
+        if (h->cfg.pos_bits == 0) h->cfg.pos_bits = n <= 0xFFFFFFFFull ? 32 : 64;
+        int rc = factorize_dispatch(h, d_text, host_text, n, emit, ctx);
+        h->cfg.pos_bits = saved.pos_bits == 0 ? 0 : h->cfg.pos_bits;
+        return rc;
+    });
+}
+
+int lz77sss_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, uint64_t z, uint8_t* out, uint64_t n) {
+    if (!h || !src || !len || (!out && n)) return fail(LZ77SSS_E_ARG, "null argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        if (n == 0) return LZ77SSS_OK;
+        if (z == 0) return fail(LZ77SSS_E_ARG, "no factors");
+        dbuf<uint64_t> d_src, d_len;
+        dbuf<uint8_t> d_out;
+        d_src.reserve(z); d_len.reserve(z); d_out.reserve(n);
+        CUDA_CHECK(cudaMemcpyAsync(d_src.get(), src, z * 8, cudaMemcpyHostToDevice, h->st));
+        CUDA_CHECK(cudaMemcpyAsync(d_len.get(), len, z * 8, cudaMemcpyHostToDevice, h->st));
+        int rounds = 0;
+        int rc = decode_factors(d_src, d_len, z, d_out, n, h->st, &rounds);
+        if (rc == -3) return fail(LZ77SSS_E_UNSUPPORTED, "decode: n >= 2^32 not built yet");
+        if (rc) return fail(LZ77SSS_E_ARG, "decode: malformed factor stream (lengths do not add up to n or a source is not earlier text)");
+        CUDA_CHECK(cudaMemcpyAsync(out, d_out.get(), n, cudaMemcpyDeviceToHost, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        return LZ77SSS_OK;
+    });
+}
+
+int lz77sss_build_sss(lz77sss_handle* h, const uint8_t* text, uint64_t n, uint64_t* S_out, uint64_t cap, uint64_t* count_out,
+                      uint64_t* num_q_out) {
+    if (!h || (!text && n)) return fail(LZ77SSS_E_ARG, "null argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        uint8_t* d = alloc_text(h->text_buf, n, h->st);
+        if (n) CUDA_CHECK(cudaMemcpyAsync(d, text, n, cudaMemcpyHostToDevice, h->st));
+        auto& P = h->p64;
+        uint64_t s_cap = n + 16;
+        P.S.reserve(s_cap);
+        uint64_t size_s = 0, numq = 0;
+        sss_build(d, n, h->cfg.tau, h->cfg.sss_base, h->cfg.sss_qmax, P.S.get(), 8, s_cap, P.sss, h->st, &size_s, &numq);
+        if (count_out) *count_out = size_s;
+        if (num_q_out) *num_q_out = numq;
+        return copy_out<uint64_t, uint64_t>(P.S.get(), size_s, S_out, cap, nullptr, h->st);
+    });
+}
+
+int lz77sss_time_sss_kernel(lz77sss_handle* h, const uint8_t* d_text, uint64_t n, int iters, double* ms_out,
+                            uint64_t* count_out) {
+    if (!h || !d_text || iters <= 0) return fail(LZ77SSS_E_ARG, "bad argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        const bool narrow = n < 0xFFFF0000ull;
+        uint64_t s_cap = std::min<uint64_t>(n, 8 * (n / h->cfg.tau) + 65536);
+        if (h->cfg.tau < 16) s_cap = n;
+        uint64_t size_s = 0, numq = 0;
+        cudaEvent_t e0, e1;
+        CUDA_CHECK(cudaEventCreate(&e0));
+        CUDA_CHECK(cudaEventCreate(&e1));
+        double total = 0;
+        for (int it = -1; it < iters; it++) {     // one untimed warm-up
+            CUDA_CHECK(cudaEventRecord(e0, h->st));
+            if (narrow) {
+                h->p32.S.reserve(s_cap);
+                sss_build(d_text, n, h->cfg.tau, h->cfg.sss_base, h->cfg.sss_qmax, h->p32.S.get(), 4, s_cap, h->p32.sss, h->st, &size_s, &numq);
+            } else {
+                h->p64.S.reserve(s_cap);
+                sss_build(d_text, n, h->cfg.tau, h->cfg.sss_base, h->cfg.sss_qmax, h->p64.S.get(), 8, s_cap, h->p64.sss, h->st, &size_s, &numq);
+            }
+            CUDA_CHECK(cudaEventRecord(e1, h->st));
+            CUDA_CHECK(cudaEventSynchronize(e1));
+            float ms = 0;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+            if (it >= 0) total += ms;
+        }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        if (ms_out) *ms_out = total / iters;
+        if (count_out) *count_out = size_s;
+        return LZ77SSS_OK;
+    });
+}
+
+int lz77sss_get_stats(lz77sss_handle* h, lz77sss_stats* out) {
+    if (!h || !out) return fail(LZ77SSS_E_ARG, "null argument");
+    *out = h->stats;
+    return LZ77SSS_OK;
+}
+
+#define NEED_RESULT() \
+    if (!h) return fail(LZ77SSS_E_ARG, "null handle"); \
+    if (!h->have_result) return fail(LZ77SSS_E_STATE, "no factorization on this handle yet")
+
+int lz77sss_get_sss(lz77sss_handle* h, uint64_t* out, uint64_t cap, uint64_t* count) {
+    NEED_RESULT();
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        if (h->pos_bytes == 4) return copy_out<uint32_t, uint64_t>(h->p32.S.get(), h->p32.s, out, cap, count, h->st);
+        return copy_out<uint64_t, uint64_t>(h->p64.S.get(), h->p64.s, out, cap, count, h->st);
+    });
+}
+
+int lz77sss_get_sa_s(lz77sss_handle* h, uint32_t* out, uint64_t cap, uint64_t* count) {
+    NEED_RESULT();
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        if (h->pos_bytes == 4) return copy_out<uint32_t, uint32_t>(h->p32.suf.SA.get(), h->p32.s, out, cap, count, h->st);
+        return copy_out<uint32_t, uint32_t>(h->p64.suf.SA.get(), h->p64.s, out, cap, count, h->st);
+    });
+}
+
+int lz77sss_get_lcp_s(lz77sss_handle* h, uint64_t* out, uint64_t cap, uint64_t* count) {
+    NEED_RESULT();
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        if (h->pos_bytes == 4) return copy_out<uint32_t, uint64_t>(h->p32.suf.LCP.get(), h->p32.s, out, cap, count, h->st);
+        return copy_out<uint64_t, uint64_t>(h->p64.suf.LCP.get(), h->p64.s, out, cap, count, h->st);
+    });
+}
+
+int lz77sss_get_lpf(lz77sss_handle* h, uint64_t* beg, uint64_t* end, uint64_t* src, uint32_t* blk_out, uint64_t cap,
+                    uint64_t* count) {
+    NEED_RESULT();
+    uint64_t k = 0;
+    for (uint32_t b = 0; b < h->LPF.size(); b++)
+        for (auto& ph : h->LPF[b]) {
+            if (k < cap) {
+                if (beg) beg[k] = ph.beg;
+                if (end) end[k] = ph.end;
+                if (src) src[k] = ph.src;
+                if (blk_out) blk_out[k] = b;
+            }
+            k++;
+        }
+    if (count) *count = k;
+    return LZ77SSS_OK;
+}
+
+int lz77sss_lce_batch(lz77sss_handle* h, const uint64_t* qi, const uint64_t* qj, uint64_t nq, uint64_t* out) {
+    NEED_RESULT();
+    if (!qi || !qj || !out) return fail(LZ77SSS_E_ARG, "null argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        if (nq == 0) return LZ77SSS_OK;
+        for (uint64_t k = 0; k < nq; k++)
+            if (qi[k] >= h->n || qj[k] >= h->n) return fail(LZ77SSS_E_ARG, "lce query out of range");
+        dbuf<uint64_t> d_i, d_j, d_o;
+        d_i.reserve(nq); d_j.reserve(nq); d_o.reserve(nq);
+        CUDA_CHECK(cudaMemcpyAsync(d_i.get(), qi, nq * 8, cudaMemcpyHostToDevice, h->st));
+        CUDA_CHECK(cudaMemcpyAsync(d_j.get(), qj, nq * 8, cudaMemcpyHostToDevice, h->st));
+        if (h->pos_bytes == 4)
+            lce_r_batch<uint32_t>(h->d_text, h->n, h->cfg.tau, h->p32.S.get(), h->p32.s, h->p32.suf, h->p32.lce, d_i, d_j, nq, d_o, h->st);
+        else
+            lce_r_batch<uint64_t>(h->d_text, h->n, h->cfg.tau, h->p64.S.get(), h->p64.s, h->p64.suf, h->p64.lce, d_i, d_j, nq, d_o, h->st);
+        CUDA_CHECK(cudaMemcpyAsync(out, d_o.get(), nq * 8, cudaMemcpyDeviceToHost, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        return LZ77SSS_OK;
+    });
+}
+
+#pragma GCC visibility pop
+}  // extern "C"

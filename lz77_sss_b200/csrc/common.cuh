@@ -1,0 +1,87 @@
+// Shared declarations of the lz77-sss B200 device library (sm_100a only).
+// Everything under csrc/ is built into liblz77sss_b200.so; the only exported symbols are
+// the extern "C" entry points declared in include/lz77sss_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <stdexcept>
+#include <string>
+
+namespace lz77sss {
+
+struct cuda_error : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+inline void cuda_check(cudaError_t e, const char* what, const char* file, int line) {
+    if (e != cudaSuccess) {
+        char buf[512];
+        snprintf(buf, sizeof buf, "%s failed at %s:%d: %s", what, file, line, cudaGetErrorString(e));
+        throw cuda_error(buf);
+    }
+}
+#define CUDA_CHECK(x) ::lz77sss::cuda_check((x), #x, __FILE__, __LINE__)
+// every kernel launch of the library goes through KERNEL_CHECK, which also counts it (bench.py's gpu_launches)
+extern unsigned long long g_kernel_launches;
+#define KERNEL_CHECK()                                                                    \
+    do {                                                                                  \
+        ::lz77sss::g_kernel_launches++;                                                   \
+        ::lz77sss::cuda_check(cudaGetLastError(), "kernel launch", __FILE__, __LINE__);   \
+    } while (0)
+
+// Owning device buffer (cudaMallocAsync on the handle's stream would also do; plain cudaMalloc keeps
+// the allocation pattern visible and the buffers are reused across calls of one handle).
+template <typename T>
+struct dbuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    dbuf() = default;
+    dbuf(const dbuf&) = delete;
+    dbuf& operator=(const dbuf&) = delete;
+    dbuf(dbuf&& o) noexcept : p(o.p), cap(o.cap) { o.p = nullptr; o.cap = 0; }
+    dbuf& operator=(dbuf&& o) noexcept {
+        if (this != &o) { release(); p = o.p; cap = o.cap; o.p = nullptr; o.cap = 0; }
+        return *this;
+    }
+    ~dbuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    // grow-only; contents are NOT preserved
+    void reserve(size_t n) {
+        if (n <= cap) return;
+        release();
+        size_t want = n + n / 8 + 64;
+        CUDA_CHECK(cudaMalloc(&p, want * sizeof(T)));
+        cap = want;
+    }
+    T* get() const { return p; }
+    operator T*() const { return p; }
+};
+
+static inline unsigned ceil_div_u(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }
+
+// ---- utility device primitives implemented in util.cu ------------------------------------------
+// exclusive prefix sum (uint32 values, uint32 sums) in place; n up to 2^31. tmp is scratch.
+struct scan_scratch {
+    dbuf<uint32_t> lvl1, lvl2;
+};
+void exclusive_scan_u32(uint32_t* d, uint64_t n, scan_scratch& s, cudaStream_t st, uint32_t* d_total = nullptr);
+
+// stable LSD radix sort of (key64, val32) pairs on bits [bit_lo, bit_hi) of the key.
+// Result ends in (keys, vals) (ping-pong handled inside; kalt/valt are scratch of the same size).
+struct sort_scratch {
+    dbuf<uint32_t> hist;
+    scan_scratch scan;
+};
+void radix_sort_pairs(uint64_t*& keys, uint64_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
+                      int bit_hi, sort_scratch& s, cudaStream_t st);
+
+void fill_u32(uint32_t* d, uint64_t n, uint32_t v, cudaStream_t st);
+void iota_u32(uint32_t* d, uint64_t n, cudaStream_t st);
+
+}  // namespace lz77sss

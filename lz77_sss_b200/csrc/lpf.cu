@@ -1,0 +1,314 @@
+// K4 + LPF candidates: range-minimum / nearest-smaller structures over (SA_S, LCP_S), the two
+// longest-previous-factor candidates of every synchronizing position, batched exact LCE queries.
+//
+// Replaces build_PSV_NSV_S (/root/reference/include/lz77_sss/algorithms/approximate/lpf_lnf/nxv_pxv.cpp:33-92,
+// a single-threaded stack scan there), the two LCE_R and two LCE_L probes per position of
+// build_LPF_opt (lpf_opt.cpp:68-139) and lce_sss::lce_lr (patched lce_sss.hpp:123-177).
+// For two synchronizing positions the exact LCE is the range minimum of LCP_S between their ranks
+// (lce_classic_for_sss.hpp:153-155), so no text is re-read for the LCE_R probes.
+#include "common.cuh"
+#include "device_utils.cuh"
+#include "stages.cuh"
+
+namespace lz77sss {
+namespace {
+
+constexpr int BLK = 32;
+
+template <typename val_t>
+__global__ void blkmin_kernel(const val_t* __restrict__ v, uint64_t s, val_t* __restrict__ tab, uint32_t nblk) {
+    const uint64_t b = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned lane = threadIdx.x & 31;
+    if (b >= nblk) return;
+    uint64_t i = b * BLK + lane;
+    val_t x = i < s ? v[i] : (val_t)~(val_t)0;
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        val_t y = __shfl_xor_sync(0xffffffffu, x, d);
+        x = y < x ? y : x;
+    }
+    if (lane == 0) tab[b] = x;
+}
+
+template <typename val_t>
+__global__ void sparse_level_kernel(val_t* __restrict__ tab, uint32_t nblk, int l) {
+    uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t half = 1ull << (l - 1);
+    if (b + (1ull << l) > nblk) return;
+    val_t x = tab[(uint64_t)(l - 1) * nblk + b], y = tab[(uint64_t)(l - 1) * nblk + b + half];
+    tab[(uint64_t)l * nblk + b] = y < x ? y : x;
+}
+
+// min of the block minima over blocks [lo, hi] (inclusive, lo <= hi)
+template <typename val_t>
+__device__ __forceinline__ val_t blk_range_min(const val_t* __restrict__ tab, uint32_t nblk, uint64_t lo, uint64_t hi) {
+    const int l = 63 - __clzll((long long)(hi - lo + 1));
+    val_t x = tab[(uint64_t)l * nblk + lo], y = tab[(uint64_t)l * nblk + hi + 1 - (1ull << l)];
+    return y < x ? y : x;
+}
+
+// min v[lo..hi] (inclusive, lo <= hi)
+template <typename val_t>
+__device__ __forceinline__ val_t range_min(const val_t* __restrict__ v, const val_t* __restrict__ tab, uint32_t nblk,
+                                           uint64_t lo, uint64_t hi) {
+    const uint64_t bl = lo / BLK, bh = hi / BLK;
+    val_t m = v[lo];
+    if (bl == bh) {
+        for (uint64_t i = lo + 1; i <= hi; i++) m = v[i] < m ? v[i] : m;
+        return m;
+    }
+    for (uint64_t i = lo + 1; i < (bl + 1) * BLK; i++) m = v[i] < m ? v[i] : m;
+    for (uint64_t i = bh * BLK; i <= hi; i++) m = v[i] < m ? v[i] : m;
+    if (bl + 1 < bh) {
+        val_t x = blk_range_min(tab, nblk, bl + 1, bh - 1);
+        m = x < m ? x : m;
+    }
+    return m;
+}
+
+// largest r' < r with SA[r'] < v, or NONE32
+__device__ __forceinline__ uint32_t prev_smaller(const uint32_t* __restrict__ SA, const uint32_t* __restrict__ tab,
+                                                 uint32_t nblk, uint64_t r, uint32_t v) {
+    const uint64_t b = r / BLK;
+    for (uint64_t j = r; j > b * BLK;) {
+        j--;
+        if (SA[j] < v) return (uint32_t)j;
+    }
+    if (b == 0) return NONE32;
+    uint64_t e = b, w = 1, lo;
+    while (true) {
+        lo = e >= w ? e - w : 0;
+        if (blk_range_min(tab, nblk, lo, e - 1) < v) break;
+        if (lo == 0) return NONE32;
+        w *= 2;
+    }
+    uint64_t hi = e - 1;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi + 1) / 2;
+        if (blk_range_min(tab, nblk, mid, hi) < v) lo = mid;
+        else hi = mid - 1;
+    }
+    for (uint64_t j = (lo + 1) * BLK; j > lo * BLK;) {
+        j--;
+        if (SA[j] < v) return (uint32_t)j;
+    }
+    return NONE32;  // unreachable
+}
+
+// smallest r' > r with SA[r'] < v, or NONE32
+__device__ __forceinline__ uint32_t next_smaller(const uint32_t* __restrict__ SA, const uint32_t* __restrict__ tab,
+                                                 uint32_t nblk, uint64_t s, uint64_t r, uint32_t v) {
+    const uint64_t b = r / BLK;
+    const uint64_t bend = min(s, (b + 1) * BLK);
+    for (uint64_t j = r + 1; j < bend; j++)
+        if (SA[j] < v) return (uint32_t)j;
+    if (b + 1 >= nblk) return NONE32;
+    uint64_t e = b + 1, w = 1, hi;   // search blocks [e, ...]
+    while (true) {
+        hi = e + w - 1 < nblk ? e + w - 1 : nblk - 1;
+        if (blk_range_min(tab, nblk, e, hi) < v) break;
+        if (hi == nblk - 1) return NONE32;
+        w *= 2;
+    }
+    uint64_t lo = e;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi) / 2;
+        if (blk_range_min(tab, nblk, lo, mid) < v) hi = mid;
+        else lo = mid + 1;
+    }
+    const uint64_t be = min(s, (lo + 1) * BLK);
+    for (uint64_t j = lo * BLK; j < be; j++)
+        if (SA[j] < v) return (uint32_t)j;
+    return NONE32;  // unreachable
+}
+
+// number of equal characters going left from T[i] and T[j] (i < j), at most cap (cap <= i + 1)
+__device__ __forceinline__ uint64_t thread_lce_left(const uint8_t* __restrict__ T, uint64_t i, uint64_t j, uint64_t cap) {
+    uint64_t k = 0;
+    while (k < cap) {
+        // the front pad of the device text makes the 8 bytes ending at i-k readable
+        uint64_t a = load_u64_unaligned(T + i - k - 7), b = load_u64_unaligned(T + j - k - 7);
+        uint64_t diff = a ^ b;
+        if (diff) {
+            k += __clzll((long long)diff) / 8;
+            return k < cap ? k : cap;
+        }
+        k += 8;
+    }
+    return cap;
+}
+
+template <typename pos_t>
+__global__ void lpf_candidates_kernel(const uint8_t* __restrict__ T, uint64_t n, const pos_t* __restrict__ S,
+                                      uint64_t s, uint64_t blk_len, uint32_t p_ref, const uint32_t* __restrict__ SA,
+                                      const uint32_t* __restrict__ ISA, const pos_t* __restrict__ LCP,
+                                      const uint32_t* __restrict__ sa_tab, const pos_t* __restrict__ lcp_tab,
+                                      uint32_t nblk, uint32_t* __restrict__ psv_idx, uint32_t* __restrict__ nsv_idx,
+                                      pos_t* __restrict__ psv_lce, pos_t* __restrict__ nsv_lce,
+                                      pos_t* __restrict__ psv_lcel, pos_t* __restrict__ nsv_lcel) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s) return;
+    const uint64_t r = ISA[i];
+    const uint64_t pos = S[i];
+    const uint32_t pr = prev_smaller(SA, sa_tab, nblk, r, (uint32_t)i);
+    const uint32_t nr = next_smaller(SA, sa_tab, nblk, s, r, (uint32_t)i);
+    // largest left extension any visit of i can ask for: the covered prefix reaches at
+    // least the previous synchronizing position, or the start of the p_ref block
+    uint64_t k = pos / blk_len;
+    if (k > p_ref - 1) k = p_ref - 1;
+    const uint64_t b = k * blk_len;
+    uint64_t prevpos = b;
+    if (i >= 2 && (uint64_t)S[i - 1] >= b) prevpos = S[i - 1];
+    const uint64_t capmax = pos - prevpos;
+    uint32_t pi = NONE32, ni = NONE32;
+    pos_t pl = 0, nl = 0, pll = 0, nll = 0;
+    if (pr != NONE32) {
+        pi = SA[pr];
+        pl = range_min(LCP, lcp_tab, nblk, (uint64_t)pr + 1, r);
+        const uint64_t src = S[pi];
+        if (src != 0 && pos != 0) pll = (pos_t)thread_lce_left(T, src - 1, pos - 1, min(capmax, src));
+    }
+    if (nr != NONE32) {
+        ni = SA[nr];
+        nl = range_min(LCP, lcp_tab, nblk, r + 1, (uint64_t)nr);
+        const uint64_t src = S[ni];
+        if (src != 0 && pos != 0) nll = (pos_t)thread_lce_left(T, src - 1, pos - 1, min(capmax, src));
+    }
+    psv_idx[i] = pi; nsv_idx[i] = ni;
+    psv_lce[i] = pl; nsv_lce[i] = nl;
+    psv_lcel[i] = pll; nsv_lcel[i] = nll;
+}
+
+template <typename pos_t>
+__global__ void succ_first_kernel(const pos_t* __restrict__ S, uint64_t s, uint32_t shift, uint64_t nb,
+                                  uint32_t* __restrict__ first) {
+    uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb) return;
+    const uint64_t x = b << shift;
+    uint64_t lo = 0, hi = s;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi) / 2;
+        if ((uint64_t)S[mid] < x) lo = mid + 1;
+        else hi = mid;
+    }
+    first[b] = (uint32_t)lo;
+}
+
+// one warp per query; lce_sss::lce / lce_lr (patched lce_sss.hpp:102-177)
+template <typename pos_t>
+__global__ void __launch_bounds__(256) lce_r_kernel(const uint8_t* __restrict__ T, uint64_t n, uint32_t tau,
+                                                    const pos_t* __restrict__ S, uint64_t s,
+                                                    const uint32_t* __restrict__ ISA, const pos_t* __restrict__ LCP,
+                                                    const pos_t* __restrict__ lcp_tab, uint32_t nblk,
+                                                    const uint32_t* __restrict__ first, uint32_t shift, uint64_t nb,
+                                                    const uint64_t* __restrict__ qi, const uint64_t* __restrict__ qj,
+                                                    uint64_t nq, uint64_t* __restrict__ out) {
+    const uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const uint64_t i = qi[q], j = qj[q];
+    uint64_t res;
+    if (i == j) {
+        res = n - i;
+    } else {
+        const uint64_t l = min(i, j), r = max(i, j);
+        const uint64_t lce_max = n - r;
+        const uint64_t local_max = min((uint64_t)3 * tau, lce_max);
+        const uint64_t local = warp_lce(T, l, r, 0, local_max);
+        if (local < local_max || local == lce_max) {
+            res = local;
+        } else {
+            auto succ = [&](uint64_t x) -> uint64_t {
+                uint64_t b = x >> shift;
+                uint64_t idx = b < nb ? first[b] : s;
+                while (idx < s && (uint64_t)S[idx] < x) idx++;
+                return idx;
+            };
+            const uint64_t l_ = succ(l), r_ = succ(r);
+            const uint64_t dl = (uint64_t)S[l_] - l, dr = (uint64_t)S[r_] - r;
+            if (dl != dr) {
+                res = min(dl, dr) + 2 * (uint64_t)tau - 1;
+            } else {
+                uint64_t a = ISA[l_], b = ISA[r_];
+                if (a > b) { uint64_t t = a; a = b; b = t; }
+                res = dl + (uint64_t)range_min(LCP, lcp_tab, nblk, a + 1, b);
+            }
+        }
+    }
+    if (lane == 0) out[q] = res;
+}
+
+}  // namespace
+
+template <typename pos_t>
+void build_lce_structures(const uint8_t* T, uint64_t n, uint32_t tau, const pos_t* S, uint64_t s,
+                          suffix_state<pos_t>& ss, lce_state<pos_t>& ls, cudaStream_t st) {
+    (void)T; (void)n;
+    if (s == 0) { ls.nblk = 0; ls.sp_levels = 0; return; }
+    ls.nblk = ceil_div_u(s, BLK);
+    int levels = 1;
+    while ((1ull << levels) <= ls.nblk) levels++;
+    ls.sp_levels = levels;
+    ls.sa_blkmin.reserve((uint64_t)levels * ls.nblk);
+    ls.lcp_blkmin.reserve((uint64_t)levels * ls.nblk);
+    unsigned g = ceil_div_u((uint64_t)ls.nblk * 32, 256);
+    blkmin_kernel<uint32_t><<<g, 256, 0, st>>>(ss.SA, s, ls.sa_blkmin, ls.nblk);
+    KERNEL_CHECK();
+    blkmin_kernel<pos_t><<<g, 256, 0, st>>>(ss.LCP, s, ls.lcp_blkmin, ls.nblk);
+    KERNEL_CHECK();
+    for (int l = 1; l < levels; l++) {
+        unsigned gl = ceil_div_u(ls.nblk, 256);
+        sparse_level_kernel<uint32_t><<<gl, 256, 0, st>>>(ls.sa_blkmin, ls.nblk, l);
+        KERNEL_CHECK();
+        sparse_level_kernel<pos_t><<<gl, 256, 0, st>>>(ls.lcp_blkmin, ls.nblk, l);
+        KERNEL_CHECK();
+    }
+    // successor index with buckets of tau positions
+    uint32_t shift = 0;
+    while ((2u << shift) <= tau) shift++;
+    ls.succ_shift = shift;
+    ls.succ_nb = ((n + TEXT_PAD) >> shift) + 2;
+    ls.succ_first.reserve(ls.succ_nb);
+    succ_first_kernel<pos_t><<<ceil_div_u(ls.succ_nb, 256), 256, 0, st>>>(S, s, shift, ls.succ_nb, ls.succ_first);
+    KERNEL_CHECK();
+}
+
+template <typename pos_t>
+void lpf_candidates(const uint8_t* T, uint64_t n, uint32_t tau, const pos_t* S, uint64_t s, uint32_t p_ref,
+                    suffix_state<pos_t>& ss, lce_state<pos_t>& ls, cudaStream_t st) {
+    (void)tau;
+    if (s == 0) return;
+    ls.psv_idx.reserve(s); ls.nsv_idx.reserve(s);
+    ls.psv_lce.reserve(s); ls.nsv_lce.reserve(s);
+    ls.psv_lcel.reserve(s); ls.nsv_lcel.reserve(s);
+    uint64_t blk_len = n / p_ref;
+    if (blk_len == 0) blk_len = 1;
+    lpf_candidates_kernel<pos_t><<<ceil_div_u(s, 128), 128, 0, st>>>(
+        T, n, S, s, blk_len, p_ref, ss.SA, ss.ISA, ss.LCP, ls.sa_blkmin, ls.lcp_blkmin, ls.nblk, ls.psv_idx,
+        ls.nsv_idx, ls.psv_lce, ls.nsv_lce, ls.psv_lcel, ls.nsv_lcel);
+    KERNEL_CHECK();
+}
+
+template <typename pos_t>
+void lce_r_batch(const uint8_t* T, uint64_t n, uint32_t tau, const pos_t* S, uint64_t s, suffix_state<pos_t>& ss,
+                 lce_state<pos_t>& ls, const uint64_t* d_qi, const uint64_t* d_qj, uint64_t nq, uint64_t* d_out,
+                 cudaStream_t st) {
+    if (nq == 0) return;
+    lce_r_kernel<pos_t><<<ceil_div_u(nq * 32, 256), 256, 0, st>>>(T, n, tau, S, s, ss.ISA, ss.LCP, ls.lcp_blkmin,
+                                                                  ls.nblk, ls.succ_first, ls.succ_shift, ls.succ_nb,
+                                                                  d_qi, d_qj, nq, d_out);
+    KERNEL_CHECK();
+}
+
+#define INST(pos_t)                                                                                                    \
+    template void build_lce_structures<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t,              \
+                                              suffix_state<pos_t>&, lce_state<pos_t>&, cudaStream_t);                  \
+    template void lpf_candidates<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t, uint32_t,          \
+                                        suffix_state<pos_t>&, lce_state<pos_t>&, cudaStream_t);                        \
+    template void lce_r_batch<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t, suffix_state<pos_t>&, \
+                                     lce_state<pos_t>&, const uint64_t*, const uint64_t*, uint64_t, uint64_t*,         \
+                                     cudaStream_t);
+INST(uint32_t)
+INST(uint64_t)
+
+}  // namespace lz77sss

@@ -1,0 +1,97 @@
+// Stage interfaces of the device pipeline (host-callable wrappers around the kernels).
+#pragma once
+#include <vector>
+#include "common.cuh"
+
+namespace lz77sss {
+
+// The device copy of the text is zero-filled for TEXT_PAD bytes after T[n-1] (the reference's
+// callers pad with 4*512 zero bytes, cli/lz77_sss_3_aprx.cpp:66; we never trust the host tail).
+constexpr uint64_t TEXT_PAD = 65536;
+constexpr uint32_t NONE32 = 0xFFFFFFFFu;
+
+// ---- sss.cu / sss_small.cu --------------------------------------------------------------------
+struct sss_scratch {
+    dbuf<unsigned long long> status;
+    dbuf<unsigned int> ticket;
+    dbuf<unsigned long long> counters;
+    dbuf<uint32_t> blk;
+    scan_scratch scan;
+};
+uint32_t sss_period_bound(uint32_t tau, uint32_t qmax);
+uint32_t sss_anchor_spacing(uint32_t tau, uint32_t P);
+void sss_build(const uint8_t* d_text, uint64_t n, uint32_t tau, uint32_t base, uint32_t qmax, void* d_S, int pos_bytes,
+               uint64_t s_cap, sss_scratch& sc, cudaStream_t st, uint64_t* h_size, uint64_t* h_numq);
+void sss_build_small_tau(const uint8_t* d_text, uint64_t n, uint32_t tau, uint32_t base, uint32_t qmax, void* d_S,
+                         int pos_bytes, uint64_t s_cap, sss_scratch& sc, cudaStream_t st);
+
+// ---- suffix.cu: order of the suffixes starting at synchronizing positions ------------------------
+template <typename pos_t>
+struct suffix_state {
+    // outputs
+    dbuf<uint32_t> SA, ISA;          // |S| each
+    dbuf<pos_t> LCP;                 // LCP[r] = lce(S[SA[r-1]], S[SA[r]]) in text characters, LCP[0] = 0
+    std::vector<dbuf<uint32_t>> rank_lvl;   // rank_lvl[l][i] = rank of sync suffix i by its first 2^l reduced symbols
+    int levels = 0;
+    // scratch
+    dbuf<uint64_t> k0, k1, enc;
+    dbuf<uint32_t> v0, v1, flags, gid, gstart, crank;
+    dbuf<uint32_t> counter;
+    sort_scratch sort;
+    scan_scratch scan;
+    // statistics
+    int ctx_levels = 0, doubling_rounds = 0;
+    uint64_t num_run_syms = 0;
+};
+template <typename pos_t>
+void suffix_sort_sync(const uint8_t* d_text, uint64_t n, uint32_t tau, uint32_t qmax, const pos_t* d_S, uint64_t s,
+                      suffix_state<pos_t>& ss, cudaStream_t st);
+
+// ---- lpf.cu: range-min / nearest-smaller structures, LPF candidates, batched LCE -------------------
+template <typename pos_t>
+struct lce_state {
+    dbuf<uint32_t> sa_blkmin;              // sparse table over block minima of SA (ANSV)
+    dbuf<pos_t> lcp_blkmin;                // sparse table over block minima of LCP (RMQ)
+    uint32_t nblk = 0;
+    int sp_levels = 0;
+    dbuf<uint32_t> succ_first;             // successor index: first[b] = smallest idx with S[idx] >> shift >= b
+    uint32_t succ_shift = 0;
+    uint64_t succ_nb = 0;
+    // per synchronizing position: the two LPF candidates
+    dbuf<uint32_t> psv_idx, nsv_idx;       // sync index of the source or NONE32
+    dbuf<pos_t> psv_lce, nsv_lce, psv_lcel, nsv_lcel;
+    scan_scratch scan;
+};
+template <typename pos_t>
+void build_lce_structures(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s,
+                          suffix_state<pos_t>& ss, lce_state<pos_t>& ls, cudaStream_t st);
+// candidates for build_LPF_opt (lpf_opt.cpp:68-139); blk_b[i] = start of the p_ref block of S[i]
+template <typename pos_t>
+void lpf_candidates(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, uint32_t p_ref,
+                    suffix_state<pos_t>& ss, lce_state<pos_t>& ls, cudaStream_t st);
+// batched exact LCE_R(i,j) (lce_sss.hpp:102-177) for arbitrary text positions
+template <typename pos_t>
+void lce_r_batch(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s,
+                 suffix_state<pos_t>& ss, lce_state<pos_t>& ls, const uint64_t* d_qi, const uint64_t* d_qj,
+                 uint64_t nq, uint64_t* d_out, cudaStream_t st);
+
+// ---- gap_hash.cu: bucket ids of the 5 rolling hashes (mod 2^107-1) for ranges of text positions ------
+struct gap_hash_params {
+    uint64_t patt_len[5];
+    uint64_t base[5];
+    uint64_t mask;       // table entries - 1
+};
+// ranges [beg[k], end[k]) of text positions; out[5 * (off[k] + (pos - beg[k])) + x] = fp_x(pos) & mask
+// for every window that fits (pos + patt_len[x] <= n), NONE32 otherwise.  The reference only hashes at
+// pos + patt_len[x] < n (rolling_hash_index_107.hpp:93,112,123) and keeps the stale fingerprint of the
+// window at n - patt_len[x] afterwards; the host emission applies that rule.
+void gap_bucket_ids(const uint8_t* d_text, uint64_t n, const gap_hash_params& gp, const uint64_t* d_beg,
+                    const uint64_t* d_end, const uint64_t* d_off, uint64_t nranges, uint64_t total, uint32_t* d_out,
+                    cudaStream_t st);
+
+// ---- decode.cu ------------------------------------------------------------------------------------
+// parallel LZ77 decode: factors (src,len) with len == 0 meaning literal src; returns 0 or an error code
+int decode_factors(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uint8_t* d_out, uint64_t n,
+                   cudaStream_t st, int* rounds);
+
+}  // namespace lz77sss
