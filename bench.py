@@ -1,0 +1,270 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the lz77-sss 3-approximation hot path on B200.
+
+Workload (BASELINE.json configs[1]): lz77-sss-3-aprx (factorize_approximate<greedy, lpf_opt>) on a 1 GiB synthetic
+chr19-like DNA text (16 MiB i.i.d. {A,C,G,T} chromosome x 64 copies with 0.1 % point mutations, seed 2),
+num_threads = 1 as in lz77-sss-bench-tau, tau = 512 by default (--tau for the other points of the sweep).
+A "step" = one complete factorization of that text.  Metric: input MiB/s factorized (higher is better).
+
+  value : text already resident in HBM (lz77sss_factorize_approximate_device), timed region = whole call
+  e2e   : the public call on a HOST buffer (lz77sss_factorize_approximate): H2D of the text and D2H of the
+          device results inside the timed region; factors delivered through the C callback into host arrays
+  roofline : the fused fingerprint+SSS-selection kernel (K1+K2), algorithmic bytes n + 4|S| over its
+             CUDA-event time on the library's stream, against the measured HBM copy peak
+  cpu_baseline : the reference's own CPU code (oracle/_ref) on a bounded prefix of the same text
+
+N > 1 (torchrun): every rank factorizes its own text of the same shape (seed 2+rank); no data-path collective
+exists yet for a single sharded text, so this is "independent texts per GPU" weak scaling.
+`--impl reference` times the reference's CPU implementation (rank 0 only).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+MIB = 1 << 20
+METRIC = "input MiB/s factorized (3-aprx)"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--tau", type=int, default=512)
+    ap.add_argument("--size-mib", type=int, default=1024)
+    ap.add_argument("--workload", default="dna", choices=["dna", "rep"])
+    ap.add_argument("--cpu-sample-mib", type=int, default=64)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def make_text(args, rank):
+    from lz77_sss_b200 import synth
+    n = args.size_mib * MIB
+    if args.workload == "dna":
+        return synth.dna_collection(n, seed=2 + rank, chrom_len=min(16 * MIB, max(n // 64, 1 << 16)))
+    return synth.random_repetitive(n, seed=1 + rank)
+
+
+def workload_name(args):
+    if args.workload == "dna":
+        return (f"C2: lz77-sss-3-aprx on {args.size_mib} MiB synthetic chr19-like DNA (64 mutated copies of one "
+                f"chromosome), tau={args.tau}, num_threads=1")
+    return f"C1: lz77-sss-3-aprx on {args.size_mib} MiB random_repetitive_string, tau={args.tau}, num_threads=1"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for k, nm in enumerate(names):
+                if len(r) > 4 + k and r[4 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_run(text, tau, threads):
+    """The reference's own factorize_approximate<greedy, lpf_opt, tau> (oracle/_ref), timed as lz77_sss.hpp:314-353."""
+    import oracle_lib as O
+    if O.ref_available(tau):
+        _, _, _, sec = O.ref_factorize(text, tau, p=threads)
+        return sec, "reference"
+    # the reference library was not prebuilt for this tau: time the oracle's sequential restatement instead
+    from lz77_sss_b200 import capi
+    t0 = time.perf_counter()
+    O.factorize(text, tau, capi.DEFAULT_GAP_BASES, p_ref=1)
+    return time.perf_counter() - t0, "port"
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    text = make_text(args, 0)
+    sample = text[: args.cpu_sample_mib * MIB]
+    cores = os.cpu_count() or 1
+    times = []
+    kind = "reference"
+    for it in range(args.warmup + args.steps):
+        sec, kind = cpu_reference_run(sample, args.tau, cores if kind == "reference" else 1)
+        if it >= args.warmup:
+            times.append(sec)
+    ms = 1e3 * sum(times) / len(times)
+    val = (sample.size / MIB) / (ms / 1e3)
+    used = cores if kind == "reference" else 1
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "MiB/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": workload_name(args), "sample": f"first {sample.size // MIB} MiB of the text per step"},
+        "cpu_baseline": {"value": val, "unit": "MiB/s", "cores": used, "kind": kind,
+                         "sample": f"first {sample.size // MIB} MiB of the workload text, num_threads={used}"},
+        "e2e": {"value": val, "unit": "MiB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    import torch
+    import torch.distributed as dist
+    from lz77_sss_b200 import capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    text = make_text(args, rank)
+    n = text.size
+    pinned = torch.empty(n, dtype=torch.uint8).pin_memory()          # plumbing: pinned host memory for the e2e leg
+    pinned.numpy()[:] = text
+    host_ptr = pinned.data_ptr()
+    F = capi.Factorizer(tau=args.tau, num_threads=1, gap_bases=capi.DEFAULT_GAP_BASES, device=local)
+    cap = n // 8 + 1024
+    src = np.empty(cap, dtype=np.uint64)
+    ln = np.empty(cap, dtype=np.uint64)
+    sink = capi.Sink(src.ctypes.data_as(C.POINTER(C.c_uint64)), ln.ctypes.data_as(C.POINTER(C.c_uint64)), cap, 0)
+    d_text = F.device_text(text)
+
+    launches = {"n": 0}
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        launches["n"] = 0
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)       # CUDA events; the host part of a step lies between them
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms / steps
+
+    def step_resident():
+        z = F.factorize_device_into(d_text, host_ptr, n, sink)
+        launches["n"] += F.stats()["kernel_launches"]
+        return z
+
+    def step_e2e():
+        return F.factorize_into(host_ptr, n, sink)
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_res = timed(step_resident, args.steps, args.warmup)
+    launches_timed = launches["n"]
+    st_res = F.stats()
+    z = st_res["num_factors"]
+    ms_e2e = timed(step_e2e, args.steps, max(1, args.warmup - 2))
+    st_e2e = F.stats()
+    clocks = sampler.stop()
+
+    # the dominant streaming kernel (K1+K2), CUDA events on the library's own stream
+    k_ms, s_size = F.time_sss_kernel(d_text, n, iters=10)
+
+    value = world * (n / MIB) / (ms_res / 1e3)
+    e2e = world * (n / MIB) / (ms_e2e / 1e3)
+    out = None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        alg_bytes = n + 4 * s_size
+        achieved = alg_bytes / (k_ms / 1e3) / 1e9
+        out = {
+            "metric": METRIC, "value": value, "unit": "MiB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_res, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic",
+            "config": {"workload": workload_name(args), "n_bytes": int(n), "tau": args.tau, "num_threads": 1,
+                       "parallelism": "single GPU" if world == 1 else f"{world} independent texts, one per GPU (no sharded single-text path yet)",
+                       "l2": "input (1 GiB) is larger than L2 (126 MB); no explicit flush", "factors": int(z),
+                       "size_sss": int(st_res["size_sss"])},
+            "e2e": {"value": e2e, "unit": "MiB/s", "h2d_bytes_per_step": int(st_e2e["h2d_bytes"]),
+                    "d2h_bytes_per_step": int(st_e2e["d2h_bytes"]), "ms_per_step": ms_e2e},
+            "gpu_launches": int(launches_timed),
+            "roofline": {"kernel": "sss_kernel (fused window fingerprints + SSS selection)", "bound": "hbm",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                         "algorithmic_bytes": int(alg_bytes), "kernel_ms": k_ms, "traffic": None},
+            "phases_ms": {k[2:-3]: st_res[k] / 1e6 for k in st_res if k.startswith("t_")},
+            "clocks": clocks,
+        }
+        if not args.no_cpu_baseline:
+            sample = text[: args.cpu_sample_mib * MIB]
+            cores = os.cpu_count() or 1
+            sec, kind = cpu_reference_run(sample, args.tau, cores)
+            used = cores if kind == "reference" else 1
+            out["cpu_baseline"] = {"value": (sample.size / MIB) / sec, "unit": "MiB/s", "cores": used, "kind": kind,
+                                   "sample": f"first {sample.size // MIB} MiB of the workload text, num_threads={used}, one run"}
+    barrier()
+    if rank == 0:
+        print(json.dumps(out))
+    F.free_device_text(d_text)
+    F.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

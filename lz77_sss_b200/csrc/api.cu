@@ -539,6 +539,7 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
         CUDA_CHECK(cudaMemcpyAsync(P.h_plcel.p, P.lce.psv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
         CUDA_CHECK(cudaMemcpyAsync(P.h_nlcel.p, P.lce.nsv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
         CUDA_CHECK(cudaStreamSynchronize(s));
+        st.d2h_bytes += size_s * (8 + 5 * sizeof(pos_t));
     }
     st.t_d2h_ns = ns_since(t0);
 
@@ -575,6 +576,7 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     }
     bp.fetch_main();
     st.t_gap_hash_ns = ns_since(t0);
+    st.h2d_bytes += 24 * bp.beg.size();
 
     // greedy emission
     t0 = clk::now();
@@ -583,6 +585,7 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     else z = greedy_emit<uint64_t>(h, host_text, g, bp, emit, ctx);
     st.num_factors = z;
     st.gap_positions_hashed = bp.hashed;
+    st.d2h_bytes += 20 * bp.hashed;
     st.t_emit_ns = ns_since(t0);
     return LZ77SSS_OK;
 }
@@ -702,6 +705,7 @@ int lz77sss_factorize_approximate(lz77sss_handle* h, const uint8_t* text, uint64
         uint64_t t_h2d = ns_since(t0);
         int rc = factorize_dispatch(h, d, text, n, emit, ctx);
         h->stats.t_h2d_ns = t_h2d;
+        h->stats.h2d_bytes += n;
         h->stats.t_total_ns += t_h2d;
         h->cfg.pos_bits = saved.pos_bits == 0 ? 0 : h->cfg.pos_bits;
         return rc;

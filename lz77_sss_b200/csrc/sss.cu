@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(NT) sss_kernel(const uint8_t* __restrict__ T, 
     uint32_t* sId = sPre + NID;                                // NID ids
     uint32_t* sE = sId + NID;                                  // NT exclusive prefix hashes
     __shared__ uint32_t s_warp[NW];
-    __shared__ uint32_t s_wmin_pre[NW], s_wmin_suf[NW];
+    __shared__ uint32_t s_wmin_pre[NW];
     __shared__ uint32_t s_tile, s_cnt[NW];
     __shared__ unsigned long long s_base;
     __shared__ uint32_t s_q;
@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(NT) sss_kernel(const uint8_t* __restrict__ T, 
             uint32_t v_id = q ? ID_INF : ((fp & 0x7FFFFFFEu) | 1u);
             if (j >= nw) v_id = (j == nw) ? 0u : ID_INF;
             id[k] = v_id;
-            if (q && j - i0 < (uint64_t)B && j < nw) qcount++;
+            if (q && (j - i0 < (uint64_t)B || tile == gridDim.x - 1) && j < nw) qcount++;   // the last tile also owns the windows past its candidates
             uint32_t bo = (own[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
             uint32_t bi = (in4[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
             fp = fp * c.base + bi - c.btau * bo;

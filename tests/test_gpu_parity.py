@@ -1,0 +1,170 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI, against
+ (1) the committed golden vectors produced by the reference's own code,
+ (2) the oracle on fresh seeded inputs (every stage: S, SA_S, LCP_S, LPF phrases, factor stream, LCE batch),
+ (3) size-independent properties at bench-scale sizes (decode round trip, factors well formed)."""
+import glob
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from lz77_sss_b200 import synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+TAUS = [4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096]
+
+
+def _eq(a, b):
+    return a.size == b.size and (a == b).all()
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_golden_vectors(capi, path):
+    g = np.load(path)
+    text = g["text"]
+    for k in [k for k in g.files if k.endswith("_src")]:
+        tau, p = k[:-4].split("_")
+        tau, p, key = int(tau[3:]), int(p[1:]), k[:-4]
+        with capi.Factorizer(tau=tau, num_threads=p, gap_bases=g[key + "_bases"]) as F:
+            src, ln = F.factorize(text)
+            assert _eq(src, g[key + "_src"]) and _eq(ln, g[key + "_len"]), (key, "factor stream")
+            assert _eq(F.sss(), g[f"tau{tau}_S"]), (key, "S")
+            assert _eq(F.sa_s(), g[f"tau{tau}_SA"]), (key, "SA_S")
+            b, e, s, blk = F.lpf()
+            lpf = g[key + "_lpf"]
+            assert _eq(b, lpf[0]) and _eq(e, lpf[1]) and _eq(s, lpf[2]) and _eq(blk.astype(np.uint64), lpf[3]), (key, "LPF")
+            assert (F.decode(src, ln, text.size) == text).all(), (key, "decode")
+
+
+def _texts():
+    rng = np.random.default_rng(5)
+    return {
+        "rep": synth.random_repetitive(400_000, seed=41),
+        "rep_runs": synth.random_repetitive(300_000, seed=42, rep=0.5, run=0.9),
+        "dna": synth.dna_collection(500_000, seed=43, chrom_len=60_000),
+        "markov": synth.markov_text(200_000, seed=44),
+        "random": rng.integers(0, 256, size=80_000).astype(np.uint8),
+        "binary": rng.integers(0, 2, size=60_000).astype(np.uint8),
+        "zeros": np.zeros(50_000, dtype=np.uint8),
+        "period3": np.tile(np.frombuffer(b"abc", dtype=np.uint8), 20_000),
+        "period100": np.tile(rng.integers(0, 4, size=100).astype(np.uint8), 900),
+        "xx": np.tile(synth.markov_text(70_000, seed=45), 2),
+    }
+
+
+@pytest.mark.parametrize("tau", TAUS)
+def test_sync_set_all_taus(capi, oracle, tau):
+    for name, text in _texts().items():
+        with capi.Factorizer(tau=tau) as F:
+            S, nq = F.build_sss(text)
+        So, nqo = oracle.sss(text, tau)
+        assert _eq(S, So), (name, tau)
+        assert nq == nqo, (name, tau)
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 6, 7, 8, 15, 100, 1022, 1023, 1024, 1025, 2047, 8191, 8192, 8193, 16385])
+def test_sync_set_tiny_and_ragged(capi, oracle, n):
+    text = synth.random_repetitive(max(n, 1), seed=n + 1)[:n]
+    for tau in (4, 16, 512, 4096):
+        with capi.Factorizer(tau=tau) as F:
+            S, nq = F.build_sss(text)
+        So, nqo = oracle.sss(text, tau)
+        assert _eq(S, So) and nq == nqo, (n, tau)
+
+
+@pytest.mark.parametrize("tau,p", [(4, 1), (8, 2), (16, 1), (32, 3), (64, 1), (128, 4), (256, 1), (512, 1), (512, 5),
+                                   (1024, 1), (2048, 2), (4096, 1)])
+def test_every_stage_against_oracle(capi, oracle, tau, p):
+    bases = (300 + tau, 70_001, 123_457, 999_983, 1_048_575)
+    for name, text in _texts().items():
+        n = text.size
+        osrc, olen, ost = oracle.factorize(text, tau, bases, p_ref=p)
+        with capi.Factorizer(tau=tau, num_threads=p, gap_bases=bases) as F:
+            src, ln = F.factorize(text)
+            S = F.sss()
+            So, _ = oracle.sss(text, tau)
+            assert _eq(S, So), (name, "S")
+            if S.size:
+                sao = oracle.sa_s(text, tau, So)
+                assert _eq(F.sa_s(), sao), (name, "SA_S")
+                assert _eq(F.lcp_s(), oracle.lcp_s(text, So, sao)), (name, "LCP_S")
+            b, e, s, blk = F.lpf()
+            bo, eo, so, blko = oracle.lpf_opt(text, tau, p_ref=p)
+            assert _eq(b, bo) and _eq(e, eo) and _eq(s, so) and _eq(blk, blko), (name, "LPF")
+            st = F.stats()
+            assert st["patt_lens"] == list(ost.patt_lens) and st["table_entries"] == ost.table_entries, (name, "gap parameters")
+            assert st["num_lpf"] == ost.num_lpf and st["num_gaps"] == ost.num_gaps and st["len_lpf_phr"] == ost.len_lpf_phr
+            assert _eq(src, osrc) and _eq(ln, olen), (name, "factor stream")
+            rng = np.random.default_rng(9)
+            qi = rng.integers(0, n, size=1500).astype(np.uint64)
+            qj = rng.integers(0, n, size=1500).astype(np.uint64)
+            if S.size > 1:
+                qi[:400] = S[rng.integers(0, S.size, size=400)]
+                qj[:400] = S[rng.integers(0, S.size, size=400)]
+            qj[400:450] = qi[400:450]
+            _, lce = oracle.lce_batch(text, tau, qi, qj)
+            assert _eq(F.lce_batch(qi, qj), lce), (name, "LCE")
+            assert (F.decode(src, ln, n) == text).all(), (name, "decode")
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 9, 17, 33, 63, 64, 65, 66, 130, 700, 1500, 3000])
+def test_short_inputs_end_of_text_rules(capi, oracle, n):
+    """Stale-fingerprint and window-fit rules at the end of the text (rolling_hash_index_107.hpp:93,112,123,145)."""
+    bases = (257, 65_599, 131_071, 524_287, 1_048_573)
+    for seed in range(4):
+        text = np.random.default_rng(1000 * n + seed).integers(0, 3, size=n).astype(np.uint8)
+        for tau in (4, 512):
+            osrc, olen, _ = oracle.factorize(text, tau, bases, p_ref=1)
+            with capi.Factorizer(tau=tau, num_threads=1, gap_bases=bases) as F:
+                src, ln = F.factorize(text)
+                assert _eq(src, osrc) and _eq(ln, olen), (n, seed, tau)
+                assert (F.decode(src, ln, n) == text).all()
+
+
+def _check_factors(text, src, ln):
+    n = text.size
+    lens = np.maximum(ln, 1).astype(np.int64)
+    pos = np.concatenate([[0], np.cumsum(lens)])
+    assert pos[-1] == n
+    cp = ln > 0
+    assert (src[cp].astype(np.int64) < pos[:-1][cp]).all()
+    assert (text[pos[:-1][~cp]] == src[~cp].astype(np.uint8)).all()
+    # spot-check the copies
+    idx = np.nonzero(cp)[0]
+    for k in idx[:: max(1, idx.size // 2000)]:
+        s, l, p = int(src[k]), int(ln[k]), int(pos[k])
+        l = min(l, 4096)
+        assert (text[s:s + l] == text[p:p + l]).all()
+
+
+def test_c1_64mib_properties(capi):
+    """BASELINE config C1 at full size: decode(factorize(T)) == T, factors well formed."""
+    text = synth.random_repetitive(64 << 20, seed=1)
+    with capi.Factorizer(tau=512, num_threads=1) as F:
+        src, ln = F.factorize(text)
+        _check_factors(text, src, ln)
+        assert (F.decode(src, ln, text.size) == text).all()
+        S = F.sss()
+        assert (np.diff(S.astype(np.int64)) > 0).all() and S[-1] == text.size - 2 * 512 + 1
+
+
+def test_c2_quarter_gib_dna_properties(capi):
+    text = synth.dna_collection(256 << 20, seed=2, chrom_len=4 << 20)
+    with capi.Factorizer(tau=512, num_threads=1) as F:
+        src, ln = F.factorize(text)
+        _check_factors(text, src, ln)
+        assert (F.decode(src, ln, text.size) == text).all()
+
+
+def test_cpp_header_example_runs(capi, tmp_path):
+    exe = tmp_path / "example"
+    cmd = ["/usr/bin/g++", "-std=c++20", "-O1", "-I" + os.path.join(ROOT, "include"),
+           "-I" + os.path.join(ROOT, "lz77_sss_b200", "include"), os.path.join(ROOT, "examples", "lz77_sss_example.cpp"),
+           "-L" + os.path.join(ROOT, "lz77_sss_b200"), "-llz77sss_b200", "-o", str(exe)]
+    subprocess.run(cmd, check=True)
+    env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(ROOT, "lz77_sss_b200"))
+    r = subprocess.run([str(exe)], capture_output=True, text=True, env=env)
+    assert r.returncode == 0 and "decode ok" in r.stdout, r.stdout + r.stderr
