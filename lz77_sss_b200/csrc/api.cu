@@ -394,6 +394,10 @@ uint64_t greedy_emit(lz77sss_handle* h, const uint8_t* T, const gap_params& g, b
     uint64_t num_fact = 0;
     uint32_t i_p = 0;
     size_t li = 0;
+    // next_lpf mutates the first surviving phrase of the next block (factorize/common.cpp:90-96); remember the
+    // shifts so that the introspection view (lz77sss_get_lpf) keeps the phrases as build_LPF_opt produced them
+    struct undo_t { uint32_t blk; size_t idx; uint64_t offs; };
+    std::vector<undo_t> undo;
     while (LPF[i_p].empty()) i_p++;
     auto next_lpf = [&]() {
         lpf_t phr = LPF[i_p][li++];
@@ -408,6 +412,7 @@ uint64_t greedy_emit(lz77sss_handle* h, const uint8_t* T, const gap_params& g, b
                         const uint64_t offs = phr.end - V[li].beg;
                         V[li].beg += offs;
                         V[li].src += offs;
+                        undo.push_back({i_p, li, offs});
                     }
                 } while (li == LPF[i_p].size() && i_p < p - 1);
             } else {
@@ -476,6 +481,7 @@ uint64_t greedy_emit(lz77sss_handle* h, const uint8_t* T, const gap_params& g, b
         while (ph.end <= i) ph = next_lpf();
     }
     LPF[p - 1].pop_back();   // keep the introspection view free of the sentinel
+    for (auto& u : undo) { LPF[u.blk][u.idx].beg -= u.offs; LPF[u.blk][u.idx].src -= u.offs; }
     return num_fact;
 }
 
