@@ -682,6 +682,7 @@ int lz77sss_create(const lz77sss_config* cfg, lz77sss_handle** out) {
         if (h->cfg.sss_base == 0) h->cfg.sss_base = 0x9E3779B1u;
         if (h->cfg.sss_qmax == 0xFFFFFFFFu) h->cfg.sss_qmax = 32;
         if ((h->cfg.sss_base & 1) == 0) return fail(LZ77SSS_E_ARG, "sss_base must be odd");
+        if (h->cfg.sss_qmax > 32) return fail(LZ77SSS_E_ARG, "sss_qmax must be <= 32 (one warp lane per candidate period)");
         std::memset(&h->stats, 0, sizeof h->stats);
         CUDA_CHECK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
         *out = h.release();

@@ -378,9 +378,11 @@ void sss_build(const uint8_t* d_text, uint64_t n, uint32_t tau, uint32_t base, u
     *h_numq = 0;
     if (n + 1 < 2 * (uint64_t)tau) return;
     sc.ticket.reserve(1);
-    sc.counters.reserve(2);
+    sc.counters.reserve(4);
     if (tau < 16) {
         sss_build_small_tau(d_text, n, tau, base, qmax, d_S, pos_bytes, s_cap, sc, st);
+    } else if (tau >= 128) {
+        sss_build_cell(d_text, n, tau, base, qmax, d_S, pos_bytes, s_cap, sc, st);
     } else {
         sss_consts c;
         c.base = base;

@@ -16,12 +16,15 @@ struct sss_scratch {
     dbuf<unsigned int> ticket;
     dbuf<unsigned long long> counters;
     dbuf<uint32_t> blk;
+    dbuf<uint16_t> stage;   // per-tile staging of selected positions (sss_cell.cu)
     scan_scratch scan;
 };
 uint32_t sss_period_bound(uint32_t tau, uint32_t qmax);
 uint32_t sss_anchor_spacing(uint32_t tau, uint32_t P);
 void sss_build(const uint8_t* d_text, uint64_t n, uint32_t tau, uint32_t base, uint32_t qmax, void* d_S, int pos_bytes,
                uint64_t s_cap, sss_scratch& sc, cudaStream_t st, uint64_t* h_size, uint64_t* h_numq);
+void sss_build_cell(const uint8_t* d_text, uint64_t n, uint32_t tau, uint32_t base, uint32_t qmax, void* d_S, int pos_bytes,
+                    uint64_t s_cap, sss_scratch& sc, cudaStream_t st);
 void sss_build_small_tau(const uint8_t* d_text, uint64_t n, uint32_t tau, uint32_t base, uint32_t qmax, void* d_S,
                          int pos_bytes, uint64_t s_cap, sss_scratch& sc, cudaStream_t st);
 
