@@ -65,6 +65,7 @@ typedef struct lz77sss_stats {
     uint64_t t_h2d_ns, t_sss_ns, t_sort_ns, t_lce_ns, t_lpf_ns, t_d2h_ns, t_chain_ns, t_gap_hash_ns, t_emit_ns, t_total_ns;
     uint64_t kernel_launches;
     uint64_t h2d_bytes, d2h_bytes;   /* bytes copied host->device / device->host inside the call */
+    uint64_t parse_rounds, parse_slices;   /* device emission: block-parse rounds over all slices, slices */
 } lz77sss_stats;
 
 /* factor callback: lz77_sss<pos_t>::factor {src,len} by value, in text order, on the calling thread

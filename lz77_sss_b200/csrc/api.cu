@@ -17,6 +17,7 @@
 #include <limits>
 #include <memory>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/lz77sss_b200.h"
@@ -91,6 +92,12 @@ struct lz77sss_handle {
     hbuf<uint32_t> h_ids;
     hbuf<uint64_t> h_rng;
     std::vector<uint8_t*> user_texts;
+    // device emission
+    gap_parse_scratch gp;
+    std::vector<uint64_t> f_src, f_len;
+    uint64_t slice_len = 1ull << 28;
+    uint32_t block_len = 2048;
+    bool host_emit = false;
 };
 
 namespace {
@@ -329,18 +336,39 @@ struct bucket_provider {
 };
 
 // rolling_hash_index_107 without the fingerprints: cur_pos, the table of last writers, and the rule for stale
-// fingerprints at the end of the text (rolling_hash_index_107.hpp:80-150)
+// fingerprints at the end of the text (rolling_hash_index_107.hpp:80-150).  table_t: dense vector (whole text on the
+// host) or the sparse view of the device table that the tail of the text needs.
 template <typename ent_t>
+struct dense_table {
+    std::vector<ent_t> H;
+    explicit dense_table(uint64_t entries) { H.assign(entries, (ent_t)~(ent_t)0); }
+    uint64_t get(uint32_t b) const { return H[b] == (ent_t)~(ent_t)0 ? ~0ull : (uint64_t)H[b]; }
+    void set(uint32_t b, uint64_t pos) { H[b] = (ent_t)pos; }
+};
+struct sparse_table {
+    std::unordered_map<uint32_t, uint64_t> H;   // every bucket the tail can touch is pre-loaded from the device
+    uint64_t get(uint32_t b) const {
+        auto it = H.find(b);
+        if (it == H.end()) throw std::logic_error("tail emission touched a bucket that was not fetched");
+        return it->second;
+    }
+    void set(uint32_t b, uint64_t pos) {
+        auto it = H.find(b);
+        if (it == H.end()) throw std::logic_error("tail emission touched a bucket that was not fetched");
+        it->second = pos;
+    }
+};
+template <typename table_t>
 struct gap_index {
     bucket_provider& bp;
+    table_t& H;
     uint64_t n;
     std::array<uint64_t, 5> L;
-    std::vector<ent_t> H;
     uint64_t cur_pos = 0;
     bool zero[5];   // fingerprint x was reset at a position where the window no longer fits: it stays 0
-    gap_index(bucket_provider& bp_, uint64_t n_, const gap_params& g) : bp(bp_), n(n_), L(g.patt_lens) {
-        H.assign(g.table_entries, (ent_t)~(ent_t)0);
-        reinit(0);
+    gap_index(bucket_provider& bp_, table_t& H_, uint64_t n_, const gap_params& g, uint64_t start_pos)
+        : bp(bp_), H(H_), n(n_), L(g.patt_lens) {
+        reinit(start_pos);
     }
     void reinit(uint64_t pos) {
         cur_pos = pos;
@@ -354,17 +382,17 @@ struct gap_index {
     }
     void advance() {
         for (int x = 0; x < 5; x++)
-            if (cur_pos + L[x] < n) H[bp.get(cur_pos, x)] = (ent_t)cur_pos;
+            if (cur_pos + L[x] < n) H.set(bp.get(cur_pos, x), cur_pos);
         cur_pos++;
     }
     void advance_i(int x) {
-        if (cur_pos + L[x] < n) H[bp.get(cur_pos, x)] = (ent_t)cur_pos;
+        if (cur_pos + L[x] < n) H.set(bp.get(cur_pos, x), cur_pos);
     }
     uint64_t advance_and_get_occ(int x) {
         const uint32_t b = bucket(x);
-        const ent_t occ = H[b];
-        H[b] = (ent_t)cur_pos;
-        return occ == (ent_t)~(ent_t)0 ? ~0ull : (uint64_t)occ;
+        const uint64_t occ = H.get(b);
+        H.set(b, cur_pos);
+        return occ;
     }
 };
 
@@ -382,25 +410,22 @@ inline uint64_t host_lce(const uint8_t* T, uint64_t n, uint64_t src, uint64_t po
     return k;
 }
 
-// factorize + next_lpf (approximate/factorize/common.cpp:66-111) and factorize_greedy (greedy.cpp:34-140)
-template <typename ent_t>
-uint64_t greedy_emit(lz77sss_handle* h, const uint8_t* T, const gap_params& g, bucket_provider& bp,
-                     lz77sss_emit_fn emit, void* ctx) {
+// next_lpf (approximate/factorize/common.cpp:74-104) takes no argument, so the sequence of phrases it returns is
+// fixed before the emission starts: the per-block lists concatenated, where the first survivor of a block is
+// trimmed against the last phrase of the previous one, and the sentinel {n, n+1, 0} (lz77_sss.hpp:418,423) at the end.
+std::vector<lpf_t> merged_phrase_list(lz77sss_handle* h) {
     const uint64_t n = h->n;
     const uint32_t p = h->cfg.num_threads;
-    auto& LPF = h->LPF;
-    LPF[p - 1].push_back(lpf_t{n, n + 1, 0});       // sentinel (lz77_sss.hpp:418,423)
-    gap_index<ent_t> idx(bp, n, g);
-    uint64_t num_fact = 0;
+    std::vector<std::vector<lpf_t>> LPF = h->LPF;    // trimmed copies; the introspection view stays as built
+    LPF[p - 1].push_back(lpf_t{n, n + 1, 0});
+    std::vector<lpf_t> ML;
     uint32_t i_p = 0;
     size_t li = 0;
-    // next_lpf mutates the first surviving phrase of the next block (factorize/common.cpp:90-96); remember the
-    // shifts so that the introspection view (lz77sss_get_lpf) keeps the phrases as build_LPF_opt produced them
-    struct undo_t { uint32_t blk; size_t idx; uint64_t offs; };
-    std::vector<undo_t> undo;
     while (LPF[i_p].empty()) i_p++;
-    auto next_lpf = [&]() {
+    while (true) {
         lpf_t phr = LPF[i_p][li++];
+        ML.push_back(phr);
+        if (phr.beg == n) break;
         if (li == LPF[i_p].size()) {
             if (i_p < p - 1 && p > 1) {
                 do {
@@ -412,14 +437,26 @@ uint64_t greedy_emit(lz77sss_handle* h, const uint8_t* T, const gap_params& g, b
                         const uint64_t offs = phr.end - V[li].beg;
                         V[li].beg += offs;
                         V[li].src += offs;
-                        undo.push_back({i_p, li, offs});
                     }
                 } while (li == LPF[i_p].size() && i_p < p - 1);
             } else {
                 li--;
             }
         }
-        return phr;
+    }
+    return ML;
+}
+
+// factorize (approximate/factorize/common.cpp:66-111) + factorize_greedy (greedy.cpp:34-140) from the state
+// (i, idx.cur_pos, k): ML[k] is the first phrase that ends behind i.
+template <typename table_t>
+uint64_t greedy_emit_from(const uint8_t* T, uint64_t n, const std::vector<lpf_t>& ML, const gap_params& g,
+                          gap_index<table_t>& idx, uint64_t i, size_t k, lz77sss_emit_fn emit, void* ctx) {
+    uint64_t num_fact = 0;
+    const size_t last = ML.size() - 1;
+    auto next_lpf = [&]() {
+        if (k < last) k++;
+        return ML[k];
     };
     auto longest_prev_occ = [&](uint64_t pos, uint64_t& f_src, uint64_t& f_len) {   // factorize/common.cpp:33-61
         f_src = T[pos];
@@ -437,8 +474,8 @@ uint64_t greedy_emit(lz77sss_handle* h, const uint8_t* T, const gap_params& g, b
         }
         idx.cur_pos++;
     };
-    lpf_t ph = next_lpf();
-    for (uint64_t i = 0;;) {
+    lpf_t ph = ML[k];
+    while (true) {
         uint64_t gap_end = ph.beg;
         if (i < gap_end) {
             if (idx.cur_pos < i) {
@@ -480,8 +517,6 @@ uint64_t greedy_emit(lz77sss_handle* h, const uint8_t* T, const gap_params& g, b
         i += ll;
         while (ph.end <= i) ph = next_lpf();
     }
-    LPF[p - 1].pop_back();   // keep the introspection view free of the sentinel
-    for (auto& u : undo) { LPF[u.blk][u.idx].beg -= u.offs; LPF[u.blk][u.idx].src -= u.offs; }
     return num_fact;
 }
 
@@ -561,37 +596,97 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     h->have_result = true;
     if (g.patt_lens[0] == 0) return fail(LZ77SSS_E_UNSUPPORTED, "degenerate phrase statistics (no LPF phrase or no gap): pattern lengths undefined in the reference (SURVEY.md A7)");
 
-    // K5: bucket ids of every position the emission can insert or probe
-    t0 = clk::now();
+    const std::vector<lpf_t> ML = merged_phrase_list(h);
     bucket_provider bp;
     bp.h = h;
     for (int x = 0; x < 5; x++) { bp.gp.patt_len[x] = g.patt_lens[x]; bp.gp.base[x] = h->cfg.gap_bases[x]; }
     bp.gp.mask = g.table_entries - 1;
-    {
-        uint64_t cur = 0;
-        for (auto& V : h->LPF)
-            for (auto& ph : V) {
-                if (ph.end <= cur) continue;
-                const uint64_t b = std::max(ph.beg, cur);
-                bp.beg.push_back(cur);
-                bp.end.push_back(b + 1);
-                cur = ph.end;
-            }
-        if (cur < n) { bp.beg.push_back(cur); bp.end.push_back(n); }
-        // the windows whose fingerprints go stale at the end of the text (n - patt_len) are fetched on demand
-    }
-    bp.fetch_main();
-    st.t_gap_hash_ns = ns_since(t0);
-    st.h2d_bytes += 24 * bp.beg.size();
 
-    // greedy emission
+    if (h->host_emit) {
+        // debugging path (LZ77SSS_HOST_EMIT=1): the whole emission on the host, bucket ids from the device
+        t0 = clk::now();
+        {
+            uint64_t cur = 0;
+            for (auto& V : h->LPF)
+                for (auto& ph : V) {
+                    if (ph.end <= cur) continue;
+                    const uint64_t b = std::max(ph.beg, cur);
+                    bp.beg.push_back(cur);
+                    bp.end.push_back(b + 1);
+                    cur = ph.end;
+                }
+            if (cur < n) { bp.beg.push_back(cur); bp.end.push_back(n); }
+        }
+        bp.fetch_main();
+        st.t_gap_hash_ns = ns_since(t0);
+        st.h2d_bytes += 24 * bp.beg.size();
+        t0 = clk::now();
+        uint64_t z;
+        if (h->cfg.pos_bits == 32) {
+            dense_table<uint32_t> H(g.table_entries);
+            gap_index<dense_table<uint32_t>> idx(bp, H, n, g, 0);
+            z = greedy_emit_from(host_text, n, ML, g, idx, 0, 0, emit, ctx);
+        } else {
+            dense_table<uint64_t> H(g.table_entries);
+            gap_index<dense_table<uint64_t>> idx(bp, H, n, g, 0);
+            z = greedy_emit_from(host_text, n, ML, g, idx, 0, 0, emit, ctx);
+        }
+        st.num_factors = z;
+        st.gap_positions_hashed = bp.hashed;
+        st.d2h_bytes += 20 * bp.hashed;
+        st.t_emit_ns = ns_since(t0);
+        return LZ77SSS_OK;
+    }
+
+    // greedy emission on the device up to n_cut; the last 65 positions (end-of-text rules of the gap index) on the host
     t0 = clk::now();
-    uint64_t z;
-    if (h->cfg.pos_bits == 32) z = greedy_emit<uint32_t>(h, host_text, g, bp, emit, ctx);
-    else z = greedy_emit<uint64_t>(h, host_text, g, bp, emit, ctx);
+    const uint64_t n_cut = n > 65 ? n - 65 : 0;
+    std::vector<uint64_t> h_ml(3 * ML.size());
+    for (size_t q = 0; q < ML.size(); q++) {
+        h_ml[q] = ML[q].beg;
+        h_ml[ML.size() + q] = ML[q].end;
+        h_ml[2 * ML.size() + q] = ML[q].src;
+    }
+    h->f_src.clear();
+    h->f_len.clear();
+    uint64_t ho[4];
+    gap_hash_params gpar = bp.gp;
+    gap_parse_run<pos_t>(d_text, n, tau, P.S.get(), size_s, P.suf, P.lce, gpar, g.table_entries, h_ml.data(), ML.size(), n_cut,
+                         h->slice_len, h->block_len, h->gp, s, h->f_src, h->f_len, ho);
+    st.h2d_bytes += 24 * ML.size();
+    st.d2h_bytes += 16 * h->f_src.size();
+    st.gap_positions_hashed = h->gp.entries_sorted / 5;
+    st.parse_rounds = h->gp.rounds;
+    st.parse_slices = h->gp.slices;
+    st.t_gap_hash_ns = ns_since(t0);
+
+    t0 = clk::now();
+    uint64_t z = h->f_src.size();
+    for (uint64_t q = 0; q < z; q++) emit(ctx, h->f_src[q], h->f_len[q]);
+    if (ho[0] < n) {
+        // tail: table entries of every bucket the remaining positions can touch
+        const uint64_t tb = n > 65 ? n - 65 : 0;
+        bp.beg.push_back(tb);
+        bp.end.push_back(n);
+        bp.fetch_main();
+        std::vector<uint32_t> buckets;
+        buckets.push_back(0);
+        for (uint64_t pos = tb; pos < n; pos++)
+            for (int x = 0; x < 5; x++)
+                if (pos + g.patt_lens[x] <= n) buckets.push_back(bp.get(pos, x));
+        std::sort(buckets.begin(), buckets.end());
+        buckets.erase(std::unique(buckets.begin(), buckets.end()), buckets.end());
+        std::vector<uint64_t> vals(buckets.size());
+        gap_parse_query(h->gp, buckets.data(), (uint32_t)buckets.size(), vals.data(), s);
+        sparse_table H;
+        for (size_t q = 0; q < buckets.size(); q++) H.H[buckets[q]] = vals[q] ? vals[q] - 1 : ~0ull;
+        gap_index<sparse_table> idx(bp, H, n, g, 0);
+        idx.cur_pos = ho[1];                       // every window fitted at the last reinit: no zero flags
+        for (int x = 0; x < 5; x++) idx.zero[x] = false;
+        z += greedy_emit_from(host_text, n, ML, g, idx, ho[0], (size_t)ho[2], emit, ctx);
+        st.d2h_bytes += 20 * bp.hashed + 8 * buckets.size();
+    }
     st.num_factors = z;
-    st.gap_positions_hashed = bp.hashed;
-    st.d2h_bytes += 20 * bp.hashed;
     st.t_emit_ns = ns_since(t0);
     return LZ77SSS_OK;
 }
@@ -684,6 +779,9 @@ int lz77sss_create(const lz77sss_config* cfg, lz77sss_handle** out) {
         if ((h->cfg.sss_base & 1) == 0) return fail(LZ77SSS_E_ARG, "sss_base must be odd");
         if (h->cfg.sss_qmax > 32) return fail(LZ77SSS_E_ARG, "sss_qmax must be <= 32 (one warp lane per candidate period)");
         std::memset(&h->stats, 0, sizeof h->stats);
+        if (const char* e = getenv("LZ77SSS_HOST_EMIT")) h->host_emit = e[0] == '1';
+        if (const char* e = getenv("LZ77SSS_SLICE_LEN")) h->slice_len = std::max<uint64_t>(64, strtoull(e, nullptr, 10));
+        if (const char* e = getenv("LZ77SSS_BLOCK_LEN")) h->block_len = (uint32_t)std::max<uint64_t>(32, strtoull(e, nullptr, 10));
         CUDA_CHECK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
         *out = h.release();
         return LZ77SSS_OK;

@@ -1,0 +1,587 @@
+// Greedy phrase emission on the device: factorize_greedy + longest_prev_occ + rolling_hash_index_107
+// (/root/reference/include/lz77_sss/algorithms/approximate/factorize/greedy.cpp:34-140,
+//  .../factorize/common.cpp:33-111, include/lz77_sss/data_structures/rolling_hash_index_107.hpp:80-150).
+//
+// The reference walks the text once, and at every gap position performs 5 read-modify-writes of one shared hash
+// table H[fp & mask] = position.  Everything here rests on one observation: positions are inserted in increasing
+// order, so "H[b] at the time position i is probed" is the LARGEST INSERTED position <= i among the entries that
+// fall into bucket b.  That is an offline predecessor problem:
+//   1. hash:   bucket ids of all 5 pattern lengths for every position of a slice (gap_entries_kernel),
+//   2. sort:   stable radix sort of the entries by bucket  ->  every bucket is a list in insertion order,
+//   3. parse:  the text is cut into blocks; one warp parses one block exactly like the reference does
+//              (gap steps, phrase steps, truncation, phrase-start probes), answering each table probe by walking
+//              its bucket list backwards to the nearest entry whose position is marked "inserted";
+//              blocks start speculatively at their first position, then
+//   4. link:   the true chain of blocks (exit state of one = entry state of the next) is followed by pointer
+//              doubling, entry states are propagated, the inserted-bitmap is rebuilt from the traces,
+//   and 3-4 repeat until no trace changes.  The fixed point is unique and equals the sequential parse
+//   (the prefix that is already right grows by at least one block per round; in practice 3-5 rounds suffice,
+//   because LZ parses re-synchronise within a few factors).
+// Slices bound the memory (5 entries per position) and carry the table as "last inserted position per bucket".
+// The last 65 positions of the text, where the reference's end-of-text rules for stale fingerprints apply,
+// are finished by the host with the table entries it asks for (api.cu).
+#include <vector>
+
+#include "common.cuh"
+#include "device_utils.cuh"
+#include "lce_device.cuh"
+#include "stages.cuh"
+
+namespace lz77sss {
+namespace {
+
+__extension__ typedef unsigned __int128 u128;
+constexpr uint64_t NONE64 = ~0ull;
+constexpr uint32_t KIND_PHR = 1u << 30, KIND_PROBED = 1u << 31, POS_MASK = (1u << 30) - 1;
+constexpr int RUN = 64;   // positions per thread in the hash kernel
+
+struct ghp5 {
+    uint64_t L[5];
+    uint64_t base[5];
+    uint64_t nb_lo[5], nb_hi[5];   // -(base^L) mod P
+    uint64_t mask;
+    uint32_t invalid_key;          // table_entries (sorts behind every bucket)
+};
+
+__device__ __forceinline__ u128 mers_mod107(u128 x) {
+    const u128 P = (((u128)1) << 107) - 1;
+    x = (x & P) + (x >> 107);
+    x = (x & P) + (x >> 107);
+    return x >= P ? x - P : x;
+}
+
+// keys[5*rel + (4-x)] = bucket of the window of pattern x at position a0+rel (insertion order of the reference:
+// positions ascending, patterns 4..0), invalid_key where the reference does not hash (pos + L >= n);
+// vals[e] = e.
+__global__ void __launch_bounds__(128) gap_entries_kernel(const uint8_t* __restrict__ T, uint64_t n, const ghp5 hp,
+                                                          uint64_t a0, uint64_t cnt, uint32_t* __restrict__ keys,
+                                                          uint32_t* __restrict__ vals) {
+    const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t nruns = (cnt + RUN - 1) / RUN;
+    if (g >= nruns * 5) return;
+    const int x = (int)(g / nruns);
+    const uint64_t r0 = (g % nruns) * RUN;
+    const uint64_t r1 = r0 + RUN < cnt ? r0 + RUN : cnt;
+    const uint64_t L = hp.L[x];
+    const u128 base = hp.base[x];
+    const u128 nb = ((u128)hp.nb_hi[x] << 64) | hp.nb_lo[x];
+    const uint64_t pos0 = a0 + r0;
+    u128 fp = 0;
+    if (pos0 + L < n)
+        for (uint64_t j = 0; j < L; j++) fp = mers_mod107(fp * base + T[pos0 + j]);
+    for (uint64_t r = r0; r < r1; r++) {
+        const uint64_t pos = a0 + r;
+        uint32_t key = hp.invalid_key;
+        if (pos + L < n) {
+            key = (uint32_t)((uint64_t)fp & hp.mask);
+            const u128 infl = mers_mod107(nb * (u128)T[pos] + T[pos + L]);   // pos + L < n
+            fp = mers_mod107(fp * base + infl);
+        }
+        const uint64_t e = 5 * r + (4 - x);
+        keys[e] = key;
+        vals[e] = (uint32_t)e;
+    }
+}
+
+__global__ void inv_kernel(const uint32_t* __restrict__ vals, uint64_t E, uint32_t* __restrict__ inv) {
+    const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < E) inv[vals[k]] = (uint32_t)k;
+}
+
+struct block_state {
+    uint64_t i, cur, k;
+    uint32_t gap;      // last step before i was a gap step (positions up to i are inserted)
+    uint32_t pad;
+};
+
+struct parse_ctx {
+    uint64_t n, n_cut, a0, a1;
+    uint32_t BL, nb;
+    const uint32_t* skey;
+    const uint32_t* sval;
+    const uint32_t* inv;
+    const uint64_t* Hc;        // last inserted position + 1 per bucket (0 = none), state before the slice
+    const uint32_t* notins;    // bit = 1: position of the slice is NOT inserted
+    const uint64_t* ml_beg;
+    const uint64_t* ml_end;
+    const uint64_t* ml_src;
+    uint64_t m;
+    block_state* entry;
+    block_state* exit_;
+    uint8_t* marked;
+    uint32_t* tr_cnt;
+    uint32_t* tr_pos;
+    uint64_t* tr_src;
+    uint64_t* tr_len;
+    uint32_t* changed;
+};
+
+__device__ __forceinline__ bool not_inserted(const uint32_t* __restrict__ bm, uint32_t rel) {
+    return (bm[rel >> 5] >> (rel & 31)) & 1u;
+}
+
+// longest_prev_occ (factorize/common.cpp:33-61) at position i, all 32 lanes; lanes 0..4 own patterns 4..0
+template <typename pos_t>
+__device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>& V, uint64_t i, uint64_t& f_src,
+                                      uint64_t& f_len) {
+    const unsigned lane = threadIdx.x & 31;
+    const uint32_t rel = (uint32_t)(i - C.a0);
+    uint64_t occ = NONE64;
+    if (lane < 5) {
+        uint32_t kk = C.inv[5ull * rel + lane];
+        const uint32_t b = C.skey[kk];
+        while (true) {
+            if (kk == 0) { occ = C.Hc[b] - 1; break; }
+            kk--;
+            if (C.skey[kk] != b) { occ = C.Hc[b] - 1; break; }
+            const uint32_t q = C.sval[kk] / 5u;
+            if (q == rel) { occ = i; break; }                     // an earlier pattern of this position wrote the bucket
+            if (!not_inserted(C.notins, q)) { occ = C.a0 + q; break; }
+        }
+    }
+    const uint8_t ci = V.T[i];
+    const bool valid = lane < 5 && occ != NONE64 && occ < i && V.T[occ] == ci;
+    const unsigned m = __ballot_sync(0xffffffffu, valid);
+    if (!m) {
+        f_src = ci;
+        f_len = 0;
+        return;
+    }
+    const int win = __ffs(m) - 1;
+    f_src = __shfl_sync(0xffffffffu, occ, win);
+    f_len = warp_lce_r(V, f_src, i);
+}
+
+template <typename pos_t>
+__global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce_view<pos_t> V) {
+    const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const unsigned lane = threadIdx.x & 31;
+    if (b >= C.nb || !C.marked[b]) return;
+    const block_state st = C.entry[b];
+    uint64_t i = st.i, cur = st.cur, k = st.k;
+    uint32_t gap = st.gap;
+    uint64_t bend = C.a0 + (uint64_t)(b + 1) * C.BL;
+    if (bend > C.a1) bend = C.a1;
+    const uint64_t lim = bend < C.n_cut ? bend : C.n_cut;
+    const uint32_t oldlen = C.tr_cnt[b];
+    const uint64_t slot0 = (uint64_t)b * C.BL;
+    uint32_t t = 0;
+    bool chg = false;
+    while (i < lim) {
+        const uint64_t pb = C.ml_beg[k], pe = C.ml_end[k];
+        uint64_t o_src, o_len;
+        uint32_t kind;
+        const uint64_t at = i;
+        if (i < pb) {   // gap step (greedy.cpp:60-97)
+            probe<pos_t>(C, V, i, o_src, o_len);
+            uint64_t i2 = i + (o_len ? o_len : 1);
+            if (i2 > pb) {
+                if (i2 <= pe) {
+                    o_len -= i2 - pb;
+                    i2 = pb;
+                } else {
+                    while (C.ml_end[k] <= i2) k++;
+                }
+            }
+            kind = 0;
+            cur = i2;
+            i = i2;
+            gap = 1;
+        } else {        // phrase step (greedy.cpp:100-131)
+            const uint64_t exc = i - pb;
+            o_src = C.ml_src[k] + exc;
+            o_len = (pe - pb) - exc;
+            kind = KIND_PHR;
+            if (cur == i) {
+                uint64_t fs, fl;
+                probe<pos_t>(C, V, i, fs, fl);
+                cur = i + 1;
+                kind |= KIND_PROBED;
+                if (fl > o_len) { o_src = fs; o_len = fl; }
+            }
+            i += o_len;
+            while (C.ml_end[k] <= i) k++;
+            gap = 0;
+        }
+        if (lane == 0) {
+            const uint64_t sl = slot0 + t;
+            const uint32_t np = (uint32_t)(at - C.a0) | kind;
+            if (t >= oldlen || C.tr_pos[sl] != np || C.tr_src[sl] != o_src || C.tr_len[sl] != o_len) chg = true;
+            C.tr_pos[sl] = np;
+            C.tr_src[sl] = o_src;
+            C.tr_len[sl] = o_len;
+        }
+        t++;
+    }
+    if (lane == 0) {
+        const block_state old = C.exit_[b];
+        if (t != oldlen || old.i != i || old.cur != cur || old.k != k || old.gap != gap) chg = true;
+        block_state ex;
+        ex.i = i; ex.cur = cur; ex.k = k; ex.gap = gap; ex.pad = 0;
+        C.exit_[b] = ex;
+        C.tr_cnt[b] = t;
+        if (chg) atomicOr(C.changed, 1u);
+    }
+}
+
+// speculative entry of every block: a factor starts at its first position, the table cursor stands there
+__global__ void spec_entry_kernel(const parse_ctx C, block_state first) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= C.nb) return;
+    const uint64_t bs = C.a0 + (uint64_t)b * C.BL;
+    uint64_t bend = bs + C.BL;
+    if (bend > C.a1) bend = C.a1;
+    block_state st;
+    st.pad = 0;
+    C.tr_cnt[b] = 0;
+    block_state z;
+    z.i = z.cur = z.k = NONE64; z.gap = 0; z.pad = 0;
+    C.exit_[b] = z;
+    if (first.i >= bend) {          // the chain enters the slice behind this block
+        C.marked[b] = 0;
+        return;
+    }
+    C.marked[b] = 1;
+    if (first.i >= bs) {
+        st = first;
+    } else {
+        st.i = bs; st.cur = bs; st.gap = 1;
+        uint64_t lo = 0, hi = C.m - 1;   // first phrase with end > bs (the sentinel ends at n+1)
+        while (lo < hi) {
+            const uint64_t mid = (lo + hi) / 2;
+            if (C.ml_end[mid] > bs) hi = mid;
+            else lo = mid + 1;
+        }
+        st.k = lo;
+    }
+    C.entry[b] = st;
+}
+
+// One CTA: follows the chain of blocks from the block that holds `first.i` by pointer doubling, marks the blocks
+// on it, hands every exit state to the block it lands in, and reports the state that leaves the slice.
+__global__ void __launch_bounds__(1024) link_kernel(const parse_ctx C, block_state first, uint32_t* __restrict__ J,
+                                                    int levels, block_state* __restrict__ slice_exit) {
+    const uint32_t nb = C.nb, N = nb + 1;
+    const uint64_t stop = C.a1 < C.n_cut ? C.a1 : C.n_cut;
+    for (uint32_t b = threadIdx.x; b < N; b += blockDim.x) {
+        uint32_t j = nb;
+        if (b < nb) {
+            const uint64_t x = C.exit_[b].i;
+            if (x != NONE64 && x < stop) j = (uint32_t)((x - C.a0) / C.BL);
+        }
+        J[b] = j;
+    }
+    __syncthreads();
+    for (int l = 1; l < levels; l++) {
+        const uint32_t* src = J + (size_t)(l - 1) * N;
+        uint32_t* dst = J + (size_t)l * N;
+        for (uint32_t b = threadIdx.x; b < N; b += blockDim.x) dst[b] = src[src[b]];
+        __syncthreads();
+    }
+    const uint32_t b0 = first.i < stop ? (uint32_t)((first.i - C.a0) / C.BL) : nb;
+    for (uint32_t b = threadIdx.x; b < nb; b += blockDim.x) C.marked[b] = (b == b0);
+    __syncthreads();
+    for (int l = levels - 1; l >= 0; l--) {
+        const uint32_t* src = J + (size_t)l * N;
+        for (uint32_t b = threadIdx.x; b < nb; b += blockDim.x)
+            if (C.marked[b]) {
+                const uint32_t j = src[b];
+                if (j < nb) C.marked[j] = 1;
+            }
+        __syncthreads();
+    }
+    if (b0 == nb && threadIdx.x == 0) *slice_exit = first;     // nothing to parse in this slice
+    for (uint32_t b = threadIdx.x; b < nb; b += blockDim.x) {
+        if (b == b0) C.entry[b] = first;
+        if (C.marked[b]) {
+            const uint32_t j = J[b];
+            if (j < nb) C.entry[j] = C.exit_[b];
+            else *slice_exit = C.exit_[b];
+        }
+    }
+}
+
+__device__ __forceinline__ void set_bits(uint32_t* __restrict__ bm, uint64_t s, uint64_t e, unsigned lane) {   // [s, e), warp
+    if (s >= e) return;
+    const uint64_t w0 = s >> 5, w1 = (e - 1) >> 5;
+    for (uint64_t w = w0 + lane; w <= w1; w += 32) {
+        uint32_t m = 0xFFFFFFFFu;
+        if (w == w0) m &= 0xFFFFFFFFu << (s & 31);
+        if (w == w1) m &= 0xFFFFFFFFu >> (31 - ((e - 1) & 31));
+        if (w == w0 || w == w1) atomicOr(&bm[w], m);
+        else bm[w] = m;
+    }
+}
+
+// not-inserted bitmap of the slice from the traces of the blocks on the chain: a phrase step at i of length l leaves
+// (i, i+l) untouched, and i itself unless the table was probed there (greedy.cpp:111-117)
+__global__ void __launch_bounds__(128) notins_kernel(const parse_ctx C, uint32_t* __restrict__ bm, block_state first) {
+    const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const unsigned lane = threadIdx.x & 31;
+    if (b >= C.nb) return;
+    const uint64_t len = C.a1 - C.a0;
+    if (b == 0 && !first.gap && first.i > C.a0) set_bits(bm, 0, (first.i < C.a1 ? first.i : C.a1) - C.a0, lane);
+    if (!C.marked[b]) return;
+    const uint32_t cnt = C.tr_cnt[b];
+    const uint64_t slot0 = (uint64_t)b * C.BL;
+    for (uint32_t t = 0; t < cnt; t++) {
+        const uint32_t p = C.tr_pos[slot0 + t];
+        if (!(p & KIND_PHR)) continue;
+        const uint64_t s = (uint64_t)(p & POS_MASK) + ((p & KIND_PROBED) ? 1 : 0);
+        uint64_t e = (uint64_t)(p & POS_MASK) + C.tr_len[slot0 + t];
+        if (e > len) e = len;
+        set_bits(bm, s, e, lane);
+    }
+}
+
+__global__ void set_range_kernel(uint32_t* __restrict__ bm, uint64_t s, uint64_t e) { set_bits(bm, s, e, threadIdx.x & 31); }
+
+// carry the table over the slice: last inserted position per bucket
+__global__ void carry_kernel(const parse_ctx C, uint64_t E, uint32_t invalid_key, unsigned long long* __restrict__ Hc) {
+    const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= E) return;
+    const uint32_t key = C.skey[k];
+    if (key >= invalid_key) return;
+    const uint32_t q = C.sval[k] / 5u;
+    if (!not_inserted(C.notins, q)) atomicMax(&Hc[key], (unsigned long long)(C.a0 + q + 1));
+}
+
+__global__ void count_kernel(const parse_ctx C, uint32_t* __restrict__ cnt) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < C.nb) cnt[b] = C.marked[b] ? C.tr_cnt[b] : 0u;
+}
+
+__global__ void __launch_bounds__(128) gather_kernel(const parse_ctx C, const uint32_t* __restrict__ off,
+                                                     uint64_t* __restrict__ fsrc, uint64_t* __restrict__ flen) {
+    const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const unsigned lane = threadIdx.x & 31;
+    if (b >= C.nb || !C.marked[b]) return;
+    const uint32_t cnt = C.tr_cnt[b], o = off[b];
+    const uint64_t slot0 = (uint64_t)b * C.BL;
+    for (uint32_t t = lane; t < cnt; t += 32) {
+        fsrc[o + t] = C.tr_src[slot0 + t];
+        flen[o + t] = C.tr_len[slot0 + t];
+    }
+}
+
+__global__ void hquery_kernel(const unsigned long long* __restrict__ Hc, const uint32_t* __restrict__ buckets, uint32_t cnt,
+                              uint64_t* __restrict__ out) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < cnt) out[k] = Hc[buckets[k]];
+}
+
+u128 h_mod(u128 x) {
+    const u128 P = (((u128)1) << 107) - 1;
+    x = (x & P) + (x >> 107);
+    x = (x & P) + (x >> 107);
+    return x >= P ? x - P : x;
+}
+u128 h_mulmod(u128 a, u128 b) {
+    u128 r = 0;
+    a = h_mod(a);
+    while (b) {
+        if (b & 1) r = h_mod(r + a);
+        a = h_mod(a + a);
+        b >>= 1;
+    }
+    return r;
+}
+
+}  // namespace
+
+template <typename pos_t>
+void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, suffix_state<pos_t>& ss,
+                   lce_state<pos_t>& ls, const gap_hash_params& gp, uint64_t table_entries, const uint64_t* h_ml,
+                   uint64_t m, uint64_t n_cut, uint64_t slice_len, uint32_t block_len, gap_parse_scratch& sc,
+                   cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4]) {
+    static_assert(sizeof(block_state) == 32, "block_state layout");
+    if (slice_len > (1ull << 28)) slice_len = 1ull << 28;
+    if (block_len < 32) block_len = 32;
+    const lce_view<pos_t> V = make_lce_view<pos_t>(d_text, n, tau, d_S, s, ss, ls);
+    ghp5 hp;
+    {
+        const u128 P = (((u128)1) << 107) - 1;
+        for (int x = 0; x < 5; x++) {
+            hp.L[x] = gp.patt_len[x];
+            hp.base[x] = gp.base[x];
+            u128 pw = 1, b = gp.base[x];
+            uint64_t e = gp.patt_len[x];
+            while (e) {
+                if (e & 1) pw = h_mulmod(pw, b);
+                b = h_mulmod(b, b);
+                e >>= 1;
+            }
+            const u128 nb = pw == 0 ? 0 : P - pw;
+            hp.nb_lo[x] = (uint64_t)nb;
+            hp.nb_hi[x] = (uint64_t)(nb >> 64);
+        }
+        hp.mask = gp.mask;
+        hp.invalid_key = (uint32_t)table_entries;
+    }
+    int key_bits = 1;
+    while ((1ull << key_bits) <= table_entries) key_bits++;      // buckets 0..table_entries-1 and the invalid key
+    sc.rounds = 0;
+    sc.slices = 0;
+    sc.entries_sorted = 0;
+
+    sc.ml.reserve(3 * m);
+    CUDA_CHECK(cudaMemcpyAsync(sc.ml.get(), h_ml, 3 * m * 8, cudaMemcpyHostToDevice, st));
+    sc.Hc.reserve(table_entries);
+    CUDA_CHECK(cudaMemsetAsync(sc.Hc.get(), 0, table_entries * 8, st));
+    sc.changed.reserve(4);
+    sc.slice_exit.reserve(sizeof(block_state));
+
+    block_state first;
+    first.i = 0; first.cur = 0; first.k = 0; first.gap = 1; first.pad = 0;
+
+    for (uint64_t a0 = 0; a0 < n; a0 += slice_len) {
+        const uint64_t a1 = a0 + slice_len < n ? a0 + slice_len : n;
+        if (first.i >= a1 && !first.gap) continue;           // a phrase covers the whole slice: nothing is inserted
+        const uint64_t cnt = a1 - a0, E = 5 * cnt;
+        const uint32_t BL = block_len;
+        const uint32_t nb = (uint32_t)((cnt + BL - 1) / BL);
+        sc.slices++;
+        sc.entries_sorted += E;
+        // 1. hash + 2. sort
+        sc.k0.reserve(E); sc.k1.reserve(E); sc.v0.reserve(E); sc.v1.reserve(E); sc.inv.reserve(E);
+        uint32_t *keys = sc.k0, *kalt = sc.k1, *vals = sc.v0, *valt = sc.v1;
+        {
+            const uint64_t nthreads = ((cnt + RUN - 1) / RUN) * 5;
+            gap_entries_kernel<<<ceil_div_u(nthreads, 128), 128, 0, st>>>(d_text, n, hp, a0, cnt, keys, vals);
+            KERNEL_CHECK();
+        }
+        radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, sc.sort, st);
+        inv_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(vals, E, sc.inv);
+        KERNEL_CHECK();
+        // per-block state
+        const uint64_t nwords = (cnt + 31) / 32 + 1;
+        sc.notins.reserve(nwords);
+        sc.entry.reserve((uint64_t)nb * sizeof(block_state));
+        sc.exit_.reserve((uint64_t)nb * sizeof(block_state));
+        sc.marked.reserve(nb + 1);
+        sc.tr_cnt.reserve(nb);
+        sc.tr_pos.reserve((uint64_t)nb * BL);
+        sc.tr_src.reserve((uint64_t)nb * BL);
+        sc.tr_len.reserve((uint64_t)nb * BL);
+        int levels = 1;
+        while ((1ull << (levels - 1)) < (uint64_t)nb + 1) levels++;
+        sc.J.reserve((uint64_t)levels * (nb + 1));
+        sc.cnt.reserve(nb + 2);
+
+        parse_ctx C;
+        C.n = n; C.n_cut = n_cut; C.a0 = a0; C.a1 = a1; C.BL = BL; C.nb = nb;
+        C.skey = keys; C.sval = vals; C.inv = sc.inv;
+        C.Hc = reinterpret_cast<const uint64_t*>(sc.Hc.get());
+        C.notins = sc.notins;
+        C.ml_beg = sc.ml.get(); C.ml_end = sc.ml.get() + m; C.ml_src = sc.ml.get() + 2 * m; C.m = m;
+        C.entry = reinterpret_cast<block_state*>(sc.entry.get());
+        C.exit_ = reinterpret_cast<block_state*>(sc.exit_.get());
+        C.marked = sc.marked;
+        C.tr_cnt = sc.tr_cnt; C.tr_pos = sc.tr_pos; C.tr_src = sc.tr_src; C.tr_len = sc.tr_len;
+        C.changed = sc.changed;
+        block_state* d_exit = reinterpret_cast<block_state*>(sc.slice_exit.get());
+        const unsigned gw = ceil_div_u((uint64_t)nb * 32, 128);
+
+        const uint64_t stop = a1 < n_cut ? a1 : n_cut;
+        bool converged = false;
+        if (first.i < stop) {
+            // round 0: speculative entries
+            spec_entry_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, first);
+            KERNEL_CHECK();
+            CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
+            notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
+            KERNEL_CHECK();
+            parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
+            KERNEL_CHECK();
+            sc.rounds++;
+            for (uint64_t round = 1; round <= (uint64_t)nb + 4; round++) {
+                link_kernel<<<1, 1024, 0, st>>>(C, first, sc.J, levels, d_exit);
+                KERNEL_CHECK();
+                CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
+                notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
+                KERNEL_CHECK();
+                CUDA_CHECK(cudaMemsetAsync(sc.changed.get(), 0, 4, st));
+                parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
+                KERNEL_CHECK();
+                sc.rounds++;
+                uint32_t chg = 0;
+                CUDA_CHECK(cudaMemcpyAsync(&chg, sc.changed.get(), 4, cudaMemcpyDeviceToHost, st));
+                CUDA_CHECK(cudaStreamSynchronize(st));
+                if (!chg) { converged = true; break; }
+            }
+            if (!converged) throw std::runtime_error("gap_parse: the block chain did not reach its fixed point");
+            // factors of the blocks on the chain, in order
+            count_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, sc.cnt);
+            KERNEL_CHECK();
+            exclusive_scan_u32(sc.cnt, nb, sc.scan, st, sc.cnt.get() + nb);
+            uint32_t zs = 0;
+            CUDA_CHECK(cudaMemcpyAsync(&zs, sc.cnt.get() + nb, 4, cudaMemcpyDeviceToHost, st));
+            block_state ex;
+            CUDA_CHECK(cudaMemcpyAsync(&ex, d_exit, sizeof ex, cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            if (zs) {
+                sc.fsrc.reserve(zs); sc.flen.reserve(zs);
+                gather_kernel<<<gw, 128, 0, st>>>(C, sc.cnt, sc.fsrc, sc.flen);
+                KERNEL_CHECK();
+                const size_t z0 = out_src.size();
+                out_src.resize(z0 + zs);
+                out_len.resize(z0 + zs);
+                CUDA_CHECK(cudaMemcpyAsync(out_src.data() + z0, sc.fsrc.get(), (size_t)zs * 8, cudaMemcpyDeviceToHost, st));
+                CUDA_CHECK(cudaMemcpyAsync(out_len.data() + z0, sc.flen.get(), (size_t)zs * 8, cudaMemcpyDeviceToHost, st));
+                CUDA_CHECK(cudaStreamSynchronize(st));
+            }
+            // the bitmap of the last round is the final one (it was built from the converged traces);
+            // positions from the exit state on have not been reached yet
+            if (ex.i < a1) {
+                set_range_kernel<<<1, 32, 0, st>>>(sc.notins, ex.i - a0, cnt);
+                KERNEL_CHECK();
+            }
+            carry_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(C, E, hp.invalid_key, sc.Hc.get());
+            KERNEL_CHECK();
+            first = ex;
+        } else {
+            // nothing to parse here, but positions up to first.i may have been inserted by a gap factor
+            CUDA_CHECK(cudaMemsetAsync(sc.marked.get(), 0, nb + 1, st));
+            CUDA_CHECK(cudaMemsetAsync(sc.tr_cnt.get(), 0, (size_t)nb * 4, st));
+            CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
+            block_state f2 = first;
+            notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, f2);
+            KERNEL_CHECK();
+            // positions at and behind first.i are not inserted yet
+            if (first.i < a1) {
+                set_range_kernel<<<1, 32, 0, st>>>(sc.notins, (first.i > a0 ? first.i : a0) - a0, cnt);
+                KERNEL_CHECK();
+            }
+            carry_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(C, E, hp.invalid_key, sc.Hc.get());
+            KERNEL_CHECK();
+        }
+    }
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    handover[0] = first.i;
+    handover[1] = first.cur;
+    handover[2] = first.k;
+    handover[3] = first.gap;
+}
+
+void gap_parse_query(gap_parse_scratch& sc, const uint32_t* h_buckets, uint32_t cnt, uint64_t* h_out, cudaStream_t st) {
+    if (!cnt) return;
+    dbuf<uint32_t> db;
+    dbuf<uint64_t> dout;
+    db.reserve(cnt);
+    dout.reserve(cnt);
+    CUDA_CHECK(cudaMemcpyAsync(db.get(), h_buckets, (size_t)cnt * 4, cudaMemcpyHostToDevice, st));
+    hquery_kernel<<<ceil_div_u(cnt, 256), 256, 0, st>>>(sc.Hc.get(), db, cnt, dout);
+    KERNEL_CHECK();
+    CUDA_CHECK(cudaMemcpyAsync(h_out, dout.get(), (size_t)cnt * 8, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+}
+
+#define INST(pos_t)                                                                                                     \
+    template void gap_parse_run<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t, suffix_state<pos_t>&, \
+                                       lce_state<pos_t>&, const gap_hash_params&, uint64_t, const uint64_t*, uint64_t,  \
+                                       uint64_t, uint64_t, uint32_t, gap_parse_scratch&, cudaStream_t,                  \
+                                       std::vector<uint64_t>&, std::vector<uint64_t>&, uint64_t[4]);
+INST(uint32_t)
+INST(uint64_t)
+
+}  // namespace lz77sss

@@ -9,11 +9,12 @@
 #include "common.cuh"
 #include "device_utils.cuh"
 #include "stages.cuh"
+#include "lce_device.cuh"
 
 namespace lz77sss {
 namespace {
 
-constexpr int BLK = 32;
+constexpr int BLK = RMQ_BLK;
 
 template <typename val_t>
 __global__ void blkmin_kernel(const val_t* __restrict__ v, uint64_t s, val_t* __restrict__ tab, uint32_t nblk) {
@@ -37,33 +38,6 @@ __global__ void sparse_level_kernel(val_t* __restrict__ tab, uint32_t nblk, int 
     if (b + (1ull << l) > nblk) return;
     val_t x = tab[(uint64_t)(l - 1) * nblk + b], y = tab[(uint64_t)(l - 1) * nblk + b + half];
     tab[(uint64_t)l * nblk + b] = y < x ? y : x;
-}
-
-// min of the block minima over blocks [lo, hi] (inclusive, lo <= hi)
-template <typename val_t>
-__device__ __forceinline__ val_t blk_range_min(const val_t* __restrict__ tab, uint32_t nblk, uint64_t lo, uint64_t hi) {
-    const int l = 63 - __clzll((long long)(hi - lo + 1));
-    val_t x = tab[(uint64_t)l * nblk + lo], y = tab[(uint64_t)l * nblk + hi + 1 - (1ull << l)];
-    return y < x ? y : x;
-}
-
-// min v[lo..hi] (inclusive, lo <= hi)
-template <typename val_t>
-__device__ __forceinline__ val_t range_min(const val_t* __restrict__ v, const val_t* __restrict__ tab, uint32_t nblk,
-                                           uint64_t lo, uint64_t hi) {
-    const uint64_t bl = lo / BLK, bh = hi / BLK;
-    val_t m = v[lo];
-    if (bl == bh) {
-        for (uint64_t i = lo + 1; i <= hi; i++) m = v[i] < m ? v[i] : m;
-        return m;
-    }
-    for (uint64_t i = lo + 1; i < (bl + 1) * BLK; i++) m = v[i] < m ? v[i] : m;
-    for (uint64_t i = bh * BLK; i <= hi; i++) m = v[i] < m ? v[i] : m;
-    if (bl + 1 < bh) {
-        val_t x = blk_range_min(tab, nblk, bl + 1, bh - 1);
-        m = x < m ? x : m;
-    }
-    return m;
 }
 
 // largest r' < r with SA[r'] < v, or NONE32
@@ -196,45 +170,13 @@ __global__ void succ_first_kernel(const pos_t* __restrict__ S, uint64_t s, uint3
 
 // one warp per query; lce_sss::lce / lce_lr (patched lce_sss.hpp:102-177)
 template <typename pos_t>
-__global__ void __launch_bounds__(256) lce_r_kernel(const uint8_t* __restrict__ T, uint64_t n, uint32_t tau,
-                                                    const pos_t* __restrict__ S, uint64_t s,
-                                                    const uint32_t* __restrict__ ISA, const pos_t* __restrict__ LCP,
-                                                    const pos_t* __restrict__ lcp_tab, uint32_t nblk,
-                                                    const uint32_t* __restrict__ first, uint32_t shift, uint64_t nb,
-                                                    const uint64_t* __restrict__ qi, const uint64_t* __restrict__ qj,
-                                                    uint64_t nq, uint64_t* __restrict__ out) {
+__global__ void __launch_bounds__(256) lce_r_kernel(const lce_view<pos_t> V, const uint64_t* __restrict__ qi,
+                                                    const uint64_t* __restrict__ qj, uint64_t nq,
+                                                    uint64_t* __restrict__ out) {
     const uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned lane = threadIdx.x & 31;
     if (q >= nq) return;
-    const uint64_t i = qi[q], j = qj[q];
-    uint64_t res;
-    if (i == j) {
-        res = n - i;
-    } else {
-        const uint64_t l = min(i, j), r = max(i, j);
-        const uint64_t lce_max = n - r;
-        const uint64_t local_max = min((uint64_t)3 * tau, lce_max);
-        const uint64_t local = warp_lce(T, l, r, 0, local_max);
-        if (local < local_max || local == lce_max) {
-            res = local;
-        } else {
-            auto succ = [&](uint64_t x) -> uint64_t {
-                uint64_t b = x >> shift;
-                uint64_t idx = b < nb ? first[b] : s;
-                while (idx < s && (uint64_t)S[idx] < x) idx++;
-                return idx;
-            };
-            const uint64_t l_ = succ(l), r_ = succ(r);
-            const uint64_t dl = (uint64_t)S[l_] - l, dr = (uint64_t)S[r_] - r;
-            if (dl != dr) {
-                res = min(dl, dr) + 2 * (uint64_t)tau - 1;
-            } else {
-                uint64_t a = ISA[l_], b = ISA[r_];
-                if (a > b) { uint64_t t = a; a = b; b = t; }
-                res = dl + (uint64_t)range_min(LCP, lcp_tab, nblk, a + 1, b);
-            }
-        }
-    }
+    const uint64_t res = warp_lce_r(V, qi[q], qj[q]);
     if (lane == 0) out[q] = res;
 }
 
@@ -294,9 +236,7 @@ void lce_r_batch(const uint8_t* T, uint64_t n, uint32_t tau, const pos_t* S, uin
                  lce_state<pos_t>& ls, const uint64_t* d_qi, const uint64_t* d_qj, uint64_t nq, uint64_t* d_out,
                  cudaStream_t st) {
     if (nq == 0) return;
-    lce_r_kernel<pos_t><<<ceil_div_u(nq * 32, 256), 256, 0, st>>>(T, n, tau, S, s, ss.ISA, ss.LCP, ls.lcp_blkmin,
-                                                                  ls.nblk, ls.succ_first, ls.succ_shift, ls.succ_nb,
-                                                                  d_qi, d_qj, nq, d_out);
+    lce_r_kernel<pos_t><<<ceil_div_u(nq * 32, 256), 256, 0, st>>>(make_lce_view<pos_t>(T, n, tau, S, s, ss, ls), d_qi, d_qj, nq, d_out);
     KERNEL_CHECK();
 }
 

@@ -92,6 +92,26 @@ void gap_bucket_ids(const uint8_t* d_text, uint64_t n, const gap_hash_params& gp
                     const uint64_t* d_end, const uint64_t* d_off, uint64_t nranges, uint64_t total, uint32_t* d_out,
                     cudaStream_t st);
 
+// ---- gap_parse.cu: greedy phrase emission on the device ------------------------------------------------
+struct gap_parse_scratch {
+    dbuf<uint32_t> k0, k1, v0, v1, inv, notins, tr_cnt, tr_pos, changed, J, cnt;
+    dbuf<uint64_t> tr_src, tr_len, ml, fsrc, flen;
+    dbuf<unsigned long long> Hc;
+    dbuf<uint8_t> entry, exit_, marked, slice_exit;
+    sort_scratch sort;
+    scan_scratch scan;
+    uint64_t rounds = 0, slices = 0, entries_sorted = 0;
+};
+// h_ml: three planes (beg, end, src) of the merged phrase list incl. the sentinel {n, n+1, 0} (m entries).
+// Parses [0, n_cut); appends the factors to out_src/out_len; handover = {i, cur_pos, phrase index, gap flag}.
+template <typename pos_t>
+void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, suffix_state<pos_t>& ss,
+                   lce_state<pos_t>& ls, const gap_hash_params& gp, uint64_t table_entries, const uint64_t* h_ml,
+                   uint64_t m, uint64_t n_cut, uint64_t slice_len, uint32_t block_len, gap_parse_scratch& sc,
+                   cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4]);
+// table entries (last inserted position + 1, 0 = none) of the given buckets after gap_parse_run
+void gap_parse_query(gap_parse_scratch& sc, const uint32_t* h_buckets, uint32_t cnt, uint64_t* h_out, cudaStream_t st);
+
 // ---- decode.cu ------------------------------------------------------------------------------------
 // parallel LZ77 decode: factors (src,len) with len == 0 meaning literal src; returns 0 or an error code
 int decode_factors(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uint8_t* d_out, uint64_t n,

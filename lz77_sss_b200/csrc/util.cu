@@ -136,7 +136,8 @@ constexpr int RS_IPT = 8;
 constexpr int RS_TILE = RS_NT * RS_IPT;   // 2048 items; warp w owns items [w*256, w*256+256) of the tile
 constexpr int RS_NW = RS_NT / 32;
 
-__global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const uint64_t* __restrict__ keys, uint64_t n, int shift,
+template <typename K>
+__global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ keys, uint64_t n, int shift,
                                                         uint32_t mask, uint32_t* __restrict__ hist, uint32_t ntiles) {
     __shared__ uint32_t cnt[256];
     cnt[threadIdx.x] = 0;
@@ -151,9 +152,10 @@ __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const uint64_t* __restri
     hist[(uint64_t)threadIdx.x * ntiles + blockIdx.x] = cnt[threadIdx.x];
 }
 
-__global__ void __launch_bounds__(RS_NT) rs_scatter_kernel(const uint64_t* __restrict__ keys,
+template <typename K>
+__global__ void __launch_bounds__(RS_NT) rs_scatter_kernel(const K* __restrict__ keys,
                                                            const uint32_t* __restrict__ vals,
-                                                           uint64_t* __restrict__ okeys, uint32_t* __restrict__ ovals,
+                                                           K* __restrict__ okeys, uint32_t* __restrict__ ovals,
                                                            uint64_t n, int shift, uint32_t mask,
                                                            const uint32_t* __restrict__ offs, uint32_t ntiles) {
     __shared__ uint32_t cnt[RS_NW][256];
@@ -161,13 +163,13 @@ __global__ void __launch_bounds__(RS_NT) rs_scatter_kernel(const uint64_t* __res
     for (int i = threadIdx.x; i < RS_NW * 256; i += RS_NT) (&cnt[0][0])[i] = 0;
     __syncthreads();
     uint64_t base = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)w * (32 * RS_IPT);
-    uint64_t key[RS_IPT];
+    K key[RS_IPT];
     uint32_t val[RS_IPT], rank[RS_IPT], dig[RS_IPT];
 #pragma unroll
     for (int k = 0; k < RS_IPT; k++) {
         uint64_t i = base + (uint64_t)k * 32 + lane;
         bool valid = i < n;
-        key[k] = valid ? keys[i] : ~0ull;
+        key[k] = valid ? keys[i] : (K)~(K)0;
         val[k] = valid ? vals[i] : 0;
         uint32_t d = valid ? ((uint32_t)(key[k] >> shift) & mask) : 256u;   // 256 = "no item"
         dig[k] = d;
@@ -210,22 +212,32 @@ void exclusive_scan_u32(uint32_t* d, uint64_t n, scan_scratch& s, cudaStream_t s
     scan_rec(d, n, s.lvl1, s.lvl2, st, d_total);
 }
 
-void radix_sort_pairs(uint64_t*& keys, uint64_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
-                      int bit_hi, sort_scratch& s, cudaStream_t st) {
+template <typename K>
+void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
+                        int bit_hi, sort_scratch& s, cudaStream_t st) {
     if (n <= 1 || bit_hi <= bit_lo) return;
     uint32_t ntiles = ceil_div_u(n, RS_TILE);
     s.hist.reserve((uint64_t)256 * ntiles);
     for (int shift = bit_lo; shift < bit_hi; shift += 8) {
         int bits = bit_hi - shift < 8 ? bit_hi - shift : 8;
         uint32_t mask = (1u << bits) - 1;
-        rs_hist_kernel<<<ntiles, RS_NT, 0, st>>>(keys, n, shift, mask, s.hist, ntiles);
+        rs_hist_kernel<K><<<ntiles, RS_NT, 0, st>>>(keys, n, shift, mask, s.hist, ntiles);
         KERNEL_CHECK();
         exclusive_scan_u32(s.hist, (uint64_t)256 * ntiles, s.scan, st);
-        rs_scatter_kernel<<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.hist, ntiles);
+        rs_scatter_kernel<K><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.hist, ntiles);
         KERNEL_CHECK();
-        uint64_t* tk = keys; keys = kalt; kalt = tk;
+        K* tk = keys; keys = kalt; kalt = tk;
         uint32_t* tv = vals; vals = valt; valt = tv;
     }
+}
+
+void radix_sort_pairs(uint64_t*& keys, uint64_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
+                      int bit_hi, sort_scratch& s, cudaStream_t st) {
+    radix_sort_pairs_t<uint64_t>(keys, kalt, vals, valt, n, bit_lo, bit_hi, s, st);
+}
+void radix_sort_pairs32(uint32_t*& keys, uint32_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
+                        int bit_hi, sort_scratch& s, cudaStream_t st) {
+    radix_sort_pairs_t<uint32_t>(keys, kalt, vals, valt, n, bit_lo, bit_hi, s, st);
 }
 
 void fill_u32(uint32_t* d, uint64_t n, uint32_t v, cudaStream_t st) {
