@@ -33,59 +33,127 @@ namespace {
 __extension__ typedef unsigned __int128 u128;
 constexpr uint64_t NONE64 = ~0ull;
 constexpr uint32_t KIND_PHR = 1u << 30, KIND_PROBED = 1u << 31, POS_MASK = (1u << 30) - 1;
-constexpr int RUN = 64;   // positions per thread in the hash kernel
+
+// residues modulo the Mersenne prime P = 2^107 - 1 as (lo: 64 bits, hi: 43 bits)
+struct m107 {
+    uint64_t lo, hi;
+};
+constexpr uint64_t HI_MASK = (1ull << 43) - 1;
 
 struct ghp5 {
     uint64_t L[5];
     uint64_t base[5];
-    uint64_t nb_lo[5], nb_hi[5];   // -(base^L) mod P
     uint64_t mask;
     uint32_t invalid_key;          // table_entries (sorts behind every bucket)
+    const m107* nbtab;             // [5][256]: (-(base^L) * c) mod P for every character c
 };
 
-__device__ __forceinline__ u128 mers_mod107(u128 x) {
-    const u128 P = (((u128)1) << 107) - 1;
-    x = (x & P) + (x >> 107);
-    x = (x & P) + (x >> 107);
-    return x >= P ? x - P : x;
+// (hi : lo) with hi < 2^63  ->  value mod P
+__device__ __forceinline__ m107 fold107(uint64_t lo, uint64_t hi) {
+    uint64_t c = hi >> 43;        // x = c * 2^107 + rest == c + rest (mod P)
+    hi &= HI_MASK;
+    lo += c;
+    hi += lo < c;
+    if (hi >> 43) {               // at most one more wrap
+        hi &= HI_MASK;
+        lo += 1;
+        hi += lo == 0;
+    }
+    if (hi == HI_MASK && lo == ~0ull) { hi = 0; lo = 0; }   // x == P
+    m107 r;
+    r.lo = lo; r.hi = hi;
+    return r;
+}
+// (fp * base + add) mod P, base < 2^20, fp and add reduced
+__device__ __forceinline__ m107 muladd107(m107 fp, uint64_t base, m107 add) {
+    uint64_t lo = fp.lo * base;
+    uint64_t hi = fp.hi * base + __umul64hi(fp.lo, base);    // < 2^63 + 2^20
+    lo += add.lo;
+    hi += add.hi + (lo < add.lo);
+    return fold107(lo, hi);
 }
 
 // keys[5*rel + (4-x)] = bucket of the window of pattern x at position a0+rel (insertion order of the reference:
-// positions ascending, patterns 4..0), invalid_key where the reference does not hash (pos + L >= n);
-// vals[e] = e.
-__global__ void __launch_bounds__(128) gap_entries_kernel(const uint8_t* __restrict__ T, uint64_t n, const ghp5 hp,
+// positions ascending, patterns 4..0), invalid_key where the reference does not hash (pos + L >= n).
+// The same value goes to tkeys (kept in time order; keys is consumed by the sort) and vals[e] = e.
+// One CTA = 2048 positions: the text tile is staged in shared memory, warp x rolls pattern x (a lane owns 64
+// consecutive positions), the 5 x 2048 bucket ids are transposed through shared memory and leave coalesced.
+constexpr int GE_TILE = 2048, GE_SEG = 64, GE_HALO = 64;
+__device__ __forceinline__ int ge_txt(int p) { return p + ((p >> 6) << 2); }          // 68-byte pitch per 64-byte segment
+__device__ __forceinline__ int ge_out(int o) { return o + o / (5 * GE_SEG); }          // 321-word pitch per lane row
+__global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restrict__ T, uint64_t n, const ghp5 hp,
                                                           uint64_t a0, uint64_t cnt, uint32_t* __restrict__ keys,
-                                                          uint32_t* __restrict__ vals) {
-    const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const uint64_t nruns = (cnt + RUN - 1) / RUN;
-    if (g >= nruns * 5) return;
-    const int x = (int)(g / nruns);
-    const uint64_t r0 = (g % nruns) * RUN;
-    const uint64_t r1 = r0 + RUN < cnt ? r0 + RUN : cnt;
-    const uint64_t L = hp.L[x];
-    const u128 base = hp.base[x];
-    const u128 nb = ((u128)hp.nb_hi[x] << 64) | hp.nb_lo[x];
-    const uint64_t pos0 = a0 + r0;
-    u128 fp = 0;
-    if (pos0 + L < n)
-        for (uint64_t j = 0; j < L; j++) fp = mers_mod107(fp * base + T[pos0 + j]);
-    for (uint64_t r = r0; r < r1; r++) {
-        const uint64_t pos = a0 + r;
-        uint32_t key = hp.invalid_key;
-        if (pos + L < n) {
-            key = (uint32_t)((uint64_t)fp & hp.mask);
-            const u128 infl = mers_mod107(nb * (u128)T[pos] + T[pos + L]);   // pos + L < n
-            fp = mers_mod107(fp * base + infl);
+                                                          uint32_t* __restrict__ tkeys, uint32_t* __restrict__ vals) {
+    __shared__ __align__(16) uint8_t sT[(GE_TILE + GE_HALO) / 64 * 68 + 16];
+    __shared__ uint32_t sOut[5 * GE_TILE + GE_TILE / GE_SEG + 8];
+    const int tid = threadIdx.x, lane = tid & 31, x = tid >> 5;          // warp x <-> pattern x
+    const uint64_t t0 = (uint64_t)blockIdx.x * GE_TILE;                   // tile start, slice-relative
+    const uint64_t g0 = a0 + t0;                                          // text position of the tile
+    const uint32_t in_tile = cnt - t0 < (uint64_t)GE_TILE ? (uint32_t)(cnt - t0) : (uint32_t)GE_TILE;
+    // stage GE_TILE + GE_HALO text bytes (the device text is zero-padded behind n); g0 is 16-byte aligned
+    // whenever a0 is (slices start at multiples of the slice length); fall back to byte loads otherwise
+    if ((g0 & 15) == 0) {
+        const uint4* src = reinterpret_cast<const uint4*>(T + g0);
+        for (int v = tid; v < (GE_TILE + GE_HALO) / 16; v += 160) {
+            const uint4 q = src[v];
+            const int p = v * 16;                                         // 16 bytes never straddle a 64-byte segment
+            uint32_t* d = reinterpret_cast<uint32_t*>(sT + ge_txt(p));
+            d[0] = q.x; d[1] = q.y; d[2] = q.z; d[3] = q.w;
         }
-        const uint64_t e = 5 * r + (4 - x);
-        keys[e] = key;
-        vals[e] = (uint32_t)e;
+    } else {
+        for (int p = tid; p < GE_TILE + GE_HALO; p += 160) sT[ge_txt(p)] = T[g0 + p];
+    }
+    __syncthreads();
+    {
+        const uint64_t L = hp.L[x];
+        const uint64_t base = hp.base[x];
+        const m107* __restrict__ nbt = hp.nbtab + x * 256;
+        const int r0 = lane * GE_SEG;
+        const uint64_t pos0 = g0 + r0;
+        m107 fp;
+        fp.lo = fp.hi = 0;
+        if (pos0 + L < n)
+            for (int j = 0; j < (int)L; j++) {
+                m107 c;
+                c.lo = sT[ge_txt(r0 + j)]; c.hi = 0;
+                fp = muladd107(fp, base, c);
+            }
+        for (int j = 0; j < GE_SEG; j++) {
+            const int r = r0 + j;
+            const uint64_t pos = g0 + r;
+            uint32_t key = hp.invalid_key;
+            if (pos + L < n) {
+                key = (uint32_t)(fp.lo & hp.mask);
+                m107 infl = nbt[sT[ge_txt(r)]];                           // -(base^L) * T[pos]
+                const uint64_t in = sT[ge_txt(r + (int)L)];               // T[pos + L], pos + L < n
+                infl.lo += in;
+                infl.hi += infl.lo < in;
+                infl = fold107(infl.lo, infl.hi);
+                fp = muladd107(fp, base, infl);
+            }
+            sOut[ge_out(5 * r + (4 - x))] = key;
+        }
+    }
+    __syncthreads();
+    const uint64_t e0 = 5 * t0;
+    for (uint32_t o = tid; o < 5 * in_tile; o += 160) {
+        const uint32_t key = sOut[ge_out(o)];
+        keys[e0 + o] = key;
+        tkeys[e0 + o] = key;
+        vals[e0 + o] = (uint32_t)(e0 + o);
     }
 }
 
-__global__ void inv_kernel(const uint32_t* __restrict__ vals, uint64_t E, uint32_t* __restrict__ inv) {
+// bstart[b] = first sorted index whose key is >= b, for b in [0, nkeys]  (nkeys = table_entries + 1 keys incl. invalid)
+__global__ void bucket_start_kernel(const uint32_t* __restrict__ skey, uint64_t E, uint32_t nkeys,
+                                    uint32_t* __restrict__ bstart) {
     const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k < E) inv[vals[k]] = (uint32_t)k;
+    if (k >= E) return;
+    const uint32_t key = skey[k];
+    const int64_t prev = k ? (int64_t)skey[k - 1] : -1;
+    for (int64_t b = prev + 1; b <= (int64_t)key; b++) bstart[b] = (uint32_t)k;
+    if (k == E - 1)
+        for (uint32_t b = key + 1; b <= nkeys; b++) bstart[b] = (uint32_t)E;
 }
 
 struct block_state {
@@ -97,9 +165,9 @@ struct block_state {
 struct parse_ctx {
     uint64_t n, n_cut, a0, a1;
     uint32_t BL, nb;
-    const uint32_t* skey;
-    const uint32_t* sval;
-    const uint32_t* inv;
+    const uint32_t* tkey;      // bucket of every entry, time order
+    const uint32_t* sval;      // entries sorted by bucket, time order inside a bucket
+    const uint32_t* bstart;    // bucket b = sval[bstart[b] .. bstart[b+1])
     const uint64_t* Hc;        // last inserted position + 1 per bucket (0 = none), state before the slice
     const uint32_t* notins;    // bit = 1: position of the slice is NOT inserted
     const uint64_t* ml_beg;
@@ -128,12 +196,19 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
     const uint32_t rel = (uint32_t)(i - C.a0);
     uint64_t occ = NONE64;
     if (lane < 5) {
-        uint32_t kk = C.inv[5ull * rel + lane];
-        const uint32_t b = C.skey[kk];
+        const uint32_t e = 5u * rel + lane;
+        const uint32_t b = C.tkey[e];
+        const uint32_t lo = C.bstart[b];
+        uint32_t l = lo, h = C.bstart[b + 1];        // the own entry by binary search (entries ascend inside a bucket)
+        while (l + 1 < h) {
+            const uint32_t mid = (l + h) >> 1;
+            if (C.sval[mid] <= e) l = mid;
+            else h = mid;
+        }
+        uint32_t kk = l;
         while (true) {
-            if (kk == 0) { occ = C.Hc[b] - 1; break; }
+            if (kk == lo) { occ = C.Hc[b] - 1; break; }
             kk--;
-            if (C.skey[kk] != b) { occ = C.Hc[b] - 1; break; }
             const uint32_t q = C.sval[kk] / 5u;
             if (q == rel) { occ = i; break; }                     // an earlier pattern of this position wrote the bucket
             if (!not_inserted(C.notins, q)) { occ = C.a0 + q; break; }
@@ -336,14 +411,53 @@ __global__ void __launch_bounds__(128) notins_kernel(const parse_ctx C, uint32_t
 
 __global__ void set_range_kernel(uint32_t* __restrict__ bm, uint64_t s, uint64_t e) { set_bits(bm, s, e, threadIdx.x & 31); }
 
-// carry the table over the slice: last inserted position per bucket
-__global__ void carry_kernel(const parse_ctx C, uint64_t E, uint32_t invalid_key, unsigned long long* __restrict__ Hc) {
-    const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= E) return;
-    const uint32_t key = C.skey[k];
-    if (key >= invalid_key) return;
-    const uint32_t q = C.sval[k] / 5u;
-    if (!not_inserted(C.notins, q)) atomicMax(&Hc[key], (unsigned long long)(C.a0 + q + 1));
+// carry the table over the slice: last inserted position per bucket.  One thread per bucket walks its list
+// backwards; lists that do not settle within 64 entries are handed to a warp each (carry_big_kernel).
+__global__ void carry_kernel(const parse_ctx C, uint32_t nbuckets, unsigned long long* __restrict__ Hc,
+                             uint32_t* __restrict__ big, uint32_t* __restrict__ nbig) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nbuckets) return;
+    const uint32_t lo = C.bstart[b];
+    uint32_t kk = C.bstart[b + 1];
+    int steps = 0;
+    while (kk > lo) {
+        kk--;
+        const uint32_t q = C.sval[kk] / 5u;
+        if (!not_inserted(C.notins, q)) {
+            Hc[b] = C.a0 + q + 1;
+            return;
+        }
+        if (++steps == 64) {
+            big[atomicAdd(nbig, 1u)] = b;
+            return;
+        }
+    }
+}
+__global__ void __launch_bounds__(128) carry_big_kernel(const parse_ctx C, unsigned long long* __restrict__ Hc,
+                                                        const uint32_t* __restrict__ big, const uint32_t* __restrict__ nbig) {
+    const unsigned lane = threadIdx.x & 31;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t w = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5); w < *nbig; w += nwarps) {
+        const uint32_t b = big[w];
+        const uint32_t lo = C.bstart[b];
+        uint32_t hi = C.bstart[b + 1];
+        while (hi > lo) {
+            bool ins = false;
+            uint32_t q = 0;
+            if (hi - lo > lane) {                            // lane 0 looks at the last entry
+                q = C.sval[hi - 1 - lane] / 5u;
+                ins = !not_inserted(C.notins, q);
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, ins);
+            if (m) {
+                const uint32_t qq = __shfl_sync(0xffffffffu, q, __ffs(m) - 1);
+                if (lane == 0) Hc[b] = C.a0 + qq + 1;
+                break;
+            }
+            if (hi - lo <= 32) break;
+            hi -= 32;
+        }
+    }
 }
 
 __global__ void count_kernel(const parse_ctx C, uint32_t* __restrict__ cnt) {
@@ -399,6 +513,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
     if (block_len < 32) block_len = 32;
     const lce_view<pos_t> V = make_lce_view<pos_t>(d_text, n, tau, d_S, s, ss, ls);
     ghp5 hp;
+    std::vector<m107> h_nbtab(5 * 256);
     {
         const u128 P = (((u128)1) << 107) - 1;
         for (int x = 0; x < 5; x++) {
@@ -412,11 +527,18 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 e >>= 1;
             }
             const u128 nb = pw == 0 ? 0 : P - pw;
-            hp.nb_lo[x] = (uint64_t)nb;
-            hp.nb_hi[x] = (uint64_t)(nb >> 64);
+            for (int c = 0; c < 256; c++) {
+                const u128 v = h_mulmod(nb, (u128)c);
+                h_nbtab[x * 256 + c].lo = (uint64_t)v;
+                h_nbtab[x * 256 + c].hi = (uint64_t)(v >> 64);
+            }
         }
         hp.mask = gp.mask;
         hp.invalid_key = (uint32_t)table_entries;
+        sc.nbtab.reserve(5 * 256 * sizeof(m107));
+        CUDA_CHECK(cudaMemcpyAsync(sc.nbtab.get(), h_nbtab.data(), 5 * 256 * sizeof(m107), cudaMemcpyHostToDevice, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));     // h_nbtab is pageable
+        hp.nbtab = reinterpret_cast<const m107*>(sc.nbtab.get());
     }
     int key_bits = 1;
     while ((1ull << key_bits) <= table_entries) key_bits++;      // buckets 0..table_entries-1 and the invalid key
@@ -443,15 +565,16 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         sc.slices++;
         sc.entries_sorted += E;
         // 1. hash + 2. sort
-        sc.k0.reserve(E); sc.k1.reserve(E); sc.v0.reserve(E); sc.v1.reserve(E); sc.inv.reserve(E);
+        sc.k0.reserve(E); sc.k1.reserve(E); sc.v0.reserve(E); sc.v1.reserve(E); sc.tkey.reserve(E);
+        sc.bstart.reserve(table_entries + 4);
+        sc.big.reserve(table_entries + 4);
         uint32_t *keys = sc.k0, *kalt = sc.k1, *vals = sc.v0, *valt = sc.v1;
         {
-            const uint64_t nthreads = ((cnt + RUN - 1) / RUN) * 5;
-            gap_entries_kernel<<<ceil_div_u(nthreads, 128), 128, 0, st>>>(d_text, n, hp, a0, cnt, keys, vals);
+            gap_entries_kernel<<<ceil_div_u(cnt, GE_TILE), 160, 0, st>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, vals);
             KERNEL_CHECK();
         }
         radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, sc.sort, st);
-        inv_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(vals, E, sc.inv);
+        bucket_start_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
         KERNEL_CHECK();
         // per-block state
         const uint64_t nwords = (cnt + 31) / 32 + 1;
@@ -470,7 +593,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
 
         parse_ctx C;
         C.n = n; C.n_cut = n_cut; C.a0 = a0; C.a1 = a1; C.BL = BL; C.nb = nb;
-        C.skey = keys; C.sval = vals; C.inv = sc.inv;
+        C.tkey = sc.tkey; C.sval = vals; C.bstart = sc.bstart;
         C.Hc = reinterpret_cast<const uint64_t*>(sc.Hc.get());
         C.notins = sc.notins;
         C.ml_beg = sc.ml.get(); C.ml_end = sc.ml.get() + m; C.ml_src = sc.ml.get() + 2 * m; C.m = m;
@@ -536,7 +659,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 set_range_kernel<<<1, 32, 0, st>>>(sc.notins, ex.i - a0, cnt);
                 KERNEL_CHECK();
             }
-            carry_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(C, E, hp.invalid_key, sc.Hc.get());
+            CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 1, 0, 4, st));
+            carry_kernel<<<ceil_div_u(table_entries, 256), 256, 0, st>>>(C, (uint32_t)table_entries, sc.Hc.get(), sc.big, sc.changed.get() + 1);
+            KERNEL_CHECK();
+            carry_big_kernel<<<1184, 128, 0, st>>>(C, sc.Hc.get(), sc.big, sc.changed.get() + 1);
             KERNEL_CHECK();
             first = ex;
         } else {
@@ -552,7 +678,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 set_range_kernel<<<1, 32, 0, st>>>(sc.notins, (first.i > a0 ? first.i : a0) - a0, cnt);
                 KERNEL_CHECK();
             }
-            carry_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(C, E, hp.invalid_key, sc.Hc.get());
+            CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 1, 0, 4, st));
+            carry_kernel<<<ceil_div_u(table_entries, 256), 256, 0, st>>>(C, (uint32_t)table_entries, sc.Hc.get(), sc.big, sc.changed.get() + 1);
+            KERNEL_CHECK();
+            carry_big_kernel<<<1184, 128, 0, st>>>(C, sc.Hc.get(), sc.big, sc.changed.get() + 1);
             KERNEL_CHECK();
         }
     }

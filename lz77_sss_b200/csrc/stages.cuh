@@ -94,10 +94,10 @@ void gap_bucket_ids(const uint8_t* d_text, uint64_t n, const gap_hash_params& gp
 
 // ---- gap_parse.cu: greedy phrase emission on the device ------------------------------------------------
 struct gap_parse_scratch {
-    dbuf<uint32_t> k0, k1, v0, v1, inv, notins, tr_cnt, tr_pos, changed, J, cnt;
+    dbuf<uint32_t> k0, k1, v0, v1, tkey, bstart, big, notins, tr_cnt, tr_pos, changed, J, cnt;
     dbuf<uint64_t> tr_src, tr_len, ml, fsrc, flen;
     dbuf<unsigned long long> Hc;
-    dbuf<uint8_t> entry, exit_, marked, slice_exit;
+    dbuf<uint8_t> entry, exit_, marked, slice_exit, nbtab;
     sort_scratch sort;
     scan_scratch scan;
     uint64_t rounds = 0, slices = 0, entries_sorted = 0;

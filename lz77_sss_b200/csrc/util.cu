@@ -131,20 +131,23 @@ __global__ void iota_u32_kernel(uint32_t* d, uint64_t n) {
 }
 
 // ---------------- radix sort ----------------------------------------------------------------
+// One LSD pass = histogram per tile, device scan of hist[digit][tile], scatter.  The scatter ranks its tile
+// with per-warp match_any counting (stable), reorders the tile in shared memory by digit and writes every
+// digit's run with consecutive threads, so global stores are coalesced runs instead of single scattered words.
 constexpr int RS_NT = 256;
-constexpr int RS_IPT = 8;
-constexpr int RS_TILE = RS_NT * RS_IPT;   // 2048 items; warp w owns items [w*256, w*256+256) of the tile
 constexpr int RS_NW = RS_NT / 32;
+template <typename K> struct rs_cfg { static constexpr int IPT = sizeof(K) == 4 ? 16 : 8; };
 
 template <typename K>
 __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ keys, uint64_t n, int shift,
                                                         uint32_t mask, uint32_t* __restrict__ hist, uint32_t ntiles) {
+    constexpr int TILE = RS_NT * rs_cfg<K>::IPT;
     __shared__ uint32_t cnt[256];
     cnt[threadIdx.x] = 0;
     __syncthreads();
-    uint64_t base = (uint64_t)blockIdx.x * RS_TILE;
+    uint64_t base = (uint64_t)blockIdx.x * TILE;
 #pragma unroll
-    for (int k = 0; k < RS_IPT; k++) {
+    for (int k = 0; k < rs_cfg<K>::IPT; k++) {
         uint64_t i = base + (uint64_t)k * RS_NT + threadIdx.x;
         if (i < n) atomicAdd(&cnt[(uint32_t)(keys[i] >> shift) & mask], 1u);
     }
@@ -158,15 +161,24 @@ __global__ void __launch_bounds__(RS_NT) rs_scatter_kernel(const K* __restrict__
                                                            K* __restrict__ okeys, uint32_t* __restrict__ ovals,
                                                            uint64_t n, int shift, uint32_t mask,
                                                            const uint32_t* __restrict__ offs, uint32_t ntiles) {
+    constexpr int IPT = rs_cfg<K>::IPT;
+    constexpr int TILE = RS_NT * IPT;
     __shared__ uint32_t cnt[RS_NW][256];
+    __shared__ uint32_t dstart[256];      // tile-local start of every digit
+    __shared__ uint32_t goff[256];        // global offset of the tile's first item of every digit
+    __shared__ K skeys[TILE];
+    __shared__ uint32_t svals[TILE];
+    __shared__ uint32_t wsum[RS_NW];
     const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < RS_NW * 256; i += RS_NT) (&cnt[0][0])[i] = 0;
     __syncthreads();
-    uint64_t base = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)w * (32 * RS_IPT);
-    K key[RS_IPT];
-    uint32_t val[RS_IPT], rank[RS_IPT], dig[RS_IPT];
+    const uint64_t tbase = (uint64_t)blockIdx.x * TILE;
+    const uint64_t base = tbase + (uint64_t)w * (32 * IPT);
+    const uint32_t in_tile = n - tbase < (uint64_t)TILE ? (uint32_t)(n - tbase) : (uint32_t)TILE;
+    K key[IPT];
+    uint32_t val[IPT], rank[IPT], dig[IPT];
 #pragma unroll
-    for (int k = 0; k < RS_IPT; k++) {
+    for (int k = 0; k < IPT; k++) {
         uint64_t i = base + (uint64_t)k * 32 + lane;
         bool valid = i < n;
         key[k] = valid ? keys[i] : (K)~(K)0;
@@ -182,24 +194,46 @@ __global__ void __launch_bounds__(RS_NT) rs_scatter_kernel(const K* __restrict__
         rank[k] = old + __popc(peers & ((1u << lane) - 1));
     }
     __syncthreads();
-    {   // thread d: turn the per-warp counts of digit d into global output offsets
-        uint32_t d = threadIdx.x;
-        uint32_t acc = offs[(uint64_t)d * ntiles + blockIdx.x];
+    {   // thread d: per-warp counts of digit d -> exclusive offsets over the warps; digit total
+        const uint32_t d = threadIdx.x;
+        uint32_t acc = 0;
 #pragma unroll
         for (int ww = 0; ww < RS_NW; ww++) {
             uint32_t t = cnt[ww][d];
             cnt[ww][d] = acc;
             acc += t;
         }
+        // exclusive scan of the digit totals over the 256 threads
+        uint32_t inc = acc;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            uint32_t y = __shfl_up_sync(0xffffffffu, inc, s);
+            if (lane >= (unsigned)s) inc += y;
+        }
+        if (lane == 31) wsum[w] = inc;
+        __syncthreads();
+        uint32_t wb = 0;
+#pragma unroll
+        for (int ww = 0; ww < RS_NW; ww++) wb += ww < (int)w ? wsum[ww] : 0u;
+        dstart[d] = wb + inc - acc;
+        goff[d] = offs[(uint64_t)d * ntiles + blockIdx.x];
     }
     __syncthreads();
 #pragma unroll
-    for (int k = 0; k < RS_IPT; k++) {
+    for (int k = 0; k < IPT; k++) {
         if (dig[k] < 256u) {
-            uint32_t pos = cnt[w][dig[k]] + rank[k];
-            okeys[pos] = key[k];
-            ovals[pos] = val[k];
+            const uint32_t lp = dstart[dig[k]] + cnt[w][dig[k]] + rank[k];
+            skeys[lp] = key[k];
+            svals[lp] = val[k];
         }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < in_tile; i += RS_NT) {
+        const K kk = skeys[i];
+        const uint32_t d = (uint32_t)(kk >> shift) & mask;
+        const uint32_t pos = goff[d] + (i - dstart[d]);
+        okeys[pos] = kk;
+        ovals[pos] = svals[i];
     }
 }
 
@@ -216,7 +250,7 @@ template <typename K>
 void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
                         int bit_hi, sort_scratch& s, cudaStream_t st) {
     if (n <= 1 || bit_hi <= bit_lo) return;
-    uint32_t ntiles = ceil_div_u(n, RS_TILE);
+    uint32_t ntiles = ceil_div_u(n, RS_NT * rs_cfg<K>::IPT);
     s.hist.reserve((uint64_t)256 * ntiles);
     for (int shift = bit_lo; shift < bit_hi; shift += 8) {
         int bits = bit_hi - shift < 8 ? bit_hi - shift : 8;
