@@ -681,8 +681,10 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
         sparse_table H;
         for (size_t q = 0; q < buckets.size(); q++) H.H[buckets[q]] = vals[q] ? vals[q] - 1 : ~0ull;
         gap_index<sparse_table> idx(bp, H, n, g, 0);
-        idx.cur_pos = ho[1];                       // every window fitted at the last reinit: no zero flags
-        for (int x = 0; x < 5; x++) idx.zero[x] = false;
+        if (n_cut > 0) {                           // the device parsed up to n - 65: every window fitted at its last
+            idx.cur_pos = ho[1];                   // reinit, so no fingerprint is stuck at zero
+            for (int x = 0; x < 5; x++) idx.zero[x] = false;
+        }                                          // else (n <= 65): reinit(0) of the constructor set the flags
         z += greedy_emit_from(host_text, n, ML, g, idx, ho[0], (size_t)ho[2], emit, ctx);
         st.d2h_bytes += 20 * bp.hashed + 8 * buckets.size();
     }
