@@ -46,8 +46,8 @@ typedef struct lz77sss_config {
                                parameter and is independent of the number of GPUs.  0 -> 1 */
     uint32_t pos_bits;      /* 32 or 64: sizeof(pos_t)*8 of the replaced lz77_sss<pos_t> (gap table sizing,
                                rolling_hash_index_107.hpp:59-67); 0 -> 32 iff n <= UINT32_MAX (cli/lz77_sss_3_aprx.cpp:73) */
-    uint32_t phr_mode;      /* LZ77SSS_PHR_* ; only LPF_OPT is implemented so far */
-    uint32_t fact_mode;     /* LZ77SSS_FACT_* ; only GREEDY is implemented so far */
+    uint32_t phr_mode;      /* LZ77SSS_PHR_* (all four phrase modes) */
+    uint32_t fact_mode;     /* LZ77SSS_FACT_* (all three; skip_phrases emits the gapped stream of skip_gaps.cpp:34-61) */
     uint32_t sss_base;      /* multiplier of the window fingerprint of the synchronizing set; 0 -> 0x9E3779B1 */
     uint32_t sss_qmax;      /* period bound cap of the low-period set Q; 0xFFFFFFFF -> 32 */
     uint64_t gap_bases[5];  /* bases of the five rk_prime<107> of the gap index (rolling_hash_index_107.hpp:72-75),

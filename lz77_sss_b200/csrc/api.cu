@@ -78,6 +78,8 @@ struct lz77sss_handle {
     lz77sss_config cfg;
     cudaStream_t st = nullptr;
     dbuf<uint8_t> text_buf;           // FRONT_PAD + n + TEXT_PAD
+    dbuf<uint8_t> rev_buf;            // the reversed text of the lpf_lnf phrase modes, same padding
+    dbuf<uint64_t> d_lq;              // leftward-LCE queries (qi, qj, out)
     const uint8_t* d_text = nullptr;  // text of the last factorization (device)
     uint64_t n = 0;
     int pos_bytes = 0;                // internal position width of the last factorization
@@ -191,6 +193,144 @@ void lpf_chain(lz77sss_handle* h, pipeline<pos_t>& P) {
             }
         }
     }
+}
+
+// host side of build_LPF_naive (lpf_naive.cpp:33-122): the longer of the two candidates without left extension,
+// then skip the synchronizing positions the phrase covers
+template <typename pos_t>
+void lpf_chain_naive(lz77sss_handle* h, pipeline<pos_t>& P) {
+    const uint64_t n = h->n, s = P.s;
+    const uint32_t p = h->cfg.num_threads;
+    h->LPF.assign(p, {});
+    const pos_t* S = P.hS.p;
+    for (uint32_t i_p = 0; i_p < p; i_p++) {
+        const uint64_t b = (uint64_t)i_p * (n / p);
+        const uint64_t e = i_p == p - 1 ? n : (uint64_t)(i_p + 1) * (n / p);
+        const uint64_t i_min = std::lower_bound(S, S + s, (pos_t)b) - S;
+        const uint64_t i_max = std::lower_bound(S, S + s, (pos_t)e) - S;
+        auto& out = h->LPF[i_p];
+        // the reference's loop header increments i once more after the skip loop below (lpf_naive.cpp:58,106-110):
+        // the synchronizing position right behind every visited one is never visited
+        for (uint64_t i = i_min; i < i_max; i++) {
+            uint64_t src = 0, len = 0;
+            if (P.h_pidx[i] != NONE32 && (uint64_t)P.h_plce[i] > len) { src = S[P.h_pidx[i]]; len = P.h_plce[i]; }
+            if (P.h_nidx[i] != NONE32 && (uint64_t)P.h_nlce[i] > len) { src = S[P.h_nidx[i]]; len = P.h_nlce[i]; }
+            const uint64_t pos = S[i];
+            if (len > 0) out.push_back(lpf_t{pos, pos + len, src});
+            do { i++; } while (i < i_max && (uint64_t)S[i] < pos + len);
+        }
+    }
+}
+
+// host side of build_LPF_all / build_LNF_all (lpf_lnf.cpp:34-134,139-249) over the device candidates of one text
+// direction.  A candidate is dropped when it starts inside the last kept phrase of its kind and has the same
+// offset; that rule needs only LCE_R and the offset, so it runs first, and the uncapped left extensions
+// (lpf_lnf_opt) are then fetched for the survivors in one batch.
+constexpr uint64_t LNF_LCAP = 64;     // left extension computed with the candidates; longer ones go to the batch
+template <typename pos_t>
+void all_chain(lz77sss_handle* h, pipeline<pos_t>& P, const uint8_t* d_text, bool lnf, bool opt) {
+    const uint64_t n = h->n, s = P.s;
+    const uint32_t p = h->cfg.num_threads;
+    const pos_t* S = P.hS.p;
+    struct pending { uint32_t i_p; size_t slot; };
+    std::vector<pending> pend;
+    std::vector<uint64_t> q;          // qi plane, then qj plane
+    std::vector<size_t> first_new(p);
+    for (uint32_t i_p = 0; i_p < p; i_p++) {
+        uint64_t b, e;
+        if (lnf) {
+            b = i_p == p - 1 ? 0 : n - (uint64_t)(i_p + 1) * (n / p);
+            e = n - (uint64_t)i_p * (n / p);
+        } else {
+            b = (uint64_t)i_p * (n / p);
+            e = i_p == p - 1 ? n : (uint64_t)(i_p + 1) * (n / p);
+        }
+        const uint64_t i_min = std::lower_bound(S, S + s, (pos_t)b) - S;
+        const uint64_t i_max = e > (uint64_t)std::numeric_limits<pos_t>::max() ? s : std::lower_bound(S, S + s, (pos_t)e) - S;
+        auto& out = h->LPF[i_p];
+        first_new[i_p] = out.size();
+        uint64_t lst_end[2] = {n, n}, lst_off[2] = {0, 0};
+        for (uint64_t i = i_min; i < i_max; i++) {
+            for (int side = 0; side < 2; side++) {
+                const uint32_t idx = side == 0 ? P.h_pidx[i] : P.h_nidx[i];
+                if (idx == NONE32) continue;
+                const uint64_t pos = S[i], src = S[idx];
+                const uint64_t off = lnf ? src - pos : pos - src;
+                if (pos < lst_end[side] && off == lst_off[side]) continue;
+                const uint64_t lce = side == 0 ? P.h_plce[i] : P.h_nlce[i];
+                const uint64_t end = pos + lce;
+                uint64_t l = 0;
+                bool full = false;
+                if (opt && src != 0 && pos != 0) {
+                    l = side == 0 ? P.h_plcel[i] : P.h_nlcel[i];
+                    full = l == LNF_LCAP && std::min(src, pos) > LNF_LCAP;
+                }
+                if (end - (pos - l) > 1) {
+                    lst_end[side] = end;
+                    lst_off[side] = off;
+                    if (full) {
+                        pend.push_back({i_p, out.size()});
+                        q.push_back(std::min(src, pos) - 1);
+                        q.push_back(std::max(src, pos) - 1);
+                    }
+                    out.push_back(lpf_t{pos - l, end, src - l});
+                }
+            }
+        }
+    }
+    if (!pend.empty()) {
+        const uint64_t nq = pend.size();
+        std::vector<uint64_t> planes(2 * nq), res(nq);
+        for (uint64_t k = 0; k < nq; k++) { planes[k] = q[2 * k]; planes[nq + k] = q[2 * k + 1]; }
+        h->d_lq.reserve(3 * nq);
+        CUDA_CHECK(cudaMemcpyAsync(h->d_lq.get(), planes.data(), 2 * nq * 8, cudaMemcpyHostToDevice, h->st));
+        left_lce_batch(d_text, h->d_lq.get(), h->d_lq.get() + nq, nq, h->d_lq.get() + 2 * nq, h->st);
+        CUDA_CHECK(cudaMemcpyAsync(res.data(), h->d_lq.get() + 2 * nq, nq * 8, cudaMemcpyDeviceToHost, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        h->stats.h2d_bytes += 16 * nq;
+        h->stats.d2h_bytes += 8 * nq;
+        for (uint64_t k = 0; k < nq; k++) {
+            lpf_t& ph = h->LPF[pend[k].i_p][pend[k].slot];
+            const uint64_t more = res[k] - LNF_LCAP;       // the first LNF_LCAP characters are already in
+            ph.beg -= more;
+            ph.src -= more;
+        }
+    }
+    if (lnf)                                               // back to positions of the forward text
+        for (uint32_t i_p = 0; i_p < p; i_p++) {
+            auto& out = h->LPF[i_p];
+            for (size_t k = first_new[i_p]; k < out.size(); k++) {
+                const lpf_t r = out[k];
+                out[k] = lpf_t{n - r.end, n - r.beg, n - (r.src + (r.end - r.beg))};
+            }
+        }
+}
+
+// greedy_phrase_selection (approximate/common.cpp:33-96): phrases ordered by (beg ascending, end descending; ties in
+// insertion order, see oracle/shim/ips4o.hpp), then a chain of phrases that each reach furthest among those
+// starting inside (or right behind) the current one; an overlapped phrase is cut at the start of its successor.
+void select_phrases(std::vector<lpf_t>& P) {
+    if (P.empty()) return;
+    std::stable_sort(P.begin(), P.end(), [](const lpf_t& a, const lpf_t& b) {
+        return a.beg < b.beg || (a.beg == b.beg && a.end > b.end);
+    });
+    const size_t cnt = P.size();
+    size_t k = 0, i = 1;
+    while (i < cnt && P[i].end < P[k].end) i++;
+    while (i < cnt) {
+        size_t x = cnt;
+        if (i + 1 < cnt) {
+            for (x = i + 1; x < cnt && P[x].beg <= P[k].end; x++)
+                if (P[x].end > P[i].end) i = x;
+            if (P[i].end <= P[k].end) i = x;
+        }
+        if (i == cnt) break;
+        if (P[i].beg < P[k].end) P[k].end = P[i].beg;
+        if (P[k].end > P[k].beg) k++;
+        P[k] = P[i];
+        i = x;
+    }
+    P.resize(k + 1);
 }
 
 // get_phrase_info (approximate/common.cpp:100-157)
@@ -520,6 +660,84 @@ uint64_t greedy_emit_from(const uint8_t* T, uint64_t n, const std::vector<lpf_t>
     return num_fact;
 }
 
+// factorize_greedy_naive (greedy_naive.cpp:34-113) from the state (i, idx.cur_pos, k): ML[k] is the next phrase
+// (ML[k].beg >= i).  Every position is inserted before the table is probed behind it.
+template <typename table_t>
+uint64_t greedy_naive_emit_from(const uint8_t* T, uint64_t n, const std::vector<lpf_t>& ML, gap_index<table_t>& idx,
+                                uint64_t i, size_t k, lz77sss_emit_fn emit, void* ctx) {
+    uint64_t num_fact = 0;
+    const size_t last = ML.size() - 1;
+    auto longest_prev_occ = [&](uint64_t pos, uint64_t& f_src, uint64_t& f_len) {
+        f_src = T[pos];
+        f_len = 0;
+        for (int x = 4; x >= 0; x--) {
+            if (f_len == 0) {
+                const uint64_t src = idx.advance_and_get_occ(x);
+                if (src < pos && T[src] == T[pos]) {
+                    f_len = host_lce(T, n, src, pos);
+                    f_src = src;
+                }
+            } else {
+                idx.advance_i(x);
+            }
+        }
+        idx.cur_pos++;
+    };
+    lpf_t ph = ML[k];
+    while (true) {
+        const uint64_t gap_end = ph.beg;
+        if (i < gap_end) {
+            while (idx.cur_pos < i) idx.advance();
+            do {
+                uint64_t fs, fl;
+                longest_prev_occ(i, fs, fl);
+                fl = std::min<uint64_t>(fl, gap_end - i);
+                emit(ctx, fs, fl);
+                num_fact++;
+                i += std::max<uint64_t>(1, fl);
+                while (idx.cur_pos < i) idx.advance();
+            } while (i < gap_end);
+        }
+        if (gap_end == n) break;
+        uint64_t ls = ph.src, ll = ph.end - ph.beg;
+        if (k < last) k++;
+        const lpf_t nxt = ML[k];
+        if (idx.cur_pos == gap_end) {
+            uint64_t fs, fl;
+            longest_prev_occ(gap_end, fs, fl);
+            fl = std::min<uint64_t>(fl, nxt.beg - gap_end);
+            if (fl > ll) { ls = fs; ll = fl; }
+        }
+        emit(ctx, ls, ll);
+        num_fact++;
+        i += ll;
+        ph = nxt;
+    }
+    return num_fact;
+}
+
+// factorize_skip_gaps (skip_gaps.cpp:34-61): the phrases and the lengths of the gaps between them
+uint64_t skip_gaps_emit(uint64_t n, const std::vector<lpf_t>& ML, lz77sss_emit_fn emit, void* ctx) {
+    uint64_t num = 0;
+    size_t k = 0;
+    const size_t last = ML.size() - 1;
+    lpf_t nxt = ML[0];
+    emit(ctx, nxt.beg, 0);
+    num++;
+    while (nxt.beg < n) {
+        const lpf_t phr = nxt;
+        if (k < last) k++;
+        nxt = ML[k];
+        emit(ctx, phr.src, phr.end - phr.beg);
+        num++;
+        if (nxt.beg > phr.end) {
+            emit(ctx, nxt.beg - phr.end, 0);
+            num++;
+        }
+    }
+    return num;
+}
+
 template <typename pos_t>
 int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n,
                    lz77sss_emit_fn emit, void* ctx) {
@@ -532,67 +750,104 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     h->pos_bytes = sizeof(pos_t);
     st.n = n;
 
-    // K1+K2
-    auto t0 = clk::now();
-    uint64_t s_cap = n / 2 + 1024;                 // |S| <= number of candidate positions; typical 2n/tau
-    if (tau >= 16) s_cap = std::min<uint64_t>(n, 8 * (n / tau) + 65536);
-    P.S.reserve(s_cap);
-    uint64_t size_s = 0, numq = 0;
-    sss_build(d_text, n, tau, h->cfg.sss_base, h->cfg.sss_qmax, P.S.get(), sizeof(pos_t), s_cap, P.sss, s, &size_s, &numq);
-    if (size_s > s_cap) {                          // rare: denser than expected, redo with the exact size
-        s_cap = size_s;
+    // build_lce (algorithms/common.cpp:58-80) on one direction of the text, the candidates of the phrase mode, and
+    // their copy to the host
+    uint64_t size_s = 0;
+    auto build_and_fetch = [&](const uint8_t* text_x, int cand_mode /* 0 lpf_opt/naive, 1 LPF_all, 2 LNF_all */) {
+        // K1+K2
+        auto t0 = clk::now();
+        uint64_t s_cap = n / 2 + 1024;                 // |S| <= number of candidate positions; typical 2n/tau
+        if (tau >= 16) s_cap = std::min<uint64_t>(n, 8 * (n / tau) + 65536);
         P.S.reserve(s_cap);
-        sss_build(d_text, n, tau, h->cfg.sss_base, h->cfg.sss_qmax, P.S.get(), sizeof(pos_t), s_cap, P.sss, s, &size_s, &numq);
-    }
-    P.s = size_s;
-    st.size_sss = size_s;
-    st.num_q = numq;
-    st.t_sss_ns = ns_since(t0);
+        uint64_t numq = 0;
+        sss_build(text_x, n, tau, h->cfg.sss_base, h->cfg.sss_qmax, P.S.get(), sizeof(pos_t), s_cap, P.sss, s, &size_s, &numq);
+        if (size_s > s_cap) {                          // rare: denser than expected, redo with the exact size
+            s_cap = size_s;
+            P.S.reserve(s_cap);
+            sss_build(text_x, n, tau, h->cfg.sss_base, h->cfg.sss_qmax, P.S.get(), sizeof(pos_t), s_cap, P.sss, s, &size_s, &numq);
+        }
+        P.s = size_s;
+        st.size_sss = size_s;
+        st.num_q = numq;
+        st.t_sss_ns += ns_since(t0);
 
-    // K3
-    t0 = clk::now();
-    suffix_sort_sync<pos_t>(d_text, n, tau, h->cfg.sss_qmax, P.S.get(), size_s, P.suf, s);
-    CUDA_CHECK(cudaStreamSynchronize(s));
-    st.ctx_levels = P.suf.ctx_levels;
-    st.doubling_rounds = P.suf.doubling_rounds;
-    st.t_sort_ns = ns_since(t0);
-
-    // range-min / nearest-smaller / successor structures, LPF candidates
-    t0 = clk::now();
-    build_lce_structures<pos_t>(d_text, n, tau, P.S.get(), size_s, P.suf, P.lce, s);
-    CUDA_CHECK(cudaStreamSynchronize(s));
-    st.t_lce_ns = ns_since(t0);
-    t0 = clk::now();
-    lpf_candidates<pos_t>(d_text, n, tau, P.S.get(), size_s, h->cfg.num_threads, P.suf, P.lce, s);
-    CUDA_CHECK(cudaStreamSynchronize(s));
-    st.t_lpf_ns = ns_since(t0);
-
-    // candidates to the host
-    t0 = clk::now();
-    if (size_s) {
-        P.hS.reserve(size_s); P.h_pidx.reserve(size_s); P.h_nidx.reserve(size_s);
-        P.h_plce.reserve(size_s); P.h_nlce.reserve(size_s); P.h_plcel.reserve(size_s); P.h_nlcel.reserve(size_s);
-        CUDA_CHECK(cudaMemcpyAsync(P.hS.p, P.S.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
-        CUDA_CHECK(cudaMemcpyAsync(P.h_pidx.p, P.lce.psv_idx.get(), size_s * 4, cudaMemcpyDeviceToHost, s));
-        CUDA_CHECK(cudaMemcpyAsync(P.h_nidx.p, P.lce.nsv_idx.get(), size_s * 4, cudaMemcpyDeviceToHost, s));
-        CUDA_CHECK(cudaMemcpyAsync(P.h_plce.p, P.lce.psv_lce.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
-        CUDA_CHECK(cudaMemcpyAsync(P.h_nlce.p, P.lce.nsv_lce.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
-        CUDA_CHECK(cudaMemcpyAsync(P.h_plcel.p, P.lce.psv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
-        CUDA_CHECK(cudaMemcpyAsync(P.h_nlcel.p, P.lce.nsv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+        // K3
+        t0 = clk::now();
+        suffix_sort_sync<pos_t>(text_x, n, tau, h->cfg.sss_qmax, P.S.get(), size_s, P.suf, s);
         CUDA_CHECK(cudaStreamSynchronize(s));
-        st.d2h_bytes += size_s * (8 + 5 * sizeof(pos_t));
+        st.ctx_levels = P.suf.ctx_levels;
+        st.doubling_rounds = P.suf.doubling_rounds;
+        st.t_sort_ns += ns_since(t0);
+
+        // range-min / nearest-smaller / successor structures, LPF candidates
+        t0 = clk::now();
+        build_lce_structures<pos_t>(text_x, n, tau, P.S.get(), size_s, P.suf, P.lce, s);
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        st.t_lce_ns += ns_since(t0);
+        t0 = clk::now();
+        if (cand_mode == 0) lpf_candidates<pos_t>(text_x, n, tau, P.S.get(), size_s, h->cfg.num_threads, P.suf, P.lce, s);
+        else all_candidates<pos_t>(text_x, n, P.S.get(), size_s, cand_mode == 2,
+                                   h->cfg.phr_mode == LZ77SSS_PHR_LPF_LNF_OPT ? LNF_LCAP : 0, P.suf, P.lce, s);
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        st.t_lpf_ns += ns_since(t0);
+
+        // candidates to the host
+        t0 = clk::now();
+        if (size_s) {
+            P.hS.reserve(size_s); P.h_pidx.reserve(size_s); P.h_nidx.reserve(size_s);
+            P.h_plce.reserve(size_s); P.h_nlce.reserve(size_s); P.h_plcel.reserve(size_s); P.h_nlcel.reserve(size_s);
+            CUDA_CHECK(cudaMemcpyAsync(P.hS.p, P.S.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(P.h_pidx.p, P.lce.psv_idx.get(), size_s * 4, cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(P.h_nidx.p, P.lce.nsv_idx.get(), size_s * 4, cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(P.h_plce.p, P.lce.psv_lce.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(P.h_nlce.p, P.lce.nsv_lce.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(P.h_plcel.p, P.lce.psv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(P.h_nlcel.p, P.lce.nsv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaStreamSynchronize(s));
+            st.d2h_bytes += size_s * (8 + 5 * sizeof(pos_t));
+        }
+        st.t_d2h_ns += ns_since(t0);
+    };
+    const bool lnf_mode = h->cfg.phr_mode == LZ77SSS_PHR_LPF_LNF_NAIVE || h->cfg.phr_mode == LZ77SSS_PHR_LPF_LNF_OPT;
+    const bool opt_mode = h->cfg.phr_mode == LZ77SSS_PHR_LPF_LNF_OPT;
+    auto t0 = clk::now();
+    if (lnf_mode) {
+        // compute_approximation, lz77_sss.hpp:384-394: LNF phrases from the reversed text, then LPF phrases
+        h->LPF.assign(h->cfg.num_threads, {});
+        uint8_t* d_rev = alloc_text(h->rev_buf, n, s);
+        reverse_text(d_text, d_rev, n, s);
+        build_and_fetch(d_rev, 2);
+        t0 = clk::now();
+        all_chain<pos_t>(h, P, d_rev, true, opt_mode);
+        st.t_chain_ns += ns_since(t0);
+        build_and_fetch(d_text, 1);
+        t0 = clk::now();
+        all_chain<pos_t>(h, P, d_text, false, opt_mode);
+        for (auto& V : h->LPF) select_phrases(V);
+        st.t_chain_ns += ns_since(t0);
+    } else {
+        build_and_fetch(d_text, 0);
     }
-    st.t_d2h_ns = ns_since(t0);
 
     // coverage chain, statistics, gap parameters (host scalars)
     t0 = clk::now();
-    lpf_chain<pos_t>(h, P);
+    const bool naive = h->cfg.fact_mode == LZ77SSS_FACT_GREEDY_NAIVE;
+    if (h->cfg.phr_mode == LZ77SSS_PHR_LPF_NAIVE) lpf_chain_naive<pos_t>(h, P);
+    else if (!lnf_mode) lpf_chain<pos_t>(h, P);
+    if (h->cfg.fact_mode == LZ77SSS_FACT_SKIP_PHRASES) {   // no statistics, no gap index (lz77_sss.hpp:417-418)
+        st.t_chain_ns += ns_since(t0);
+        h->have_result = true;
+        t0 = clk::now();
+        st.num_factors = skip_gaps_emit(n, merged_phrase_list(h), emit, ctx);
+        st.t_emit_ns = ns_since(t0);
+        return LZ77SSS_OK;
+    }
     phrase_info(h);
     gap_params g = choose_gap_params(h);
     for (int x = 0; x < 5; x++) st.patt_lens[x] = g.patt_lens[x];
     st.roll_threshold = g.roll_threshold;
     st.table_entries = g.table_entries;
-    st.t_chain_ns = ns_since(t0);
+    st.t_chain_ns += ns_since(t0);
     h->have_result = true;
     if (g.patt_lens[0] == 0) return fail(LZ77SSS_E_UNSUPPORTED, "degenerate phrase statistics (no LPF phrase or no gap): pattern lengths undefined in the reference (SURVEY.md A7)");
 
@@ -625,11 +880,13 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
         if (h->cfg.pos_bits == 32) {
             dense_table<uint32_t> H(g.table_entries);
             gap_index<dense_table<uint32_t>> idx(bp, H, n, g, 0);
-            z = greedy_emit_from(host_text, n, ML, g, idx, 0, 0, emit, ctx);
+            z = naive ? greedy_naive_emit_from(host_text, n, ML, idx, 0, 0, emit, ctx)
+                      : greedy_emit_from(host_text, n, ML, g, idx, 0, 0, emit, ctx);
         } else {
             dense_table<uint64_t> H(g.table_entries);
             gap_index<dense_table<uint64_t>> idx(bp, H, n, g, 0);
-            z = greedy_emit_from(host_text, n, ML, g, idx, 0, 0, emit, ctx);
+            z = naive ? greedy_naive_emit_from(host_text, n, ML, idx, 0, 0, emit, ctx)
+                      : greedy_emit_from(host_text, n, ML, g, idx, 0, 0, emit, ctx);
         }
         st.num_factors = z;
         st.gap_positions_hashed = bp.hashed;
@@ -652,7 +909,7 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     uint64_t ho[4];
     gap_hash_params gpar = bp.gp;
     gap_parse_run<pos_t>(d_text, n, tau, P.S.get(), size_s, P.suf, P.lce, gpar, g.table_entries, h_ml.data(), ML.size(), n_cut,
-                         h->slice_len, h->block_len, h->gp, s, h->f_src, h->f_len, ho);
+                         h->slice_len, h->block_len, h->gp, s, h->f_src, h->f_len, ho, naive);
     st.h2d_bytes += 24 * ML.size();
     st.d2h_bytes += 16 * h->f_src.size();
     st.gap_positions_hashed = h->gp.entries_sorted / 5;
@@ -665,7 +922,8 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     for (uint64_t q = 0; q < z; q++) emit(ctx, h->f_src[q], h->f_len[q]);
     if (ho[0] < n) {
         // tail: table entries of every bucket the remaining positions can touch
-        const uint64_t tb = n > 65 ? n - 65 : 0;
+        // (greedy_naive: the host re-inserts position n_cut - 1, so that "table cursor == i" keeps its meaning)
+        const uint64_t tb = n_cut - (naive && n_cut > 0 ? 1 : 0);
         bp.beg.push_back(tb);
         bp.end.push_back(n);
         bp.fetch_main();
@@ -684,8 +942,11 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
         if (n_cut > 0) {                           // the device parsed up to n - 65: every window fitted at its last
             idx.cur_pos = ho[1];                   // reinit, so no fingerprint is stuck at zero
             for (int x = 0; x < 5; x++) idx.zero[x] = false;
+            // greedy_naive: the device table already holds every position below n_cut
+            if (naive && ho[1] != ho[0]) idx.cur_pos = std::max<uint64_t>(ho[1], n_cut - 1);
         }                                          // else (n <= 65): reinit(0) of the constructor set the flags
-        z += greedy_emit_from(host_text, n, ML, g, idx, ho[0], (size_t)ho[2], emit, ctx);
+        if (naive) z += greedy_naive_emit_from(host_text, n, ML, idx, ho[0], (size_t)ho[2], emit, ctx);
+        else z += greedy_emit_from(host_text, n, ML, g, idx, ho[0], (size_t)ho[2], emit, ctx);
         st.d2h_bytes += 20 * bp.hashed + 8 * buckets.size();
     }
     st.num_factors = z;
@@ -697,8 +958,8 @@ int factorize_dispatch(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* 
                        lz77sss_emit_fn emit, void* ctx) {
     if (!h || !host_text || !emit) return fail(LZ77SSS_E_ARG, "null argument");
     if (n == 0) return fail(LZ77SSS_E_ARG, "empty input");
-    if (h->cfg.phr_mode != LZ77SSS_PHR_LPF_OPT || h->cfg.fact_mode != LZ77SSS_FACT_GREEDY)
-        return fail(LZ77SSS_E_UNSUPPORTED, "only factorize_approximate<greedy, lpf_opt> is implemented");
+    if (h->cfg.phr_mode > LZ77SSS_PHR_LPF_LNF_OPT || h->cfg.fact_mode > LZ77SSS_FACT_SKIP_PHRASES)
+        return fail(LZ77SSS_E_ARG, "unknown phrase or factorization mode");
     if (h->cfg.num_threads > n) return fail(LZ77SSS_E_ARG, "num_threads > n");
     if (h->cfg.pos_bits == 32 && n > 0xFFFFFFFFull) return fail(LZ77SSS_E_ARG, "pos_bits == 32 but n > UINT32_MAX");
     std::memset(&h->stats, 0, sizeof h->stats);

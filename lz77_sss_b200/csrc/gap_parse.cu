@@ -20,6 +20,7 @@
 // Slices bound the memory (5 entries per position) and carry the table as "last inserted position per bucket".
 // The last 65 positions of the text, where the reference's end-of-text rules for stale fingerprints apply,
 // are finished by the host with the table entries it asks for (api.cu).
+#include <algorithm>
 #include <vector>
 
 #include "common.cuh"
@@ -165,6 +166,8 @@ struct block_state {
 struct parse_ctx {
     uint64_t n, n_cut, a0, a1;
     uint32_t BL, nb;
+    uint32_t naive;            // factorize_greedy_naive (greedy_naive.cpp:34-113): every position is inserted, gap
+                               // factors stop at the next phrase, phrase-start probes stop at the phrase after it
     const uint32_t* tkey;      // bucket of every entry, time order
     const uint32_t* sval;      // entries sorted by bucket, time order inside a bucket
     const uint32_t* bstart;    // bucket b = sval[bstart[b] .. bstart[b+1])
@@ -247,8 +250,9 @@ __global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce
         uint64_t o_src, o_len;
         uint32_t kind;
         const uint64_t at = i;
-        if (i < pb) {   // gap step (greedy.cpp:60-97)
+        if (i < pb) {   // gap step (greedy.cpp:60-97, greedy_naive.cpp:56-67)
             probe<pos_t>(C, V, i, o_src, o_len);
+            if (C.naive && o_len > pb - i) o_len = pb - i;
             uint64_t i2 = i + (o_len ? o_len : 1);
             if (i2 > pb) {
                 if (i2 <= pe) {
@@ -272,10 +276,14 @@ __global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce
                 probe<pos_t>(C, V, i, fs, fl);
                 cur = i + 1;
                 kind |= KIND_PROBED;
+                if (C.naive && k + 1 < C.m) {            // greedy_naive.cpp:82-85: clipped to the next phrase start
+                    const uint64_t room = C.ml_beg[k + 1] > i ? C.ml_beg[k + 1] - i : 0;
+                    if (fl > room) fl = room;
+                }
                 if (fl > o_len) { o_src = fs; o_len = fl; }
             }
             i += o_len;
-            while (C.ml_end[k] <= i) k++;
+            while (k + 1 < C.m && C.ml_end[k] <= i) k++;
             gap = 0;
         }
         if (lane == 0) {
@@ -507,7 +515,8 @@ template <typename pos_t>
 void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, suffix_state<pos_t>& ss,
                    lce_state<pos_t>& ls, const gap_hash_params& gp, uint64_t table_entries, const uint64_t* h_ml,
                    uint64_t m, uint64_t n_cut, uint64_t slice_len, uint32_t block_len, gap_parse_scratch& sc,
-                   cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4]) {
+                   cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4],
+                   bool naive) {
     static_assert(sizeof(block_state) == 32, "block_state layout");
     if (slice_len > (1ull << 28)) slice_len = 1ull << 28;
     if (block_len < 32) block_len = 32;
@@ -558,7 +567,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
 
     for (uint64_t a0 = 0; a0 < n; a0 += slice_len) {
         const uint64_t a1 = a0 + slice_len < n ? a0 + slice_len : n;
-        if (first.i >= a1 && !first.gap) continue;           // a phrase covers the whole slice: nothing is inserted
+        if (first.i >= a1 && !first.gap && !naive) continue; // a phrase covers the whole slice: nothing is inserted
         const uint64_t cnt = a1 - a0, E = 5 * cnt;
         const uint32_t BL = block_len;
         const uint32_t nb = (uint32_t)((cnt + BL - 1) / BL);
@@ -592,7 +601,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         sc.cnt.reserve(nb + 2);
 
         parse_ctx C;
-        C.n = n; C.n_cut = n_cut; C.a0 = a0; C.a1 = a1; C.BL = BL; C.nb = nb;
+        C.n = n; C.n_cut = n_cut; C.a0 = a0; C.a1 = a1; C.BL = BL; C.nb = nb; C.naive = naive ? 1u : 0u;
         C.tkey = sc.tkey; C.sval = vals; C.bstart = sc.bstart;
         C.Hc = reinterpret_cast<const uint64_t*>(sc.Hc.get());
         C.notins = sc.notins;
@@ -612,8 +621,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             spec_entry_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, first);
             KERNEL_CHECK();
             CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
-            notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
-            KERNEL_CHECK();
+            if (!naive) {                                   // greedy_naive inserts every position: the bitmap stays zero
+                notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
+                KERNEL_CHECK();
+            }
             parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
             KERNEL_CHECK();
             sc.rounds++;
@@ -621,8 +632,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 link_kernel<<<1, 1024, 0, st>>>(C, first, sc.J, levels, d_exit);
                 KERNEL_CHECK();
                 CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
-                notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
-                KERNEL_CHECK();
+                if (!naive) {
+                    notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
+                    KERNEL_CHECK();
+                }
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get(), 0, 4, st));
                 parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
                 KERNEL_CHECK();
@@ -655,8 +668,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             }
             // the bitmap of the last round is the final one (it was built from the converged traces);
             // positions from the exit state on have not been reached yet
-            if (ex.i < a1) {
-                set_range_kernel<<<1, 32, 0, st>>>(sc.notins, ex.i - a0, cnt);
+            // (greedy_naive: every position below the exit state is inserted before the next probe)
+            const uint64_t unreached = naive ? std::max<uint64_t>({n_cut, ex.i, a0}) : ex.i;
+            if (unreached < a1) {
+                set_range_kernel<<<1, 32, 0, st>>>(sc.notins, unreached - a0, cnt);
                 KERNEL_CHECK();
             }
             CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 1, 0, 4, st));
@@ -671,11 +686,14 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             CUDA_CHECK(cudaMemsetAsync(sc.tr_cnt.get(), 0, (size_t)nb * 4, st));
             CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
             block_state f2 = first;
-            notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, f2);
-            KERNEL_CHECK();
-            // positions at and behind first.i are not inserted yet
-            if (first.i < a1) {
-                set_range_kernel<<<1, 32, 0, st>>>(sc.notins, (first.i > a0 ? first.i : a0) - a0, cnt);
+            if (!naive) {
+                notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, f2);
+                KERNEL_CHECK();
+            }
+            // positions at and behind first.i (greedy_naive: behind n_cut) are not inserted yet
+            const uint64_t unreached = naive ? std::max<uint64_t>(n_cut, first.i) : first.i;
+            if (unreached < a1) {
+                set_range_kernel<<<1, 32, 0, st>>>(sc.notins, (unreached > a0 ? unreached : a0) - a0, cnt);
                 KERNEL_CHECK();
             }
             CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 1, 0, 4, st));
@@ -709,7 +727,7 @@ void gap_parse_query(gap_parse_scratch& sc, const uint32_t* h_buckets, uint32_t 
     template void gap_parse_run<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t, suffix_state<pos_t>&, \
                                        lce_state<pos_t>&, const gap_hash_params&, uint64_t, const uint64_t*, uint64_t,  \
                                        uint64_t, uint64_t, uint32_t, gap_parse_scratch&, cudaStream_t,                  \
-                                       std::vector<uint64_t>&, std::vector<uint64_t>&, uint64_t[4]);
+                                       std::vector<uint64_t>&, std::vector<uint64_t>&, uint64_t[4], bool);
 INST(uint32_t)
 INST(uint64_t)
 

@@ -153,6 +153,88 @@ __global__ void lpf_candidates_kernel(const uint8_t* __restrict__ T, uint64_t n,
     psv_lcel[i] = pll; nsv_lcel[i] = nll;
 }
 
+// Candidates of build_LPF_all / build_LNF_all (lpf_lnf.cpp:34-134,139-249): for every synchronizing position the
+// nearest smaller (LPF) or nearest greater (LNF, on the reversed text) SA_S value on both sides of its rank, the
+// exact LCE_R with it (range minimum of LCP_S) and the leftward LCE capped at lcap characters.  SAx is SA_S itself
+// or its bitwise complement (nearest greater value == nearest smaller complement), tab the block minima of SAx.
+template <typename pos_t>
+__global__ void all_candidates_kernel(const uint8_t* __restrict__ T, const pos_t* __restrict__ S, uint64_t s,
+                                      const uint32_t* __restrict__ SAx, uint32_t flip, const uint32_t* __restrict__ ISA,
+                                      const pos_t* __restrict__ LCP, const uint32_t* __restrict__ tab,
+                                      const pos_t* __restrict__ lcp_tab, uint32_t nblk, uint64_t lcap,
+                                      uint32_t* __restrict__ p_idx, uint32_t* __restrict__ n_idx,
+                                      pos_t* __restrict__ p_lce, pos_t* __restrict__ n_lce,
+                                      pos_t* __restrict__ p_lcel, pos_t* __restrict__ n_lcel) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s) return;
+    const uint64_t r = ISA[i];
+    const uint64_t pos = S[i];
+    const uint32_t v = (uint32_t)i ^ flip;
+    const uint32_t pr = prev_smaller(SAx, tab, nblk, r, v);
+    const uint32_t nr = next_smaller(SAx, tab, nblk, s, r, v);
+    uint32_t pi = NONE32, ni = NONE32;
+    pos_t pl = 0, nl = 0, pll = 0, nll = 0;
+    auto left = [&](uint64_t src) -> pos_t {
+        if (src == 0 || pos == 0 || lcap == 0) return 0;
+        const uint64_t lo = src < pos ? src : pos, hi = src < pos ? pos : src;
+        return (pos_t)thread_lce_left(T, lo - 1, hi - 1, min(lcap, lo));
+    };
+    if (pr != NONE32) {
+        pi = SAx[pr] ^ flip;
+        pl = range_min(LCP, lcp_tab, nblk, (uint64_t)pr + 1, r);
+        pll = left(S[pi]);
+    }
+    if (nr != NONE32) {
+        ni = SAx[nr] ^ flip;
+        nl = range_min(LCP, lcp_tab, nblk, r + 1, (uint64_t)nr);
+        nll = left(S[ni]);
+    }
+    p_idx[i] = pi; n_idx[i] = ni;
+    p_lce[i] = pl; n_lce[i] = nl;
+    p_lcel[i] = pll; n_lcel[i] = nll;
+}
+
+__global__ void flip_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t s) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < s) out[i] = ~in[i];
+}
+
+// lce_l_64 (include/lz77_sss/algorithms/lce_l.hpp:33-83) without a cap: equal characters going left from T[qi] and
+// T[qj] (qi < qj), at most qi + 1.  One warp per query, 256 bytes per step.
+__global__ void __launch_bounds__(256) left_lce_kernel(const uint8_t* __restrict__ T, const uint64_t* __restrict__ qi,
+                                                       const uint64_t* __restrict__ qj, uint64_t nq,
+                                                       uint64_t* __restrict__ out) {
+    const uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const uint64_t i = qi[q], j = qj[q], cap = i + 1;
+    uint64_t k = 0, res = cap;
+    while (k < cap) {
+        const uint64_t kk = k + 8ull * lane;
+        uint32_t eq = 8;                               // equal bytes in this lane's word (8 = all)
+        if (kk < cap) {
+            // the front pad of the device text makes the 8 bytes ending at i - kk readable
+            const uint64_t a = load_u64_unaligned(T + i - kk - 7), b = load_u64_unaligned(T + j - kk - 7);
+            const uint64_t diff = a ^ b;
+            if (diff) eq = (uint32_t)(__clzll((long long)diff) / 8);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, eq < 8);
+        if (m) {
+            const int w = __ffs(m) - 1;
+            const uint32_t e = __shfl_sync(0xffffffffu, eq, w);
+            res = k + 8ull * w + e;
+            break;
+        }
+        k += 256;
+    }
+    if (lane == 0) out[q] = res < cap ? res : cap;
+}
+
+__global__ void reverse_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, uint64_t n) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[n - 1 - i];
+}
+
 template <typename pos_t>
 __global__ void succ_first_kernel(const pos_t* __restrict__ S, uint64_t s, uint32_t shift, uint64_t nb,
                                   uint32_t* __restrict__ first) {
@@ -232,6 +314,49 @@ void lpf_candidates(const uint8_t* T, uint64_t n, uint32_t tau, const pos_t* S, 
 }
 
 template <typename pos_t>
+void all_candidates(const uint8_t* T, uint64_t n, const pos_t* S, uint64_t s, bool greater, uint64_t lcap,
+                    suffix_state<pos_t>& ss, lce_state<pos_t>& ls, cudaStream_t st) {
+    (void)n;
+    if (s == 0) return;
+    ls.psv_idx.reserve(s); ls.nsv_idx.reserve(s);
+    ls.psv_lce.reserve(s); ls.nsv_lce.reserve(s);
+    ls.psv_lcel.reserve(s); ls.nsv_lcel.reserve(s);
+    const uint32_t* SAx = ss.SA;
+    const uint32_t* tab = ls.sa_blkmin;
+    if (greater) {
+        ls.sa_flip.reserve(s);
+        ls.saf_blkmin.reserve((uint64_t)ls.sp_levels * ls.nblk);
+        flip_kernel<<<ceil_div_u(s, 256), 256, 0, st>>>(ss.SA, ls.sa_flip, s);
+        KERNEL_CHECK();
+        blkmin_kernel<uint32_t><<<ceil_div_u((uint64_t)ls.nblk * 32, 256), 256, 0, st>>>(ls.sa_flip, s, ls.saf_blkmin, ls.nblk);
+        KERNEL_CHECK();
+        for (int l = 1; l < ls.sp_levels; l++) {
+            sparse_level_kernel<uint32_t><<<ceil_div_u(ls.nblk, 256), 256, 0, st>>>(ls.saf_blkmin, ls.nblk, l);
+            KERNEL_CHECK();
+        }
+        SAx = ls.sa_flip;
+        tab = ls.saf_blkmin;
+    }
+    all_candidates_kernel<pos_t><<<ceil_div_u(s, 128), 128, 0, st>>>(
+        T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.psv_idx,
+        ls.nsv_idx, ls.psv_lce, ls.nsv_lce, ls.psv_lcel, ls.nsv_lcel);
+    KERNEL_CHECK();
+}
+
+void left_lce_batch(const uint8_t* T, const uint64_t* d_qi, const uint64_t* d_qj, uint64_t nq, uint64_t* d_out,
+                    cudaStream_t st) {
+    if (nq == 0) return;
+    left_lce_kernel<<<ceil_div_u(nq * 32, 256), 256, 0, st>>>(T, d_qi, d_qj, nq, d_out);
+    KERNEL_CHECK();
+}
+
+void reverse_text(const uint8_t* d_in, uint8_t* d_out, uint64_t n, cudaStream_t st) {
+    if (n == 0) return;
+    reverse_kernel<<<ceil_div_u(n, 256), 256, 0, st>>>(d_in, d_out, n);
+    KERNEL_CHECK();
+}
+
+template <typename pos_t>
 void lce_r_batch(const uint8_t* T, uint64_t n, uint32_t tau, const pos_t* S, uint64_t s, suffix_state<pos_t>& ss,
                  lce_state<pos_t>& ls, const uint64_t* d_qi, const uint64_t* d_qj, uint64_t nq, uint64_t* d_out,
                  cudaStream_t st) {
@@ -244,6 +369,8 @@ void lce_r_batch(const uint8_t* T, uint64_t n, uint32_t tau, const pos_t* S, uin
     template void build_lce_structures<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t,              \
                                               suffix_state<pos_t>&, lce_state<pos_t>&, cudaStream_t);                  \
     template void lpf_candidates<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t, uint32_t,          \
+                                        suffix_state<pos_t>&, lce_state<pos_t>&, cudaStream_t);                        \
+    template void all_candidates<pos_t>(const uint8_t*, uint64_t, const pos_t*, uint64_t, bool, uint64_t,              \
                                         suffix_state<pos_t>&, lce_state<pos_t>&, cudaStream_t);                        \
     template void lce_r_batch<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t, suffix_state<pos_t>&, \
                                      lce_state<pos_t>&, const uint64_t*, const uint64_t*, uint64_t, uint64_t*,         \

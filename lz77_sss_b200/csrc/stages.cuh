@@ -63,6 +63,7 @@ struct lce_state {
     // per synchronizing position: the two LPF candidates
     dbuf<uint32_t> psv_idx, nsv_idx;       // sync index of the source or NONE32
     dbuf<pos_t> psv_lce, nsv_lce, psv_lcel, nsv_lcel;
+    dbuf<uint32_t> sa_flip, saf_blkmin;    // ~SA and its block minima (nearest GREATER values for build_LNF_all)
     scan_scratch scan;
 };
 template <typename pos_t>
@@ -72,6 +73,15 @@ void build_lce_structures(const uint8_t* d_text, uint64_t n, uint32_t tau, const
 template <typename pos_t>
 void lpf_candidates(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, uint32_t p_ref,
                     suffix_state<pos_t>& ss, lce_state<pos_t>& ls, cudaStream_t st);
+// candidates for build_LPF_all (greater = false) / build_LNF_all (greater = true, text reversed), lpf_lnf.cpp:34-249:
+// nearest smaller / greater SA_S value on both sides, exact LCE_R, leftward LCE capped at lcap
+template <typename pos_t>
+void all_candidates(const uint8_t* d_text, uint64_t n, const pos_t* d_S, uint64_t s, bool greater, uint64_t lcap,
+                    suffix_state<pos_t>& ss, lce_state<pos_t>& ls, cudaStream_t st);
+// uncapped leftward LCE (lce_l.hpp:33-83) of T[..qi] and T[..qj], qi < qj
+void left_lce_batch(const uint8_t* d_text, const uint64_t* d_qi, const uint64_t* d_qj, uint64_t nq, uint64_t* d_out,
+                    cudaStream_t st);
+void reverse_text(const uint8_t* d_in, uint8_t* d_out, uint64_t n, cudaStream_t st);
 // batched exact LCE_R(i,j) (lce_sss.hpp:102-177) for arbitrary text positions
 template <typename pos_t>
 void lce_r_batch(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s,
@@ -108,7 +118,8 @@ template <typename pos_t>
 void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, suffix_state<pos_t>& ss,
                    lce_state<pos_t>& ls, const gap_hash_params& gp, uint64_t table_entries, const uint64_t* h_ml,
                    uint64_t m, uint64_t n_cut, uint64_t slice_len, uint32_t block_len, gap_parse_scratch& sc,
-                   cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4]);
+                   cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4],
+                   bool naive = false);
 // table entries (last inserted position + 1, 0 = none) of the given buckets after gap_parse_run
 void gap_parse_query(gap_parse_scratch& sc, const uint32_t* h_buckets, uint32_t cnt, uint64_t* h_out, cudaStream_t st);
 

@@ -43,19 +43,19 @@ int64_t run_approximate(const uint8_t* text, uint64_t n, int phr_mode, int fact_
     using L = lz77_sss<pos_t>;
     auto t0 = std::chrono::steady_clock::now();   // timed like lz77_sss.hpp:314-353: around the call only
 #define RUN(FM, PM) L::template factorize_approximate<FM, PM, tau>(T, N, out, prm)
-    if (fact_mode == greedy) {
-        switch (phr_mode) {
-            case lpf_naive: RUN(greedy, lpf_naive); break;
-            case lpf_lnf_naive: RUN(greedy, lpf_lnf_naive); break;
-            case lpf_opt: RUN(greedy, lpf_opt); break;
-            case lpf_lnf_opt: RUN(greedy, lpf_lnf_opt); break;
-            default: return -1;
-        }
-    } else if (fact_mode == greedy_naive && phr_mode == lpf_opt) {
-        RUN(greedy_naive, lpf_opt);
-    } else {
-        return -1;
+#define RUN_PM(FM)                                                   \
+    switch (phr_mode) {                                              \
+        case lpf_naive: RUN(FM, lpf_naive); break;                   \
+        case lpf_lnf_naive: RUN(FM, lpf_lnf_naive); break;           \
+        case lpf_opt: RUN(FM, lpf_opt); break;                       \
+        case lpf_lnf_opt: RUN(FM, lpf_lnf_opt); break;               \
+        default: return -1;                                          \
     }
+    if (fact_mode == greedy) { RUN_PM(greedy) }
+    else if (fact_mode == greedy_naive) { RUN_PM(greedy_naive) }
+    else if (fact_mode == skip_phrases) { RUN_PM(skip_phrases) }
+    else return -1;
+#undef RUN_PM
 #undef RUN
     if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     return (int64_t)sink.z;
@@ -103,7 +103,7 @@ int64_t refdrv_factorize_approximate(const uint8_t* text, uint64_t n, int phr_mo
     int64_t z;
     if (n <= 0xFFFFFFFFull) z = run_approximate<uint32_t, REF_TAU>(text, n, phr_mode, fact_mode, num_threads, s, seconds);
     else z = run_approximate<uint64_t, REF_TAU>(text, n, phr_mode, fact_mode, num_threads, s, seconds);
-    if (z >= 0 && fact_mode == greedy) {
+    if (z >= 0 && fact_mode != skip_phrases) {   // skip_phrases builds no gap index (lz77_sss.hpp:417-418)
         int builds = (phr_mode == lpf_lnf_naive || phr_mode == lpf_lnf_opt) ? 1 : 1;
         for (int i = 0; i < 5 * builds; i++) draw(mirror());   // advance past the bases that run consumed
     }

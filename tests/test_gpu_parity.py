@@ -13,7 +13,9 @@ from lz77_sss_b200 import synth
 
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+_ALL_NPZ = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+GOLDEN = [p for p in _ALL_NPZ if not os.path.basename(p).startswith("modes_")]
+GOLDEN_MODES = [p for p in _ALL_NPZ if os.path.basename(p).startswith("modes_")]
 TAUS = [4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096]
 
 
@@ -37,6 +39,39 @@ def test_golden_vectors(capi, path):
             lpf = g[key + "_lpf"]
             assert _eq(b, lpf[0]) and _eq(e, lpf[1]) and _eq(s, lpf[2]) and _eq(blk.astype(np.uint64), lpf[3]), (key, "LPF")
             assert (F.decode(src, ln, text.size) == text).all(), (key, "decode")
+
+
+@pytest.mark.parametrize("path", GOLDEN_MODES, ids=[os.path.basename(p)[:-4] for p in GOLDEN_MODES])
+def test_golden_vectors_all_modes(capi, path):
+    """Every factorize_mode x phrase_mode (lz77_sss.hpp:47-58) against the reference's own output."""
+    g = np.load(path)
+    text = g["text"]
+    keys = [k[:-4] for k in g.files if k.endswith("_src")]
+    assert keys
+    for key in keys:
+        tau, p, fm, pm = key.split("_")
+        tau, p, fm, pm = int(tau[3:]), int(p[1:]), int(fm[2:]), int(pm[2:])
+        with capi.Factorizer(tau=tau, num_threads=p, gap_bases=g[key + "_bases"], phr_mode=pm, fact_mode=fm) as F:
+            src, ln = F.factorize(text)
+            assert _eq(src, g[key + "_src"]) and _eq(ln, g[key + "_len"]), (key, "factor stream")
+            if fm != capi.FACT_SKIP_PHRASES:
+                assert (F.decode(src, ln, text.size) == text).all(), (key, "decode")
+
+
+@pytest.mark.parametrize("fm,pm", [(fm, pm) for fm in (0, 1, 2) for pm in (0, 1, 2, 3)])
+def test_modes_against_reference_build(capi, oracle, fm, pm):
+    """Fresh inputs against oracle/_ref (the reference's own headers), where that build travelled to this box."""
+    tau = 64
+    if not oracle.ref_available(tau):
+        pytest.skip("oracle/_ref was not prebuilt")
+    for name, text in _texts().items():
+        if name in ("zeros", "period3"):
+            continue      # no LPF phrase or no gap: pattern lengths undefined in the reference (SURVEY.md A7)
+        for p in (1, 2):
+            rs, rl, bases, _ = oracle.ref_factorize(text, tau, p=p, phr_mode=pm, fact_mode=fm)
+            with capi.Factorizer(tau=tau, num_threads=p, gap_bases=bases, phr_mode=pm, fact_mode=fm) as F:
+                src, ln = F.factorize(text)
+                assert _eq(src, rs) and _eq(ln, rl), (name, p, fm, pm)
 
 
 def _texts():
