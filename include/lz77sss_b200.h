@@ -66,6 +66,7 @@ typedef struct lz77sss_stats {
     uint64_t kernel_launches;
     uint64_t h2d_bytes, d2h_bytes;   /* bytes copied host->device / device->host inside the call */
     uint64_t parse_rounds, parse_slices;   /* device emission: block-parse rounds over all slices, slices */
+    uint64_t sparse_slices, sparse_fallbacks;  /* slices parsed with gap-only index entries / redone with all positions */
 } lz77sss_stats;
 
 /* factor callback: lz77_sss<pos_t>::factor {src,len} by value, in text order, on the calling thread

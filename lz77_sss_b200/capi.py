@@ -40,7 +40,7 @@ class Stats(C.Structure):
                [(k, C.c_uint64) for k in ("roll_threshold", "table_entries", "ctx_levels", "doubling_rounds",
                                           "gap_positions_hashed", "t_h2d_ns", "t_sss_ns", "t_sort_ns", "t_lce_ns",
                                           "t_lpf_ns", "t_d2h_ns", "t_chain_ns", "t_gap_hash_ns", "t_emit_ns", "t_total_ns",
-                                          "kernel_launches", "h2d_bytes", "d2h_bytes", "parse_rounds", "parse_slices")]
+                                          "kernel_launches", "h2d_bytes", "d2h_bytes", "parse_rounds", "parse_slices", "sparse_slices", "sparse_fallbacks")]
 
     def as_dict(self):
         d = {}

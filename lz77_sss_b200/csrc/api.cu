@@ -915,6 +915,8 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     st.gap_positions_hashed = h->gp.entries_sorted / 5;
     st.parse_rounds = h->gp.rounds;
     st.parse_slices = h->gp.slices;
+    st.sparse_slices = h->gp.sparse_slices;
+    st.sparse_fallbacks = h->gp.sparse_fallbacks;
     st.t_gap_hash_ns = ns_since(t0);
 
     t0 = clk::now();

@@ -84,9 +84,12 @@ __device__ __forceinline__ int ge_txt(int p) { return p + ((p >> 6) << 2); }    
 __device__ __forceinline__ int ge_out(int o) { return o + o / (5 * GE_SEG); }          // 321-word pitch per lane row
 __global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restrict__ T, uint64_t n, const ghp5 hp,
                                                           uint64_t a0, uint64_t cnt, uint32_t* __restrict__ keys,
-                                                          uint32_t* __restrict__ tkeys, uint32_t* __restrict__ vals) {
+                                                          uint32_t* __restrict__ tkeys, uint32_t* __restrict__ vals,
+                                                          const uint32_t* __restrict__ skip,
+                                                          const uint32_t* __restrict__ tile_off) {
     __shared__ __align__(16) uint8_t sT[(GE_TILE + GE_HALO) / 64 * 68 + 16];
     __shared__ uint32_t sOut[5 * GE_TILE + GE_TILE / GE_SEG + 8];
+    __shared__ uint32_t sNeed[GE_TILE / 32], sRank[GE_TILE / 32];
     const int tid = threadIdx.x, lane = tid & 31, x = tid >> 5;          // warp x <-> pattern x
     const uint64_t t0 = (uint64_t)blockIdx.x * GE_TILE;                   // tile start, slice-relative
     const uint64_t g0 = a0 + t0;                                          // text position of the tile
@@ -137,12 +140,64 @@ __global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restr
     }
     __syncthreads();
     const uint64_t e0 = 5 * t0;
-    for (uint32_t o = tid; o < 5 * in_tile; o += 160) {
-        const uint32_t key = sOut[ge_out(o)];
-        keys[e0 + o] = key;
-        tkeys[e0 + o] = key;
-        vals[e0 + o] = (uint32_t)(e0 + o);
+    if (!skip) {
+        for (uint32_t o = tid; o < 5 * in_tile; o += 160) {
+            const uint32_t key = sOut[ge_out(o)];
+            keys[e0 + o] = key;
+            tkeys[e0 + o] = key;
+            vals[e0 + o] = (uint32_t)(e0 + o);
+        }
+        return;
     }
+    // sparse slice: only the positions whose skip bit is clear get entries; the sort sees them compacted (in time
+    // order), the time-order copy keeps its dense index so that a probe finds the buckets of its position directly
+    if (tid < GE_TILE / 32) {
+        const uint64_t wi = t0 / 32 + tid;
+        uint32_t need = (uint64_t)tid * 32 < in_tile ? ~skip[wi] : 0u;
+        if (((uint64_t)tid + 1) * 32 > in_tile && (uint64_t)tid * 32 < in_tile) need &= (1u << (in_tile & 31)) - 1u;
+        sNeed[tid] = need;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t acc = 0;
+        for (int k = 0; k < GE_TILE / 32; k++) { sRank[k] = acc; acc += __popc(sNeed[k]); }
+    }
+    __syncthreads();
+    const uint64_t c0 = 5ull * tile_off[blockIdx.x];
+    for (uint32_t o = tid; o < 5 * in_tile; o += 160) {
+        const uint32_t r = o / 5u, j = o - 5u * r;
+        const uint32_t need = sNeed[r >> 5];
+        if (!((need >> (r & 31)) & 1u)) continue;
+        const uint32_t rank = sRank[r >> 5] + __popc(need & ((1u << (r & 31)) - 1u));
+        const uint32_t key = sOut[ge_out(o)];
+        keys[c0 + 5ull * rank + j] = key;
+        vals[c0 + 5ull * rank + j] = (uint32_t)(e0 + o);
+        tkeys[e0 + o] = key;
+    }
+}
+
+// positions of the slice that need no entry when no gap factor runs over a whole phrase: the inside (beg, end) of
+// every phrase (the phrase start is probed, greedy.cpp:111-117).  One warp per phrase k0 + w.
+__global__ void __launch_bounds__(128) skip_bits_kernel(const uint64_t* __restrict__ ml_beg, const uint64_t* __restrict__ ml_end,
+                                                        uint64_t k0, uint64_t k1, uint64_t a0, uint64_t a1,
+                                                        uint32_t* __restrict__ bm, int adjacent_starts);
+
+// needed positions per tile of GE_TILE positions
+__global__ void tile_need_kernel(const uint32_t* __restrict__ skip, uint64_t cnt, uint32_t ntiles, uint32_t* __restrict__ out) {
+    const uint32_t t = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const unsigned lane = threadIdx.x & 31;
+    if (t >= ntiles) return;
+    uint32_t c = 0;
+    for (int k = lane; k < GE_TILE / 32; k += 32) {
+        const uint64_t p0 = (uint64_t)t * GE_TILE + (uint64_t)k * 32;
+        if (p0 >= cnt) continue;
+        uint32_t need = ~skip[p0 / 32];
+        if (p0 + 32 > cnt) need &= (1u << (cnt - p0)) - 1u;
+        c += __popc(need);
+    }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+    if (lane == 0) out[t] = c;
 }
 
 // bstart[b] = first sorted index whose key is >= b, for b in [0, nkeys]  (nkeys = table_entries + 1 keys incl. invalid)
@@ -166,6 +221,7 @@ struct block_state {
 struct parse_ctx {
     uint64_t n, n_cut, a0, a1;
     uint32_t BL, nb;
+    uint32_t bmin;             // blocks below it cannot change in this round (nothing before them changed in the last one)
     uint32_t naive;            // factorize_greedy_naive (greedy_naive.cpp:34-113): every position is inserted, gap
                                // factors stop at the next phrase, phrase-start probes stop at the phrase after it
     const uint32_t* tkey;      // bucket of every entry, time order
@@ -173,6 +229,8 @@ struct parse_ctx {
     const uint32_t* bstart;    // bucket b = sval[bstart[b] .. bstart[b+1])
     const uint64_t* Hc;        // last inserted position + 1 per bucket (0 = none), state before the slice
     const uint32_t* notins;    // bit = 1: position of the slice is NOT inserted
+    const uint32_t* skip;      // sparse slice: bit = 1: the position has no entries (nullptr: every position has)
+    uint8_t* ovr;              // per block: its parse needed entries that a sparse slice does not have
     const uint64_t* ml_beg;
     const uint64_t* ml_end;
     const uint64_t* ml_src;
@@ -194,9 +252,15 @@ __device__ __forceinline__ bool not_inserted(const uint32_t* __restrict__ bm, ui
 // longest_prev_occ (factorize/common.cpp:33-61) at position i, all 32 lanes; lanes 0..4 own patterns 4..0
 template <typename pos_t>
 __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>& V, uint64_t i, uint64_t& f_src,
-                                      uint64_t& f_len) {
+                                      uint64_t& f_len, bool& bad) {
     const unsigned lane = threadIdx.x & 31;
     const uint32_t rel = (uint32_t)(i - C.a0);
+    if (C.skip && ((C.skip[rel >> 5] >> (rel & 31)) & 1u)) {       // only a wrong speculation or an overrun gets here
+        bad = true;
+        f_src = V.T[i];
+        f_len = 0;
+        return;
+    }
     uint64_t occ = NONE64;
     if (lane < 5) {
         const uint32_t e = 5u * rel + lane;
@@ -234,7 +298,7 @@ template <typename pos_t>
 __global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce_view<pos_t> V) {
     const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     const unsigned lane = threadIdx.x & 31;
-    if (b >= C.nb || !C.marked[b]) return;
+    if (b >= C.nb || b < C.bmin || !C.marked[b]) return;
     const block_state st = C.entry[b];
     uint64_t i = st.i, cur = st.cur, k = st.k;
     uint32_t gap = st.gap;
@@ -244,14 +308,14 @@ __global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce
     const uint32_t oldlen = C.tr_cnt[b];
     const uint64_t slot0 = (uint64_t)b * C.BL;
     uint32_t t = 0;
-    bool chg = false;
+    bool chg = false, bad = false;
     while (i < lim) {
         const uint64_t pb = C.ml_beg[k], pe = C.ml_end[k];
         uint64_t o_src, o_len;
         uint32_t kind;
         const uint64_t at = i;
         if (i < pb) {   // gap step (greedy.cpp:60-97, greedy_naive.cpp:56-67)
-            probe<pos_t>(C, V, i, o_src, o_len);
+            probe<pos_t>(C, V, i, o_src, o_len, bad);
             if (C.naive && o_len > pb - i) o_len = pb - i;
             uint64_t i2 = i + (o_len ? o_len : 1);
             if (i2 > pb) {
@@ -259,6 +323,7 @@ __global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce
                     o_len -= i2 - pb;
                     i2 = pb;
                 } else {
+                    bad = true;                     // positions inside a phrase get inserted: a sparse slice lacks them
                     while (C.ml_end[k] <= i2) k++;
                 }
             }
@@ -273,7 +338,7 @@ __global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce
             kind = KIND_PHR;
             if (cur == i) {
                 uint64_t fs, fl;
-                probe<pos_t>(C, V, i, fs, fl);
+                probe<pos_t>(C, V, i, fs, fl, bad);
                 cur = i + 1;
                 kind |= KIND_PROBED;
                 if (C.naive && k + 1 < C.m) {            // greedy_naive.cpp:82-85: clipped to the next phrase start
@@ -303,7 +368,12 @@ __global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce
         ex.i = i; ex.cur = cur; ex.k = k; ex.gap = gap; ex.pad = 0;
         C.exit_[b] = ex;
         C.tr_cnt[b] = t;
-        if (chg) atomicOr(C.changed, 1u);
+        C.ovr[b] = bad ? 1 : 0;
+        if (chg) {
+            atomicOr(C.changed, 1u);
+            atomicAdd(C.changed + 3, 1u);
+            atomicMin(C.changed + 4, b);
+        }
     }
 }
 
@@ -334,6 +404,14 @@ __global__ void spec_entry_kernel(const parse_ctx C, block_state first) {
             const uint64_t mid = (lo + hi) / 2;
             if (C.ml_end[mid] > bs) hi = mid;
             else lo = mid + 1;
+        }
+        // inside a phrase the true parse most likely arrives by taking that phrase to its end without touching
+        // the table there (greedy.cpp:100-131)
+        if (C.ml_beg[lo] < bs) {
+            st.i = C.ml_end[lo];
+            st.cur = C.ml_beg[lo] + 1 < st.i ? C.ml_beg[lo] + 1 : C.ml_beg[lo];
+            st.gap = 0;
+            while (lo + 1 < C.m && C.ml_end[lo] <= st.i) lo++;
         }
         st.k = lo;
     }
@@ -419,6 +497,32 @@ __global__ void __launch_bounds__(128) notins_kernel(const parse_ctx C, uint32_t
 
 __global__ void set_range_kernel(uint32_t* __restrict__ bm, uint64_t s, uint64_t e) { set_bits(bm, s, e, threadIdx.x & 31); }
 
+__global__ void __launch_bounds__(128) skip_bits_kernel(const uint64_t* __restrict__ ml_beg, const uint64_t* __restrict__ ml_end,
+                                                        uint64_t k0, uint64_t k1, uint64_t a0, uint64_t a1,
+                                                        uint32_t* __restrict__ bm, int adjacent_starts) {
+    const uint64_t k = k0 + (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (k >= k1) return;
+    uint64_t s = ml_beg[k] + 1, e = ml_end[k];
+    // a phrase that follows its predecessor without a gap is (most likely) not probed at its start either
+    if (adjacent_starts && k > 0 && ml_end[k - 1] >= ml_beg[k]) s = ml_beg[k];
+    if (s < a0) s = a0;
+    if (e > a1) e = a1;
+    if (s < e) set_bits(bm, s - a0, e - a0, threadIdx.x & 31);
+}
+
+// clear [s, e) (one warp)
+__global__ void clear_range_kernel(uint32_t* __restrict__ bm, uint64_t s, uint64_t e) {
+    if (s >= e) return;
+    const unsigned lane = threadIdx.x & 31;
+    const uint64_t w0 = s >> 5, w1 = (e - 1) >> 5;
+    for (uint64_t w = w0 + lane; w <= w1; w += 32) {
+        uint32_t m = 0xFFFFFFFFu;
+        if (w == w0) m &= 0xFFFFFFFFu << (s & 31);
+        if (w == w1) m &= 0xFFFFFFFFu >> (31 - ((e - 1) & 31));
+        bm[w] &= ~m;
+    }
+}
+
 // carry the table over the slice: last inserted position per bucket.  One thread per bucket walks its list
 // backwards; lists that do not settle within 64 entries are handed to a warp each (carry_big_kernel).
 __global__ void carry_kernel(const parse_ctx C, uint32_t nbuckets, unsigned long long* __restrict__ Hc,
@@ -470,7 +574,10 @@ __global__ void __launch_bounds__(128) carry_big_kernel(const parse_ctx C, unsig
 
 __global__ void count_kernel(const parse_ctx C, uint32_t* __restrict__ cnt) {
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b < C.nb) cnt[b] = C.marked[b] ? C.tr_cnt[b] : 0u;
+    if (b < C.nb) {
+        cnt[b] = C.marked[b] ? C.tr_cnt[b] : 0u;
+        if (C.marked[b] && C.ovr[b]) atomicOr(C.changed + 2, 1u);
+    }
 }
 
 __global__ void __launch_bounds__(128) gather_kernel(const parse_ctx C, const uint32_t* __restrict__ off,
@@ -554,12 +661,18 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
     sc.rounds = 0;
     sc.slices = 0;
     sc.entries_sorted = 0;
+    sc.sparse_slices = 0;
+    sc.sparse_fallbacks = 0;
+    // Sparse slices pay only when no gap factor runs over a whole phrase; on the bench texts such overruns occur in
+    // every slice and the dense redo makes the attempt a loss, so it is opt-in (LZ77SSS_SPARSE_GAP_INDEX=1).
+    const bool sparse_ok = getenv("LZ77SSS_SPARSE_GAP_INDEX") != nullptr;
 
     sc.ml.reserve(3 * m);
     CUDA_CHECK(cudaMemcpyAsync(sc.ml.get(), h_ml, 3 * m * 8, cudaMemcpyHostToDevice, st));
     sc.Hc.reserve(table_entries);
     CUDA_CHECK(cudaMemsetAsync(sc.Hc.get(), 0, table_entries * 8, st));
-    sc.changed.reserve(4);
+    sc.changed.reserve(8);
+    const bool dbg_rounds = getenv("LZ77SSS_DEBUG_ROUNDS") != nullptr;
     sc.slice_exit.reserve(sizeof(block_state));
 
     block_state first;
@@ -568,26 +681,63 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
     for (uint64_t a0 = 0; a0 < n; a0 += slice_len) {
         const uint64_t a1 = a0 + slice_len < n ? a0 + slice_len : n;
         if (first.i >= a1 && !first.gap && !naive) continue; // a phrase covers the whole slice: nothing is inserted
-        const uint64_t cnt = a1 - a0, E = 5 * cnt;
+        const uint64_t cnt = a1 - a0;
         const uint32_t BL = block_len;
         const uint32_t nb = (uint32_t)((cnt + BL - 1) / BL);
+        const uint64_t nwords = (cnt + 31) / 32 + 1;
+        const uint32_t ntiles = ceil_div_u(cnt, GE_TILE);
         sc.slices++;
+        // Attempt 0 (sparse): entries only for the positions that can be inserted or probed when no gap factor runs
+        // over a whole phrase (greedy.cpp:68-77), i.e. the gaps and the phrase starts.  If the converged parse
+        // did overrun (or the gaps are most of the slice anyway), attempt 1 redoes the slice with every position.
+        // phrases that overlap the slice (the sentinel is not one of them)
+        const uint64_t k0 = std::upper_bound(h_ml + m, h_ml + m + (m - 1), a0) - (h_ml + m);
+        const uint64_t k1 = std::lower_bound(h_ml, h_ml + (m - 1), a1) - h_ml;
+      for (int attempt = (naive || !sparse_ok) ? 1 : 0; attempt < 2; attempt++) {
+        bool sparse = attempt == 0;
+        uint64_t E = 5 * cnt;
+        if (sparse) {
+            sc.skip.reserve(nwords);
+            sc.tile_off.reserve(ntiles + 2);
+            CUDA_CHECK(cudaMemsetAsync(sc.skip.get(), 0, nwords * 4, st));
+            if (k1 > k0) {
+                skip_bits_kernel<<<ceil_div_u((k1 - k0) * 32, 128), 128, 0, st>>>(sc.ml.get(), sc.ml.get() + m, k0, k1, a0, a1, sc.skip, 0);
+                KERNEL_CHECK();
+            }
+            if (first.gap && first.i > a0) {          // a gap factor reaches into the slice: those positions are inserted
+                clear_range_kernel<<<1, 32, 0, st>>>(sc.skip, 0, (first.i < a1 ? first.i : a1) - a0);
+                KERNEL_CHECK();
+            }
+            tile_need_kernel<<<ceil_div_u((uint64_t)ntiles * 32, 256), 256, 0, st>>>(sc.skip, cnt, ntiles, sc.tile_off);
+            KERNEL_CHECK();
+            exclusive_scan_u32(sc.tile_off, ntiles, sc.scan, st, sc.tile_off.get() + ntiles);
+            uint32_t needed = 0;
+            CUDA_CHECK(cudaMemcpyAsync(&needed, sc.tile_off.get() + ntiles, 4, cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            if ((uint64_t)needed * 2 > cnt) continue;   // mostly gaps: the dense slice costs about the same and cannot fail
+            E = 5ull * needed;
+        }
         sc.entries_sorted += E;
         // 1. hash + 2. sort
-        sc.k0.reserve(E); sc.k1.reserve(E); sc.v0.reserve(E); sc.v1.reserve(E); sc.tkey.reserve(E);
+        sc.k0.reserve(E + 8); sc.k1.reserve(E + 8); sc.v0.reserve(E + 8); sc.v1.reserve(E + 8); sc.tkey.reserve(5 * cnt);
         sc.bstart.reserve(table_entries + 4);
         sc.big.reserve(table_entries + 4);
         uint32_t *keys = sc.k0, *kalt = sc.k1, *vals = sc.v0, *valt = sc.v1;
         {
-            gap_entries_kernel<<<ceil_div_u(cnt, GE_TILE), 160, 0, st>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, vals);
+            gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, vals,
+                                                       sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
             KERNEL_CHECK();
         }
+        if (E == 0) {                                  // no entry at all: every bucket list is empty
+            CUDA_CHECK(cudaMemsetAsync(sc.bstart.get(), 0, (table_entries + 2) * 4, st));
+        } else {
         radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, sc.sort, st);
         bucket_start_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
         KERNEL_CHECK();
+        }
         // per-block state
-        const uint64_t nwords = (cnt + 31) / 32 + 1;
         sc.notins.reserve(nwords);
+        sc.ovr.reserve(nb + 1);
         sc.entry.reserve((uint64_t)nb * sizeof(block_state));
         sc.exit_.reserve((uint64_t)nb * sizeof(block_state));
         sc.marked.reserve(nb + 1);
@@ -601,10 +751,12 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         sc.cnt.reserve(nb + 2);
 
         parse_ctx C;
-        C.n = n; C.n_cut = n_cut; C.a0 = a0; C.a1 = a1; C.BL = BL; C.nb = nb; C.naive = naive ? 1u : 0u;
+        C.n = n; C.n_cut = n_cut; C.a0 = a0; C.a1 = a1; C.BL = BL; C.nb = nb; C.naive = naive ? 1u : 0u; C.bmin = 0;
         C.tkey = sc.tkey; C.sval = vals; C.bstart = sc.bstart;
         C.Hc = reinterpret_cast<const uint64_t*>(sc.Hc.get());
         C.notins = sc.notins;
+        C.skip = sparse ? sc.skip.get() : nullptr;
+        C.ovr = sc.ovr;
         C.ml_beg = sc.ml.get(); C.ml_end = sc.ml.get() + m; C.ml_src = sc.ml.get() + 2 * m; C.m = m;
         C.entry = reinterpret_cast<block_state*>(sc.entry.get());
         C.exit_ = reinterpret_cast<block_state*>(sc.exit_.get());
@@ -622,6 +774,15 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             KERNEL_CHECK();
             CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
             if (!naive) {                                   // greedy_naive inserts every position: the bitmap stays zero
+                // speculative bitmap of round 0: the inside of every phrase is not inserted
+                if (k1 > k0) {
+                    skip_bits_kernel<<<ceil_div_u((k1 - k0) * 32, 128), 128, 0, st>>>(sc.ml.get(), sc.ml.get() + m, k0, k1, a0, a1, sc.notins, 1);
+                    KERNEL_CHECK();
+                }
+                if (first.gap && first.i > a0) {
+                    clear_range_kernel<<<1, 32, 0, st>>>(sc.notins, 0, (first.i < a1 ? first.i : a1) - a0);
+                    KERNEL_CHECK();
+                }
                 notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
                 KERNEL_CHECK();
             }
@@ -637,24 +798,39 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                     KERNEL_CHECK();
                 }
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get(), 0, 4, st));
+                CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 3, 0, 4, st));
+                CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 4, 0xFF, 4, st));
                 parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
                 KERNEL_CHECK();
                 sc.rounds++;
                 uint32_t chg = 0;
                 CUDA_CHECK(cudaMemcpyAsync(&chg, sc.changed.get(), 4, cudaMemcpyDeviceToHost, st));
                 CUDA_CHECK(cudaStreamSynchronize(st));
+                if (dbg_rounds) {
+                    uint32_t d[2];
+                    CUDA_CHECK(cudaMemcpy(d, sc.changed.get() + 3, 8, cudaMemcpyDeviceToHost));
+                    fprintf(stderr, "slice %llu round %llu: %u of %u blocks changed, first %u\n", (unsigned long long)a0,
+                            (unsigned long long)round, d[0], nb, d[1]);
+                }
                 if (!chg) { converged = true; break; }
+                CUDA_CHECK(cudaMemcpy(&C.bmin, sc.changed.get() + 4, 4, cudaMemcpyDeviceToHost));
             }
             if (!converged) throw std::runtime_error("gap_parse: the block chain did not reach its fixed point");
             // factors of the blocks on the chain, in order
+            CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 2, 0, 4, st));
             count_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, sc.cnt);
             KERNEL_CHECK();
             exclusive_scan_u32(sc.cnt, nb, sc.scan, st, sc.cnt.get() + nb);
-            uint32_t zs = 0;
+            uint32_t zs = 0, overrun = 0;
+            CUDA_CHECK(cudaMemcpyAsync(&overrun, sc.changed.get() + 2, 4, cudaMemcpyDeviceToHost, st));
             CUDA_CHECK(cudaMemcpyAsync(&zs, sc.cnt.get() + nb, 4, cudaMemcpyDeviceToHost, st));
             block_state ex;
             CUDA_CHECK(cudaMemcpyAsync(&ex, d_exit, sizeof ex, cudaMemcpyDeviceToHost, st));
             CUDA_CHECK(cudaStreamSynchronize(st));
+            if (sparse && overrun) {                    // the parse used positions that have no entries: redo dense
+                sc.sparse_fallbacks++;
+                continue;
+            }
             if (zs) {
                 sc.fsrc.reserve(zs); sc.flen.reserve(zs);
                 gather_kernel<<<gw, 128, 0, st>>>(C, sc.cnt, sc.fsrc, sc.flen);
@@ -702,6 +878,9 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             carry_big_kernel<<<1184, 128, 0, st>>>(C, sc.Hc.get(), sc.big, sc.changed.get() + 1);
             KERNEL_CHECK();
         }
+        if (sparse) sc.sparse_slices++;
+        break;
+      }
     }
     CUDA_CHECK(cudaStreamSynchronize(st));
     handover[0] = first.i;

@@ -107,10 +107,11 @@ struct gap_parse_scratch {
     dbuf<uint32_t> k0, k1, v0, v1, tkey, bstart, big, notins, tr_cnt, tr_pos, changed, J, cnt;
     dbuf<uint64_t> tr_src, tr_len, ml, fsrc, flen;
     dbuf<unsigned long long> Hc;
-    dbuf<uint8_t> entry, exit_, marked, slice_exit, nbtab;
+    dbuf<uint8_t> entry, exit_, marked, slice_exit, nbtab, ovr;
+    dbuf<uint32_t> skip, tile_off;         // sparse slices: positions without entries, compaction offsets per tile
     sort_scratch sort;
     scan_scratch scan;
-    uint64_t rounds = 0, slices = 0, entries_sorted = 0;
+    uint64_t rounds = 0, slices = 0, entries_sorted = 0, sparse_slices = 0, sparse_fallbacks = 0;
 };
 // h_ml: three planes (beg, end, src) of the merged phrase list incl. the sentinel {n, n+1, 0} (m entries).
 // Parses [0, n_cut); appends the factors to out_src/out_len; handover = {i, cur_pos, phrase index, gap flag}.

@@ -159,6 +159,30 @@ def test_short_inputs_end_of_text_rules(capi, oracle, n):
                 assert (F.decode(src, ln, n) == text).all()
 
 
+@pytest.mark.parametrize("env", [{"LZ77SSS_SPARSE_GAP_INDEX": "1"}, {"LZ77SSS_SLICE_LEN": "40000", "LZ77SSS_BLOCK_LEN": "64"},
+                                 {"LZ77SSS_SPARSE_GAP_INDEX": "1", "LZ77SSS_SLICE_LEN": "100000"}],
+                         ids=["sparse", "small_slices", "sparse_small_slices"])
+def test_emission_variants_give_the_same_factors(capi, oracle, env, monkeypatch):
+    """Slicing, block length and the sparse gap index (entries only for gaps and phrase starts, dense redo when a
+    gap factor overruns a phrase) are internal choices: the factor stream must not depend on them."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    bases = (401, 70_001, 123_457, 999_983, 1_048_575)
+    for name, text in _texts().items():
+        if name in ("zeros", "period3"):
+            continue
+        for tau, fm in ((16, capi.FACT_GREEDY), (512, capi.FACT_GREEDY), (64, capi.FACT_GREEDY_NAIVE)):
+            if fm == capi.FACT_GREEDY:
+                osrc, olen, _ = oracle.factorize(text, tau, bases, p_ref=1)
+            elif oracle.ref_available(tau):
+                osrc, olen, bases, _ = oracle.ref_factorize(text, tau, p=1, fact_mode=oracle.GREEDY_NAIVE)
+            else:
+                continue
+            with capi.Factorizer(tau=tau, num_threads=1, gap_bases=bases, fact_mode=fm) as F:
+                src, ln = F.factorize(text)
+                assert _eq(src, osrc) and _eq(ln, olen), (name, tau, fm, env)
+
+
 def _check_factors(text, src, ln):
     n = text.size
     lens = np.maximum(ln, 1).astype(np.int64)

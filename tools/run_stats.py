@@ -1,0 +1,20 @@
+"""Run one factorization of the bench text on the GPU box and print the library's statistics."""
+import json, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+from lz77_sss_b200 import capi, synth
+mib = int(sys.argv[1]) if len(sys.argv) > 1 else 256
+workload = sys.argv[2] if len(sys.argv) > 2 else "dna"
+reps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
+n = mib << 20
+text = synth.dna_collection(n, seed=2, chrom_len=min(16 << 20, max(n // 64, 1 << 16))) if workload == "dna" else synth.random_repetitive(n, seed=1)
+with capi.Factorizer(tau=512, num_threads=1) as F:
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        src, ln = F.factorize(text)
+        dt = time.perf_counter() - t0
+        st = F.stats()
+        keep = {k: v for k, v in st.items() if not k.startswith("t_")}
+        keep.update({k: round(v / 1e6, 2) for k, v in st.items() if k.startswith("t_")})
+        print(json.dumps({"wall_ms": round(dt * 1e3, 1), **keep}))
