@@ -104,6 +104,27 @@ int lz77sss_device_text_free(lz77sss_handle* h, uint8_t* d_text);
 int lz77sss_factorize_approximate_device(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n,
                                          lz77sss_emit_fn emit, void* ctx);
 
+/* ---- one text sharded over several GPUs ------------------------------------------------------------
+ * One process per GPU; every rank holds the whole text in HBM (the host layer all-gathers the shards over NVLink) and
+ * runs lz77sss_shard_prepare (synchronizing set, SA_S, LPF phrases, gap parameters: replicated, 1/5 of the work).
+ * The gap index and the greedy emission (factorize_greedy, greedy.cpp:34-140; rolling_hash_index_107.hpp:33-173) are
+ * split by text range: a rank parses [beg, end) from an entry state {i, table cursor, phrase index, gap flag} and
+ * the table "last inserted position + 1 per bucket before beg" (device array of lz77sss_shard_table_entries u64).
+ * Entry states and tables of ranges behind the first are guesses at first; the host layer exchanges exit states and
+ * tables (NCCL all-gather) and re-parses the ranges whose inputs changed until nothing changes.  A re-parse resumes
+ * from the sorted entries and traces the handle kept.  The result is the sequential factor stream.
+ * lz77_sss_b200/sharded.py is that host layer. */
+int lz77sss_shard_prepare(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n);
+int lz77sss_shard_table_entries(lz77sss_handle* h, uint64_t* entries);
+int lz77sss_shard_entry_guess(lz77sss_handle* h, uint64_t pos, uint64_t state[4]);
+int lz77sss_shard_parse(lz77sss_handle* h, uint64_t beg, uint64_t end, const uint64_t entry[4], const uint64_t* d_table_in,
+                        uint64_t* d_table_out, uint64_t exit_state[4], uint64_t* num_factors);
+/* factors of the last lz77sss_shard_parse on this handle (HOST arrays) */
+int lz77sss_shard_factors(lz77sss_handle* h, uint64_t* src, uint64_t* len, uint64_t cap, uint64_t* count);
+/* the last 65 positions of the text (end-of-text rules of the gap index), on the rank that parsed the last range,
+ * right after its final lz77sss_shard_parse: emits the remaining factors from `state` */
+int lz77sss_shard_finish(lz77sss_handle* h, const uint64_t state[4], lz77sss_emit_fn emit, void* ctx);
+
 /* lz77_sss<pos_t>::decode (algorithms/common.cpp:33-54): z factors -> n bytes into the HOST buffer out. */
 int lz77sss_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, uint64_t z, uint8_t* out, uint64_t n);
 

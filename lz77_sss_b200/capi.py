@@ -25,6 +25,8 @@ EXPORTS = [
     "lz77sss_device_text_free", "lz77sss_factorize_approximate_device", "lz77sss_decode", "lz77sss_build_sss",
     "lz77sss_time_sss_kernel", "lz77sss_get_stats", "lz77sss_get_sss", "lz77sss_get_sa_s", "lz77sss_get_lcp_s",
     "lz77sss_get_lpf", "lz77sss_lce_batch", "lz77sss_sink_emit",
+    "lz77sss_shard_prepare", "lz77sss_shard_table_entries", "lz77sss_shard_entry_guess", "lz77sss_shard_parse",
+    "lz77sss_shard_factors", "lz77sss_shard_finish",
 ]
 
 
@@ -89,6 +91,13 @@ def lib():
         L.lz77sss_get_lcp_s.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.lz77sss_get_lpf.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.lz77sss_lce_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+        L.lz77sss_shard_prepare.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+        L.lz77sss_shard_table_entries.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        L.lz77sss_shard_entry_guess.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_shard_parse.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p,
+                                          C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.lz77sss_shard_factors.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_shard_finish.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -242,3 +251,43 @@ class Factorizer:
         out = np.empty(max(1, qi.size), dtype=np.uint64)
         _check(lib().lz77sss_lce_batch(self._h, _ptr(qi), _ptr(qj), qi.size, _ptr(out)))
         return out[:qi.size]
+
+    # --- one text sharded over several GPUs (include/lz77sss_b200.h, lz77sss_shard_*) -------------
+    def shard_prepare(self, d_text_ptr, host_ptr, n):
+        _check(lib().lz77sss_shard_prepare(self._h, C.c_void_p(d_text_ptr), C.c_void_p(host_ptr), n))
+
+    def shard_table_entries(self):
+        e = C.c_uint64(0)
+        _check(lib().lz77sss_shard_table_entries(self._h, C.byref(e)))
+        return int(e.value)
+
+    def shard_entry_guess(self, pos):
+        st = (C.c_uint64 * 4)()
+        _check(lib().lz77sss_shard_entry_guess(self._h, pos, st))
+        return tuple(int(x) for x in st)
+
+    def shard_parse(self, beg, end, entry, table_in_ptr, table_out_ptr):
+        """Parses [beg, end); returns (exit_state, number of factors). Table pointers are device addresses (or 0)."""
+        e = (C.c_uint64 * 4)(*[int(x) for x in entry])
+        x = (C.c_uint64 * 4)()
+        z = C.c_uint64(0)
+        _check(lib().lz77sss_shard_parse(self._h, beg, end, e, C.c_void_p(table_in_ptr or None), C.c_void_p(table_out_ptr or None),
+                                         x, C.byref(z)))
+        return tuple(int(v) for v in x), int(z.value)
+
+    def shard_factors(self):
+        cnt = C.c_uint64(0)
+        _check(lib().lz77sss_shard_factors(self._h, None, None, 0, C.byref(cnt)))
+        z = int(cnt.value)
+        src = np.empty(max(1, z), dtype=np.uint64)
+        ln = np.empty(max(1, z), dtype=np.uint64)
+        _check(lib().lz77sss_shard_factors(self._h, _ptr(src), _ptr(ln), z, C.byref(cnt)))
+        return src[:z], ln[:z]
+
+    def shard_finish(self, state, cap=4096):
+        src, ln, s = self._sink(cap)
+        st = (C.c_uint64 * 4)(*[int(x) for x in state])
+        emit = C.cast(lib().lz77sss_sink_emit, C.c_void_p)
+        _check(lib().lz77sss_shard_finish(self._h, st, emit, C.byref(s)))
+        z = int(s.count)
+        return src[:z].copy(), ln[:z].copy()

@@ -100,6 +100,12 @@ struct lz77sss_handle {
     uint64_t slice_len = 1ull << 28;
     uint32_t block_len = 2048;
     bool host_emit = false;
+    // sharded run (lz77sss_shard_*): what lz77sss_shard_prepare leaves for the range parses
+    bool prepare_only = false, prepared = false;
+    const uint8_t* host_text = nullptr;
+    std::vector<lpf_t> ML;
+    std::vector<uint64_t> ml_planes;
+    uint64_t table_entries = 0;
 };
 
 namespace {
@@ -738,6 +744,46 @@ uint64_t skip_gaps_emit(uint64_t n, const std::vector<lpf_t>& ML, lz77sss_emit_f
     return num;
 }
 
+// The last 65 positions (end-of-text rules of the gap index, rolling_hash_index_107.hpp:93,112,123,145) on the host,
+// from the state the device parse handed over, with the table entries of every bucket they can touch.
+uint64_t emit_tail(lz77sss_handle* h, const uint8_t* host_text, uint64_t n, const std::vector<lpf_t>& ML, const gap_params& g,
+                   bucket_provider& bp, const uint64_t ho[4], bool naive, lz77sss_emit_fn emit, void* ctx) {
+    auto& st = h->stats;
+    cudaStream_t s = h->st;
+    const uint64_t n_cut = n > 65 ? n - 65 : 0;
+    uint64_t z = 0;
+    {
+        // tail: table entries of every bucket the remaining positions can touch
+        // (greedy_naive: the host re-inserts position n_cut - 1, so that "table cursor == i" keeps its meaning)
+        const uint64_t tb = n_cut - (naive && n_cut > 0 ? 1 : 0);
+        bp.beg.push_back(tb);
+        bp.end.push_back(n);
+        bp.fetch_main();
+        std::vector<uint32_t> buckets;
+        buckets.push_back(0);
+        for (uint64_t pos = tb; pos < n; pos++)
+            for (int x = 0; x < 5; x++)
+                if (pos + g.patt_lens[x] <= n) buckets.push_back(bp.get(pos, x));
+        std::sort(buckets.begin(), buckets.end());
+        buckets.erase(std::unique(buckets.begin(), buckets.end()), buckets.end());
+        std::vector<uint64_t> vals(buckets.size());
+        gap_parse_query(h->gp, buckets.data(), (uint32_t)buckets.size(), vals.data(), s);
+        sparse_table H;
+        for (size_t q = 0; q < buckets.size(); q++) H.H[buckets[q]] = vals[q] ? vals[q] - 1 : ~0ull;
+        gap_index<sparse_table> idx(bp, H, n, g, 0);
+        if (n_cut > 0) {                           // the device parsed up to n - 65: every window fitted at its last
+            idx.cur_pos = ho[1];                   // reinit, so no fingerprint is stuck at zero
+            for (int x = 0; x < 5; x++) idx.zero[x] = false;
+            // greedy_naive: the device table already holds every position below n_cut
+            if (naive && ho[1] != ho[0]) idx.cur_pos = std::max<uint64_t>(ho[1], n_cut - 1);
+        }                                          // else (n <= 65): reinit(0) of the constructor set the flags
+        if (naive) z += greedy_naive_emit_from(host_text, n, ML, idx, ho[0], (size_t)ho[2], emit, ctx);
+        else z += greedy_emit_from(host_text, n, ML, g, idx, ho[0], (size_t)ho[2], emit, ctx);
+        st.d2h_bytes += 20 * bp.hashed + 8 * buckets.size();
+    }
+    return z;
+}
+
 template <typename pos_t>
 int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n,
                    lz77sss_emit_fn emit, void* ctx) {
@@ -852,6 +898,13 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     if (g.patt_lens[0] == 0) return fail(LZ77SSS_E_UNSUPPORTED, "degenerate phrase statistics (no LPF phrase or no gap): pattern lengths undefined in the reference (SURVEY.md A7)");
 
     const std::vector<lpf_t> ML = merged_phrase_list(h);
+    if (h->prepare_only) {                     // lz77sss_shard_prepare: the ranges are parsed by lz77sss_shard_parse
+        h->ML = ML;
+        h->table_entries = g.table_entries;
+        h->host_text = host_text;
+        h->prepared = true;
+        return LZ77SSS_OK;
+    }
     bucket_provider bp;
     bp.h = h;
     for (int x = 0; x < 5; x++) { bp.gp.patt_len[x] = g.patt_lens[x]; bp.gp.base[x] = h->cfg.gap_bases[x]; }
@@ -922,35 +975,7 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     t0 = clk::now();
     uint64_t z = h->f_src.size();
     for (uint64_t q = 0; q < z; q++) emit(ctx, h->f_src[q], h->f_len[q]);
-    if (ho[0] < n) {
-        // tail: table entries of every bucket the remaining positions can touch
-        // (greedy_naive: the host re-inserts position n_cut - 1, so that "table cursor == i" keeps its meaning)
-        const uint64_t tb = n_cut - (naive && n_cut > 0 ? 1 : 0);
-        bp.beg.push_back(tb);
-        bp.end.push_back(n);
-        bp.fetch_main();
-        std::vector<uint32_t> buckets;
-        buckets.push_back(0);
-        for (uint64_t pos = tb; pos < n; pos++)
-            for (int x = 0; x < 5; x++)
-                if (pos + g.patt_lens[x] <= n) buckets.push_back(bp.get(pos, x));
-        std::sort(buckets.begin(), buckets.end());
-        buckets.erase(std::unique(buckets.begin(), buckets.end()), buckets.end());
-        std::vector<uint64_t> vals(buckets.size());
-        gap_parse_query(h->gp, buckets.data(), (uint32_t)buckets.size(), vals.data(), s);
-        sparse_table H;
-        for (size_t q = 0; q < buckets.size(); q++) H.H[buckets[q]] = vals[q] ? vals[q] - 1 : ~0ull;
-        gap_index<sparse_table> idx(bp, H, n, g, 0);
-        if (n_cut > 0) {                           // the device parsed up to n - 65: every window fitted at its last
-            idx.cur_pos = ho[1];                   // reinit, so no fingerprint is stuck at zero
-            for (int x = 0; x < 5; x++) idx.zero[x] = false;
-            // greedy_naive: the device table already holds every position below n_cut
-            if (naive && ho[1] != ho[0]) idx.cur_pos = std::max<uint64_t>(ho[1], n_cut - 1);
-        }                                          // else (n <= 65): reinit(0) of the constructor set the flags
-        if (naive) z += greedy_naive_emit_from(host_text, n, ML, idx, ho[0], (size_t)ho[2], emit, ctx);
-        else z += greedy_emit_from(host_text, n, ML, g, idx, ho[0], (size_t)ho[2], emit, ctx);
-        st.d2h_bytes += 20 * bp.hashed + 8 * buckets.size();
-    }
+    if (ho[0] < n) z += emit_tail(h, host_text, n, ML, g, bp, ho, naive, emit, ctx);
     st.num_factors = z;
     st.t_emit_ns = ns_since(t0);
     return LZ77SSS_OK;
@@ -981,6 +1006,57 @@ int factorize_dispatch(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* 
                s.t_gap_hash_ns / 1e6, s.t_emit_ns / 1e6, s.t_total_ns / 1e6);
     }
     return rc;
+}
+
+gap_params stored_gap_params(const lz77sss_handle* h) {
+    gap_params g;
+    for (int x = 0; x < 5; x++) g.patt_lens[x] = h->stats.patt_lens[x];
+    g.roll_threshold = h->stats.roll_threshold;
+    g.table_entries = h->table_entries;
+    return g;
+}
+
+// One range of a sharded run: the device emission over [beg, end) from the given entry state and table.
+template <typename pos_t>
+int shard_parse_impl(lz77sss_handle* h, uint64_t beg, uint64_t end, const uint64_t entry[4], const uint64_t* d_table_in,
+                     uint64_t* d_table_out, uint64_t exit_state[4], uint64_t* num_factors) {
+    auto& P = pipe<pos_t>(h);
+    const uint64_t n = h->n;
+    const gap_params g = stored_gap_params(h);
+    gap_hash_params gpar;
+    for (int x = 0; x < 5; x++) { gpar.patt_len[x] = g.patt_lens[x]; gpar.base[x] = h->cfg.gap_bases[x]; }
+    gpar.mask = g.table_entries - 1;
+    const size_t m = h->ML.size();
+    if (h->ml_planes.size() != 3 * m) {
+        h->ml_planes.resize(3 * m);
+        for (size_t q = 0; q < m; q++) {
+            h->ml_planes[q] = h->ML[q].beg;
+            h->ml_planes[m + q] = h->ML[q].end;
+            h->ml_planes[2 * m + q] = h->ML[q].src;
+        }
+    }
+    h->f_src.clear();
+    h->f_len.clear();
+    gap_parse_range R;
+    R.beg = beg; R.end = end;
+    for (int k = 0; k < 4; k++) R.entry[k] = entry[k];
+    R.d_table_in = d_table_in;
+    R.d_table_out = d_table_out;
+    R.retain = true;
+    uint64_t ho[4];
+    const uint64_t n_cut = n > 65 ? n - 65 : 0;
+    auto t0 = clk::now();
+    gap_parse_run<pos_t>(h->d_text, n, h->cfg.tau, P.S.get(), P.s, P.suf, P.lce, gpar, g.table_entries, h->ml_planes.data(), m,
+                         n_cut, h->slice_len, h->block_len, h->gp, h->st, h->f_src, h->f_len, ho,
+                         h->cfg.fact_mode == LZ77SSS_FACT_GREEDY_NAIVE, &R);
+    h->stats.t_gap_hash_ns += ns_since(t0);
+    h->stats.parse_rounds += h->gp.rounds;
+    h->stats.parse_slices += h->gp.slices;
+    h->stats.gap_positions_hashed += h->gp.entries_sorted / 5;
+    h->stats.d2h_bytes += 16 * h->f_src.size();
+    for (int k = 0; k < 4; k++) exit_state[k] = ho[k];
+    if (num_factors) *num_factors = h->f_src.size();
+    return LZ77SSS_OK;
 }
 
 template <typename pos_t, typename out_t>
@@ -1127,6 +1203,100 @@ int lz77sss_factorize_approximate_device(lz77sss_handle* h, const uint8_t* d_tex
         int rc = factorize_dispatch(h, d_text, host_text, n, emit, ctx);
         h->cfg.pos_bits = saved.pos_bits == 0 ? 0 : h->cfg.pos_bits;
         return rc;
+    });
+}
+
+#define NEED_PREPARED() \
+    if (!h) return fail(LZ77SSS_E_ARG, "null handle"); \
+    if (!h->prepared) return fail(LZ77SSS_E_STATE, "lz77sss_shard_prepare has not run on this handle")
+
+int lz77sss_shard_prepare(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n) {
+    if (!h || !d_text || !host_text) return fail(LZ77SSS_E_ARG, "null argument");
+    if (h->cfg.fact_mode == LZ77SSS_FACT_SKIP_PHRASES) return fail(LZ77SSS_E_UNSUPPORTED, "skip_phrases has no gap index to shard");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        lz77sss_config saved = h->cfg;
+        if (h->cfg.pos_bits == 0) h->cfg.pos_bits = n <= 0xFFFFFFFFull ? 32 : 64;
+        h->prepared = false;
+        h->prepare_only = true;
+        h->gp.keep.clear();
+        h->ml_planes.clear();
+        auto nop = +[](void*, uint64_t, uint64_t) {};
+        int rc = factorize_dispatch(h, d_text, host_text, n, nop, nullptr);
+        h->prepare_only = false;
+        h->cfg.pos_bits = saved.pos_bits == 0 ? 0 : h->cfg.pos_bits;
+        h->stats.t_gap_hash_ns = 0;
+        return rc;
+    });
+}
+
+int lz77sss_shard_table_entries(lz77sss_handle* h, uint64_t* entries) {
+    NEED_PREPARED();
+    if (!entries) return fail(LZ77SSS_E_ARG, "null argument");
+    *entries = h->table_entries;
+    return LZ77SSS_OK;
+}
+
+int lz77sss_shard_entry_guess(lz77sss_handle* h, uint64_t pos, uint64_t state[4]) {
+    NEED_PREPARED();
+    if (!state || pos >= h->n) return fail(LZ77SSS_E_ARG, "bad argument");
+    // the speculation the blocks of a slice start from (gap_parse.cu, spec_entry_kernel)
+    const auto& ML = h->ML;
+    size_t lo = 0, hi = ML.size() - 1;              // first phrase with end > pos (the sentinel ends at n + 1)
+    while (lo < hi) {
+        const size_t mid = (lo + hi) / 2;
+        if (ML[mid].end > pos) hi = mid;
+        else lo = mid + 1;
+    }
+    state[0] = pos; state[1] = pos; state[3] = 1;
+    if (pos > 0 && ML[lo].beg < pos && h->cfg.fact_mode != LZ77SSS_FACT_GREEDY_NAIVE) {
+        state[0] = ML[lo].end;
+        state[1] = ML[lo].beg + 1 < state[0] ? ML[lo].beg + 1 : ML[lo].beg;
+        state[3] = 0;
+        while (lo + 1 < ML.size() && ML[lo].end <= state[0]) lo++;
+    }
+    state[2] = lo;
+    return LZ77SSS_OK;
+}
+
+int lz77sss_shard_parse(lz77sss_handle* h, uint64_t beg, uint64_t end, const uint64_t entry[4], const uint64_t* d_table_in,
+                        uint64_t* d_table_out, uint64_t exit_state[4], uint64_t* num_factors) {
+    NEED_PREPARED();
+    if (!entry || !exit_state || beg >= end || end > h->n) return fail(LZ77SSS_E_ARG, "bad argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        const unsigned long long l0 = g_kernel_launches;
+        int rc = h->pos_bytes == 4 ? shard_parse_impl<uint32_t>(h, beg, end, entry, d_table_in, d_table_out, exit_state, num_factors)
+                                   : shard_parse_impl<uint64_t>(h, beg, end, entry, d_table_in, d_table_out, exit_state, num_factors);
+        h->stats.kernel_launches += g_kernel_launches - l0;
+        return rc;
+    });
+}
+
+int lz77sss_shard_factors(lz77sss_handle* h, uint64_t* src, uint64_t* len, uint64_t cap, uint64_t* count) {
+    NEED_PREPARED();
+    const uint64_t z = h->f_src.size();
+    if (count) *count = z;
+    const uint64_t m = std::min(z, cap);
+    if (src) std::memcpy(src, h->f_src.data(), m * 8);
+    if (len) std::memcpy(len, h->f_len.data(), m * 8);
+    return LZ77SSS_OK;
+}
+
+int lz77sss_shard_finish(lz77sss_handle* h, const uint64_t state[4], lz77sss_emit_fn emit, void* ctx) {
+    NEED_PREPARED();
+    if (!state || !emit) return fail(LZ77SSS_E_ARG, "null argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        if (state[0] >= h->n) return LZ77SSS_OK;
+        const gap_params g = stored_gap_params(h);
+        bucket_provider bp;
+        bp.h = h;
+        for (int x = 0; x < 5; x++) { bp.gp.patt_len[x] = g.patt_lens[x]; bp.gp.base[x] = h->cfg.gap_bases[x]; }
+        bp.gp.mask = g.table_entries - 1;
+        h->stats.num_factors += emit_tail(h, h->host_text, h->n, h->ML, g, bp, state,
+                                          h->cfg.fact_mode == LZ77SSS_FACT_GREEDY_NAIVE, emit, ctx);
+        return LZ77SSS_OK;
     });
 }
 

@@ -623,7 +623,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                    lce_state<pos_t>& ls, const gap_hash_params& gp, uint64_t table_entries, const uint64_t* h_ml,
                    uint64_t m, uint64_t n_cut, uint64_t slice_len, uint32_t block_len, gap_parse_scratch& sc,
                    cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4],
-                   bool naive) {
+                   bool naive, const gap_parse_range* range) {
     static_assert(sizeof(block_state) == 32, "block_state layout");
     if (slice_len > (1ull << 28)) slice_len = 1ull << 28;
     if (block_len < 32) block_len = 32;
@@ -670,17 +670,41 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
     sc.ml.reserve(3 * m);
     CUDA_CHECK(cudaMemcpyAsync(sc.ml.get(), h_ml, 3 * m * 8, cudaMemcpyHostToDevice, st));
     sc.Hc.reserve(table_entries);
-    CUDA_CHECK(cudaMemsetAsync(sc.Hc.get(), 0, table_entries * 8, st));
+    if (range && range->d_table_in)
+        CUDA_CHECK(cudaMemcpyAsync(sc.Hc.get(), range->d_table_in, table_entries * 8, cudaMemcpyDeviceToDevice, st));
+    else
+        CUDA_CHECK(cudaMemsetAsync(sc.Hc.get(), 0, table_entries * 8, st));
     sc.changed.reserve(8);
     const bool dbg_rounds = getenv("LZ77SSS_DEBUG_ROUNDS") != nullptr;
     sc.slice_exit.reserve(sizeof(block_state));
 
     block_state first;
     first.i = 0; first.cur = 0; first.k = 0; first.gap = 1; first.pad = 0;
+    // A sharded run parses only [r_beg, r_end) from a given entry state and table, keeps the sorted
+    // entries and the traces of every slice, and resumes from them when the entry state or the table changed.
+    const uint64_t r_beg = range ? range->beg : 0, r_end = range ? range->end : n;
+    const bool retain = range && range->retain;
+    if (range) { first.i = range->entry[0]; first.cur = range->entry[1]; first.k = range->entry[2]; first.gap = (uint32_t)range->entry[3]; }
+    if (!retain) sc.keep.clear();
+    auto swap_keep = [&](slice_keep& K) {
+        std::swap(K.v0, sc.v0); std::swap(K.v1, sc.v1); std::swap(K.tkey, sc.tkey); std::swap(K.bstart, sc.bstart);
+        std::swap(K.entry, sc.entry); std::swap(K.exit_, sc.exit_); std::swap(K.marked, sc.marked); std::swap(K.ovr, sc.ovr);
+        std::swap(K.tr_cnt, sc.tr_cnt); std::swap(K.tr_pos, sc.tr_pos); std::swap(K.tr_src, sc.tr_src); std::swap(K.tr_len, sc.tr_len);
+    };
 
-    for (uint64_t a0 = 0; a0 < n; a0 += slice_len) {
-        const uint64_t a1 = a0 + slice_len < n ? a0 + slice_len : n;
+    size_t slice_no = 0;
+    for (uint64_t a0 = r_beg; a0 < r_end; a0 += slice_len, slice_no++) {
+        const uint64_t a1 = a0 + slice_len < r_end ? a0 + slice_len : r_end;
         if (first.i >= a1 && !first.gap && !naive) continue; // a phrase covers the whole slice: nothing is inserted
+        slice_keep* K = nullptr;
+        if (retain) {
+            while (sc.keep.size() <= slice_no) sc.keep.emplace_back(new slice_keep());
+            K = sc.keep[slice_no].get();
+            swap_keep(*K);
+        }
+        struct swap_back { slice_keep* K; decltype(swap_keep)& f; ~swap_back() { if (K) f(*K); } } guard{K, swap_keep};
+        const bool have_sorted = K && K->sorted;
+        const bool have_parse = K && K->parsed;
         const uint64_t cnt = a1 - a0;
         const uint32_t BL = block_len;
         const uint32_t nb = (uint32_t)((cnt + BL - 1) / BL);
@@ -693,7 +717,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         // phrases that overlap the slice (the sentinel is not one of them)
         const uint64_t k0 = std::upper_bound(h_ml + m, h_ml + m + (m - 1), a0) - (h_ml + m);
         const uint64_t k1 = std::lower_bound(h_ml, h_ml + (m - 1), a1) - h_ml;
-      for (int attempt = (naive || !sparse_ok) ? 1 : 0; attempt < 2; attempt++) {
+      for (int attempt = (naive || !sparse_ok || retain) ? 1 : 0; attempt < 2; attempt++) {
         bool sparse = attempt == 0;
         uint64_t E = 5 * cnt;
         if (sparse) {
@@ -723,6 +747,9 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         sc.bstart.reserve(table_entries + 4);
         sc.big.reserve(table_entries + 4);
         uint32_t *keys = sc.k0, *kalt = sc.k1, *vals = sc.v0, *valt = sc.v1;
+        if (have_sorted) {
+            vals = K->vals_in_v0 ? sc.v0.get() : sc.v1.get();
+        } else {
         {
             gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, vals,
                                                        sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
@@ -734,6 +761,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, sc.sort, st);
         bucket_start_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
         KERNEL_CHECK();
+        }
+        if (K) { K->sorted = true; K->vals_in_v0 = vals == sc.v0.get(); }
         }
         // per-block state
         sc.notins.reserve(nwords);
@@ -769,6 +798,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         const uint64_t stop = a1 < n_cut ? a1 : n_cut;
         bool converged = false;
         if (first.i < stop) {
+          if (!have_parse) {     // (a resumed slice starts from the traces and exit states of its last parse)
             // round 0: speculative entries
             spec_entry_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, first);
             KERNEL_CHECK();
@@ -789,6 +819,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
             KERNEL_CHECK();
             sc.rounds++;
+          }
+            if (K) K->parsed = true;
             for (uint64_t round = 1; round <= (uint64_t)nb + 4; round++) {
                 link_kernel<<<1, 1024, 0, st>>>(C, first, sc.J, levels, d_exit);
                 KERNEL_CHECK();
@@ -858,6 +890,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             first = ex;
         } else {
             // nothing to parse here, but positions up to first.i may have been inserted by a gap factor
+            if (K) K->parsed = false;
             CUDA_CHECK(cudaMemsetAsync(sc.marked.get(), 0, nb + 1, st));
             CUDA_CHECK(cudaMemsetAsync(sc.tr_cnt.get(), 0, (size_t)nb * 4, st));
             CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
@@ -882,6 +915,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         break;
       }
     }
+    if (range && range->d_table_out)
+        CUDA_CHECK(cudaMemcpyAsync(range->d_table_out, sc.Hc.get(), table_entries * 8, cudaMemcpyDeviceToDevice, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
     handover[0] = first.i;
     handover[1] = first.cur;
@@ -906,7 +941,8 @@ void gap_parse_query(gap_parse_scratch& sc, const uint32_t* h_buckets, uint32_t 
     template void gap_parse_run<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t, suffix_state<pos_t>&, \
                                        lce_state<pos_t>&, const gap_hash_params&, uint64_t, const uint64_t*, uint64_t,  \
                                        uint64_t, uint64_t, uint32_t, gap_parse_scratch&, cudaStream_t,                  \
-                                       std::vector<uint64_t>&, std::vector<uint64_t>&, uint64_t[4], bool);
+                                       std::vector<uint64_t>&, std::vector<uint64_t>&, uint64_t[4], bool,                 \
+                                       const gap_parse_range*);
 INST(uint32_t)
 INST(uint64_t)
 

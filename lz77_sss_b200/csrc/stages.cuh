@@ -1,5 +1,6 @@
 // Stage interfaces of the device pipeline (host-callable wrappers around the kernels).
 #pragma once
+#include <memory>
 #include <vector>
 #include "common.cuh"
 
@@ -103,6 +104,22 @@ void gap_bucket_ids(const uint8_t* d_text, uint64_t n, const gap_hash_params& gp
                     cudaStream_t st);
 
 // ---- gap_parse.cu: greedy phrase emission on the device ------------------------------------------------
+// per-slice buffers a sharded run keeps between its passes (sorted entries, traces, block states)
+struct slice_keep {
+    dbuf<uint32_t> v0, v1, tkey, bstart, tr_cnt, tr_pos;
+    dbuf<uint64_t> tr_src, tr_len;
+    dbuf<uint8_t> entry, exit_, marked, ovr;
+    bool sorted = false, parsed = false, vals_in_v0 = true;
+};
+// sharded run: parse only [beg, end) from the entry state {i, table cursor, phrase index, gap flag} and the table
+// d_table_in (last inserted position + 1 per bucket before beg; nullptr = empty), write the table behind end
+struct gap_parse_range {
+    uint64_t beg, end;
+    uint64_t entry[4];
+    const uint64_t* d_table_in;
+    uint64_t* d_table_out;
+    bool retain;               // keep the slices' sorted entries and traces; later calls with the same range resume
+};
 struct gap_parse_scratch {
     dbuf<uint32_t> k0, k1, v0, v1, tkey, bstart, big, notins, tr_cnt, tr_pos, changed, J, cnt;
     dbuf<uint64_t> tr_src, tr_len, ml, fsrc, flen;
@@ -112,6 +129,7 @@ struct gap_parse_scratch {
     sort_scratch sort;
     scan_scratch scan;
     uint64_t rounds = 0, slices = 0, entries_sorted = 0, sparse_slices = 0, sparse_fallbacks = 0;
+    std::vector<std::unique_ptr<slice_keep>> keep;
 };
 // h_ml: three planes (beg, end, src) of the merged phrase list incl. the sentinel {n, n+1, 0} (m entries).
 // Parses [0, n_cut); appends the factors to out_src/out_len; handover = {i, cur_pos, phrase index, gap flag}.
@@ -120,7 +138,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                    lce_state<pos_t>& ls, const gap_hash_params& gp, uint64_t table_entries, const uint64_t* h_ml,
                    uint64_t m, uint64_t n_cut, uint64_t slice_len, uint32_t block_len, gap_parse_scratch& sc,
                    cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4],
-                   bool naive = false);
+                   bool naive = false, const gap_parse_range* range = nullptr);
 // table entries (last inserted position + 1, 0 = none) of the given buckets after gap_parse_run
 void gap_parse_query(gap_parse_scratch& sc, const uint32_t* h_buckets, uint32_t cnt, uint64_t* h_out, cudaStream_t st);
 

@@ -1,0 +1,212 @@
+"""One text factorized by several GPUs: the host layer above the lz77sss_shard_* C ABI.
+
+One process per GPU (torch.distributed, NCCL over NVLink; gloo in the CPU tests of this file's logic).
+  1. every rank uploads its shard of the text and the shards are all-gathered, so each GPU holds the whole text;
+  2. every rank runs the replicated front of the pipeline (synchronizing set, SA_S, LPF phrases, gap parameters:
+     lz77sss_shard_prepare);
+  3. the gap index and the greedy emission (factorize_greedy, greedy.cpp:34-140) are split by text range.  A range is
+     parsed from an entry state and the table "last inserted position per bucket before the range".  Both are guesses
+     for every range but the first; after each pass the ranks exchange exit states (all-gather of 4 words) and the
+     per-range tables (all-gather of table_entries words), and the ranges whose inputs changed are parsed again
+     (resuming from the sorted entries and traces the handle kept).  When no input changes any more, every range was
+     parsed from the true state of the sequential algorithm, so the concatenated factors are the sequential stream;
+  4. the rank of the last range finishes the last 65 positions on the host; the factors are gathered on rank 0.
+Nothing here computes on text: it moves states and tables between ranks.  `backend` is the object that does the work
+(CudaBackend = the C ABI; the CPU tests plug in a small reference parser to exercise the exchange logic).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+FRONT_PAD = 256          # api.cu: readable zero bytes in front of the text
+TEXT_PAD = 65536         # stages.cuh: zero bytes behind it
+
+
+def split_ranges(n: int, world: int, align: int = 2048):
+    """world contiguous ranges covering [0, n), equal up to alignment; empty ranges at the end for tiny texts."""
+    per = -(-n // world)
+    per = -(-per // align) * align
+    out = []
+    for r in range(world):
+        b = min(n, r * per)
+        e = min(n, (r + 1) * per)
+        out.append((b, e))
+    return out
+
+
+def chain_entries(exits, ranges, first_entry):
+    """Entry state of every range from the exit states of the last pass: a range whose predecessor's parse already
+    ran past its end is passed through (its exit will be its entry), so its successor gets the same state now."""
+    entries = [tuple(first_entry)]
+    for r in range(1, len(ranges)):
+        prev_entry = entries[r - 1]
+        pb, pe = ranges[r - 1]
+        if pb >= pe or prev_entry[0] >= pe:        # empty or passed-through range: nothing starts inside it
+            entries.append(prev_entry)
+        else:
+            entries.append(tuple(int(x) for x in exits[r - 1]))
+    return entries
+
+
+class CudaBackend:
+    """The C ABI on this rank's GPU."""
+
+    def __init__(self, factorizer, device):
+        self.F = factorizer
+        self.device = device
+        self.text = None
+
+    def distribute_text(self, host_shard: np.ndarray, n: int, group=None):
+        """host_shard: this rank's bytes of the text (ranges of split_ranges(n, world, 1<<16)).  Returns the address of
+        T[0] in a padded device buffer that holds the whole text."""
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        per = split_ranges(n, world, 1 << 16)[0][1]
+        buf = torch.zeros(FRONT_PAD + per * world + TEXT_PAD, dtype=torch.uint8, device=self.device)
+        body = buf[FRONT_PAD:FRONT_PAD + per * world]
+        mine = torch.zeros(per, dtype=torch.uint8, device=self.device)
+        if host_shard.size:
+            mine[:host_shard.size].copy_(torch.from_numpy(host_shard), non_blocking=True)
+        if world > 1:
+            dist.all_gather_into_tensor(body, mine, group=group)
+        else:
+            body.copy_(mine)
+        buf[FRONT_PAD + n:].zero_()
+        torch.cuda.synchronize(self.device)
+        self.text = buf
+        return buf.data_ptr() + FRONT_PAD
+
+    def prepare(self, d_text_ptr, host_ptr, n):
+        self.F.shard_prepare(d_text_ptr, host_ptr, n)
+        return self.F.shard_table_entries()
+
+    def new_table(self, entries):
+        return torch.zeros(entries, dtype=torch.int64, device=self.device)
+
+    def entry_guess(self, pos):
+        return self.F.shard_entry_guess(pos)
+
+    def parse(self, beg, end, entry, table_in, table_out):
+        torch.cuda.synchronize(self.device)       # the tables were written on torch's stream
+        return self.F.shard_parse(beg, end, entry, table_in.data_ptr(), table_out.data_ptr())
+
+    def factors(self):
+        return self.F.shard_factors()
+
+    def finish(self, state):
+        return self.F.shard_finish(state)
+
+
+class TorchComm:
+    """The collectives of step 3/4 over torch.distributed (NCCL on the GPUs, gloo in the CPU tests)."""
+
+    def __init__(self, rank, world, device, group=None):
+        self.rank, self.world, self.device, self.group = rank, world, device, group
+
+    def all_gather(self, t):
+        if self.world == 1:
+            return [t]
+        out = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(out, t, group=self.group)
+        return out
+
+    def any(self, flag: bool) -> bool:
+        t = torch.tensor([1 if flag else 0], dtype=torch.int64, device=self.device)
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return bool(int(t.item()))
+
+
+class ThreadComm:
+    """Same interface for `world` virtual ranks running as threads of one process on one GPU (tests)."""
+
+    def __init__(self, rank, world, device, shared):
+        self.rank, self.world, self.device, self.sh = rank, world, device, shared
+
+    @staticmethod
+    def make_shared(world):
+        import threading
+        return {"barrier": threading.Barrier(world), "slots": [None] * world}
+
+    def all_gather(self, t):
+        if t.is_cuda:
+            torch.cuda.synchronize(t.device)
+        self.sh["slots"][self.rank] = t.clone()
+        self.sh["barrier"].wait()
+        out = [x.clone() for x in self.sh["slots"]]
+        self.sh["barrier"].wait()
+        return out
+
+    def any(self, flag: bool) -> bool:
+        got = self.all_gather(torch.tensor([1 if flag else 0], dtype=torch.int64))
+        return any(int(g.item()) for g in got)
+
+
+def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int, device, group=None, max_passes=None,
+                      log=None, comm=None):
+    """Steps 3 and 4 of the module docstring.  Returns (src, len, passes) on rank 0 and (None, None, passes) elsewhere."""
+    comm = comm or TorchComm(rank, world, device, group)
+    ranges = split_ranges(n, world)
+    beg, end = ranges[rank]
+    first_entry = (0, 0, 0, 1)
+    entry = first_entry if rank == 0 or beg >= n else backend.entry_guess(beg)
+    table_in = backend.new_table(table_entries)
+    table_out = backend.new_table(table_entries)
+    local = backend.new_table(table_entries)
+    exit_state = entry
+    passes = 0
+    need_parse = True
+    limit = max_passes if max_passes is not None else world + 2
+    while True:
+        if need_parse:
+            if beg < end:
+                exit_state, _ = backend.parse(beg, end, entry, table_in, table_out)
+                torch.where(table_out != table_in, table_out, torch.zeros_like(table_out), out=local)
+            else:
+                exit_state = entry
+                local.zero_()
+        passes += 1
+        # exchange: exit states and the per-range tables (last inserted position + 1 per bucket inside the range)
+        exits = [tuple(t.tolist()) for t in
+                 comm.all_gather(torch.tensor([int(x) for x in exit_state], dtype=torch.int64, device=device))]
+        gathered = comm.all_gather(local)
+        new_in = torch.zeros_like(table_in)
+        for r in range(rank):                      # positions grow with the rank: the maximum is the latest writer
+            torch.maximum(new_in, gathered[r], out=new_in)
+        new_entry = chain_entries(exits, ranges, first_entry)[rank]
+        changed = tuple(new_entry) != tuple(entry) or not torch.equal(new_in, table_in)
+        any_changed = comm.any(changed)
+        if log is not None:
+            log.append({"pass": passes, "changed_here": bool(changed), "parsed": bool(need_parse), "exit": exit_state})
+        if not any_changed:
+            break
+        if passes >= limit:
+            raise RuntimeError("sharded factorization did not reach its fixed point")   # cannot happen: rank r is final after pass r+1
+        need_parse = changed
+        if changed:
+            entry = tuple(new_entry)
+            table_in.copy_(new_in)
+    # step 4: factors of the own range (+ the tail on the last non-empty range), gathered on rank 0
+    if beg < end:
+        src, ln = backend.factors()
+    else:
+        src, ln = np.empty(0, np.uint64), np.empty(0, np.uint64)
+    last_rank = max(r for r in range(world) if ranges[r][0] < ranges[r][1])
+    if rank == last_rank and exit_state[0] < n:
+        ts, tl = backend.finish(exit_state)
+        src, ln = np.concatenate([src, ts]), np.concatenate([ln, tl])
+    if world == 1:
+        return src, ln, passes
+    counts = [int(c.item()) for c in comm.all_gather(torch.tensor([src.size], dtype=torch.int64, device=device))]
+    zmax = max(max(counts), 1)
+    mine = torch.zeros(2 * zmax, dtype=torch.int64, device=device)
+    if src.size:
+        mine[:src.size] = torch.from_numpy(src.astype(np.int64)).to(device)
+        mine[zmax:zmax + src.size] = torch.from_numpy(ln.astype(np.int64)).to(device)
+    parts = comm.all_gather(mine)
+    if rank != 0:
+        return None, None, passes
+    srcs = [parts[r][:counts[r]].cpu().numpy().astype(np.uint64) for r in range(world)]
+    lens = [parts[r][zmax:zmax + counts[r]].cpu().numpy().astype(np.uint64) for r in range(world)]
+    return np.concatenate(srcs), np.concatenate(lens), passes

@@ -183,6 +183,66 @@ def test_emission_variants_give_the_same_factors(capi, oracle, env, monkeypatch)
                 assert _eq(src, osrc) and _eq(ln, olen), (name, tau, fm, env)
 
 
+def _sharded_virtual(capi, text, world, tau, bases, fact_mode=None, env_slice=None):
+    """world virtual ranks (threads, one handle each) on cuda:0 through lz77_sss_b200.sharded."""
+    import threading
+    import torch
+    from lz77_sss_b200 import sharded
+    fact_mode = capi.FACT_GREEDY if fact_mode is None else fact_mode
+    n = text.size
+    dev = torch.device("cuda", 0)
+    shared = sharded.ThreadComm.make_shared(world)
+    res, err = [None] * world, []
+    host = np.ascontiguousarray(text)
+
+    def run(r):
+        try:
+            with capi.Factorizer(tau=tau, num_threads=1, gap_bases=bases, fact_mode=fact_mode) as F:
+                be = sharded.CudaBackend(F, dev)
+                d_ptr = be.distribute_text(host, n)          # world == 1 inside: every virtual rank uploads the whole text
+                entries = be.prepare(d_ptr, host.ctypes.data, n)
+                comm = sharded.ThreadComm(r, world, dev, shared)
+                res[r] = sharded.factorize_sharded(be, n, entries, r, world, dev, comm=comm)
+        except Exception as e:  # noqa: BLE001
+            err.append(e)
+            shared["barrier"].abort()
+
+    th = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join(timeout=600)
+    if err:
+        raise err[0]
+    return res[0]
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 5])
+def test_sharded_single_text_equals_sequential(capi, oracle, world):
+    """ranges of one text parsed by different ranks, states and tables exchanged until nothing changes."""
+    bases = (401, 70_001, 123_457, 999_983, 1_048_575)
+    for name, text in _texts().items():
+        if name in ("zeros", "period3"):
+            continue
+        for tau in (16, 512):
+            osrc, olen, _ = oracle.factorize(text, tau, bases, p_ref=1)
+            src, ln, passes = _sharded_virtual(capi, text, world, tau, bases)
+            assert _eq(src, osrc) and _eq(ln, olen), (name, tau, world, passes)
+
+
+def test_sharded_greedy_naive_and_small_slices(capi, oracle, monkeypatch):
+    monkeypatch.setenv("LZ77SSS_SLICE_LEN", "30000")      # several slices per range: the resumed passes walk them all
+    tau = 64
+    if not oracle.ref_available(tau):
+        pytest.skip("oracle/_ref was not prebuilt")
+    for name in ("rep", "dna", "xx"):
+        text = _texts()[name]
+        for fm in (oracle.GREEDY, oracle.GREEDY_NAIVE):
+            rs, rl, bases, _ = oracle.ref_factorize(text, tau, p=1, fact_mode=fm)
+            src, ln, _ = _sharded_virtual(capi, text, 3, tau, bases, fact_mode=fm)
+            assert _eq(src, rs) and _eq(ln, rl), (name, fm)
+
+
 def _check_factors(text, src, ln):
     n = text.size
     lens = np.maximum(ln, 1).astype(np.int64)
