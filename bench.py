@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--workload", default="dna", choices=["dna", "rep"])
     ap.add_argument("--cpu-sample-mib", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--independent", action="store_true",
+                    help="N > 1: every rank factorizes its own text (weak scaling) instead of sharding one text")
     return ap.parse_args()
 
 
@@ -144,6 +146,112 @@ def run_reference(args):
     }))
 
 
+def run_sharded(args, world, rank, local, barrier):
+    """N > 1: ONE text, sharded (lz77_sss_b200/sharded.py).  Strong scaling: the text is BASELINE's
+    configs[1] for every N.  value: shards resident in HBM, timed = all-gather of the shards + replicated front +
+    range parses with their exchanges + gather of the factors on rank 0.  e2e: the shards start in pinned host memory."""
+    import torch
+    import torch.distributed as dist
+    from lz77_sss_b200 import capi, sharded
+    dev = torch.device("cuda", local)
+    text = make_text(args, 0)                      # the same text on every rank; a rank only uploads its shard
+    n = text.size
+    sh_ranges = sharded.split_ranges(n, world, 1 << 16)
+    sb, se = sh_ranges[rank]
+    pinned = torch.empty(max(1, se - sb), dtype=torch.uint8).pin_memory()
+    pinned.numpy()[:se - sb] = text[sb:se]
+    per = sh_ranges[0][1]
+    F = capi.Factorizer(tau=args.tau, num_threads=1, gap_bases=capi.DEFAULT_GAP_BASES, device=local)
+    be = sharded.CudaBackend(F, dev)
+    buf = torch.zeros(sharded.FRONT_PAD + per * world + sharded.TEXT_PAD, dtype=torch.uint8, device=dev)
+    body = buf[sharded.FRONT_PAD:sharded.FRONT_PAD + per * world]
+    mine = torch.zeros(per, dtype=torch.uint8, device=dev)
+    d_ptr = buf.data_ptr() + sharded.FRONT_PAD
+    stats = {"launches": 0, "passes": 0, "z": 0, "h2d": 0, "d2h": 0}
+
+    def step(from_host):
+        if from_host:
+            mine[:se - sb].copy_(pinned[:se - sb], non_blocking=True)
+        dist.all_gather_into_tensor(body, mine)
+        buf[sharded.FRONT_PAD + n:].zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        entries = be.prepare(d_ptr, text.ctypes.data, n)
+        t1 = time.perf_counter()
+        log = []
+        src, ln, passes = sharded.factorize_sharded(be, n, entries, rank, world, dev, log=log)
+        if os.environ.get("LZ77SSS_BENCH_VERBOSE"):
+            print(f"rank {rank}: prepare {1e3 * (t1 - t0):.1f} ms, sharded {1e3 * (time.perf_counter() - t1):.1f} ms, {log}",
+                  file=sys.stderr, flush=True)
+        st = F.stats()
+        stats["launches"] += st["kernel_launches"]
+        stats["passes"] = passes
+        stats["h2d"] = (se - sb if from_host else 0) + st["h2d_bytes"]
+        stats["d2h"] = st["d2h_bytes"]
+        if rank == 0:
+            stats["z"] = int(src.size)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        stats["launches"] = 0
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps
+
+    mine[:se - sb].copy_(pinned[:se - sb])
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_res = timed(lambda: step(False), args.steps, args.warmup)
+    lt = torch.tensor([stats["launches"]], device="cuda", dtype=torch.int64)
+    dist.all_reduce(lt)
+    ms_e2e = timed(lambda: step(True), args.steps, max(1, args.warmup - 2))
+    clocks = sampler.stop()
+    st = F.stats()
+    k_ms, s_size = F.time_sss_kernel(C.c_void_p(d_ptr), n, iters=10)
+    hb = torch.tensor([stats["h2d"], stats["d2h"]], device="cuda", dtype=torch.int64)
+    dist.all_reduce(hb)
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        alg_bytes = n + 4 * s_size
+        achieved = alg_bytes / (k_ms / 1e3) / 1e9
+        out = {
+            "metric": METRIC, "value": (n / MIB) / (ms_res / 1e3), "unit": "MiB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_res, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": workload_name(args), "n_bytes": int(n), "tau": args.tau, "num_threads": 1,
+                       "parallelism": f"one text sharded over {world} GPUs: shards all-gathered (NCCL), replicated SSS/SA_S/LPF "
+                                      f"front, gap index + greedy emission split by text range, tables and exit states "
+                                      f"all-gathered between passes ({stats['passes']} passes)",
+                       "l2": "input (1 GiB) is larger than L2 (126 MB); no explicit flush", "factors": stats["z"],
+                       "size_sss": int(st["size_sss"])},
+            "e2e": {"value": (n / MIB) / (ms_e2e / 1e3), "unit": "MiB/s", "h2d_bytes_per_step": int(hb[0].item()),
+                    "d2h_bytes_per_step": int(hb[1].item()), "ms_per_step": ms_e2e},
+            "gpu_launches": int(lt.item()),
+            "roofline": {"kernel": "sss_kernel (fused window fingerprints + SSS selection)", "bound": "hbm",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                         "algorithmic_bytes": int(alg_bytes), "kernel_ms": k_ms, "traffic": None},
+            "phases_ms": {k[2:-3]: st[k] / 1e6 for k in st if k.startswith("t_")},
+            "clocks": clocks,
+        }
+        print(json.dumps(out))
+    barrier()
+    F.close()
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -166,6 +274,11 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if world > 1 and not args.independent:
+        run_sharded(args, world, rank, local, barrier)
+        dist.destroy_process_group()
+        return
 
     text = make_text(args, rank)
     n = text.size

@@ -117,6 +117,10 @@ int lz77sss_factorize_approximate_device(lz77sss_handle* h, const uint8_t* d_tex
 int lz77sss_shard_prepare(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n);
 int lz77sss_shard_table_entries(lz77sss_handle* h, uint64_t* entries);
 int lz77sss_shard_entry_guess(lz77sss_handle* h, uint64_t pos, uint64_t state[4]);
+/* optional, before the first lz77sss_shard_parse of a range: hash and sort its gap-index entries (kept for the parses) and
+ * write a GUESS of the range's table (last position per bucket among the positions the phrase list alone says are
+ * inserted); exchanged once, it gives the later ranges a nearly right table for their first parse */
+int lz77sss_shard_index(lz77sss_handle* h, uint64_t beg, uint64_t end, uint64_t* d_table_guess_out);
 int lz77sss_shard_parse(lz77sss_handle* h, uint64_t beg, uint64_t end, const uint64_t entry[4], const uint64_t* d_table_in,
                         uint64_t* d_table_out, uint64_t exit_state[4], uint64_t* num_factors);
 /* factors of the last lz77sss_shard_parse on this handle (HOST arrays) */

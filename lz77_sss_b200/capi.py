@@ -26,7 +26,7 @@ EXPORTS = [
     "lz77sss_time_sss_kernel", "lz77sss_get_stats", "lz77sss_get_sss", "lz77sss_get_sa_s", "lz77sss_get_lcp_s",
     "lz77sss_get_lpf", "lz77sss_lce_batch", "lz77sss_sink_emit",
     "lz77sss_shard_prepare", "lz77sss_shard_table_entries", "lz77sss_shard_entry_guess", "lz77sss_shard_parse",
-    "lz77sss_shard_factors", "lz77sss_shard_finish",
+    "lz77sss_shard_factors", "lz77sss_shard_finish", "lz77sss_shard_index",
 ]
 
 
@@ -96,6 +96,7 @@ def lib():
         L.lz77sss_shard_entry_guess.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.lz77sss_shard_parse.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p,
                                           C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.lz77sss_shard_index.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
         L.lz77sss_shard_factors.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.lz77sss_shard_finish.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
         _lib = L
@@ -274,6 +275,9 @@ class Factorizer:
         _check(lib().lz77sss_shard_parse(self._h, beg, end, e, C.c_void_p(table_in_ptr or None), C.c_void_p(table_out_ptr or None),
                                          x, C.byref(z)))
         return tuple(int(v) for v in x), int(z.value)
+
+    def shard_index(self, beg, end, table_guess_ptr):
+        _check(lib().lz77sss_shard_index(self._h, beg, end, C.c_void_p(table_guess_ptr)))
 
     def shard_factors(self):
         cnt = C.c_uint64(0)

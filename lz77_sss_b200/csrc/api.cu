@@ -1019,7 +1019,7 @@ gap_params stored_gap_params(const lz77sss_handle* h) {
 // One range of a sharded run: the device emission over [beg, end) from the given entry state and table.
 template <typename pos_t>
 int shard_parse_impl(lz77sss_handle* h, uint64_t beg, uint64_t end, const uint64_t entry[4], const uint64_t* d_table_in,
-                     uint64_t* d_table_out, uint64_t exit_state[4], uint64_t* num_factors) {
+                     uint64_t* d_table_out, uint64_t exit_state[4], uint64_t* num_factors, bool index_only = false) {
     auto& P = pipe<pos_t>(h);
     const uint64_t n = h->n;
     const gap_params g = stored_gap_params(h);
@@ -1043,6 +1043,7 @@ int shard_parse_impl(lz77sss_handle* h, uint64_t beg, uint64_t end, const uint64
     R.d_table_in = d_table_in;
     R.d_table_out = d_table_out;
     R.retain = true;
+    R.index_only = index_only;
     uint64_t ho[4];
     const uint64_t n_cut = n > 65 ? n - 65 : 0;
     auto t0 = clk::now();
@@ -1219,7 +1220,7 @@ int lz77sss_shard_prepare(lz77sss_handle* h, const uint8_t* d_text, const uint8_
         if (h->cfg.pos_bits == 0) h->cfg.pos_bits = n <= 0xFFFFFFFFull ? 32 : 64;
         h->prepared = false;
         h->prepare_only = true;
-        h->gp.keep.clear();
+        for (auto& K : h->gp.keep) K->sorted = K->parsed = false;     // the buffers stay, their contents are stale
         h->ml_planes.clear();
         auto nop = +[](void*, uint64_t, uint64_t) {};
         int rc = factorize_dispatch(h, d_text, host_text, n, nop, nullptr);
@@ -1268,6 +1269,21 @@ int lz77sss_shard_parse(lz77sss_handle* h, uint64_t beg, uint64_t end, const uin
         const unsigned long long l0 = g_kernel_launches;
         int rc = h->pos_bytes == 4 ? shard_parse_impl<uint32_t>(h, beg, end, entry, d_table_in, d_table_out, exit_state, num_factors)
                                    : shard_parse_impl<uint64_t>(h, beg, end, entry, d_table_in, d_table_out, exit_state, num_factors);
+        h->stats.kernel_launches += g_kernel_launches - l0;
+        return rc;
+    });
+}
+
+int lz77sss_shard_index(lz77sss_handle* h, uint64_t beg, uint64_t end, uint64_t* d_table_guess_out) {
+    NEED_PREPARED();
+    if (beg >= end || end > h->n) return fail(LZ77SSS_E_ARG, "bad argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        const unsigned long long l0 = g_kernel_launches;
+        const uint64_t entry[4] = {beg, beg, 0, 1};
+        uint64_t ex[4];
+        int rc = h->pos_bytes == 4 ? shard_parse_impl<uint32_t>(h, beg, end, entry, nullptr, d_table_guess_out, ex, nullptr, true)
+                                   : shard_parse_impl<uint64_t>(h, beg, end, entry, nullptr, d_table_guess_out, ex, nullptr, true);
         h->stats.kernel_launches += g_kernel_launches - l0;
         return rc;
     });

@@ -231,6 +231,8 @@ struct parse_ctx {
     const uint32_t* notins;    // bit = 1: position of the slice is NOT inserted
     const uint32_t* skip;      // sparse slice: bit = 1: the position has no entries (nullptr: every position has)
     uint8_t* ovr;              // per block: its parse needed entries that a sparse slice does not have
+    uint8_t* dirty;            // per block: an input of its parse (entry state, a bitmap bit or a table entry that one
+                               // of its probes can have read) changed since it was parsed
     const uint64_t* ml_beg;
     const uint64_t* ml_end;
     const uint64_t* ml_src;
@@ -298,7 +300,7 @@ template <typename pos_t>
 __global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce_view<pos_t> V) {
     const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     const unsigned lane = threadIdx.x & 31;
-    if (b >= C.nb || b < C.bmin || !C.marked[b]) return;
+    if (b >= C.nb || b < C.bmin || !C.marked[b] || !C.dirty[b]) return;
     const block_state st = C.entry[b];
     uint64_t i = st.i, cur = st.cur, k = st.k;
     uint32_t gap = st.gap;
@@ -369,6 +371,7 @@ __global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce
         C.exit_[b] = ex;
         C.tr_cnt[b] = t;
         C.ovr[b] = bad ? 1 : 0;
+        C.dirty[b] = 0;
         if (chg) {
             atomicOr(C.changed, 1u);
             atomicAdd(C.changed + 3, 1u);
@@ -387,6 +390,7 @@ __global__ void spec_entry_kernel(const parse_ctx C, block_state first) {
     block_state st;
     st.pad = 0;
     C.tr_cnt[b] = 0;
+    C.dirty[b] = 1;
     block_state z;
     z.i = z.cur = z.k = NONE64; z.gap = 0; z.pad = 0;
     C.exit_[b] = z;
@@ -452,13 +456,76 @@ __global__ void __launch_bounds__(1024) link_kernel(const parse_ctx C, block_sta
         __syncthreads();
     }
     if (b0 == nb && threadIdx.x == 0) *slice_exit = first;     // nothing to parse in this slice
+    auto assign = [&](uint32_t j, const block_state& v) {
+        const block_state o = C.entry[j];
+        if (o.i != v.i || o.cur != v.cur || o.k != v.k || o.gap != v.gap) {
+            C.entry[j] = v;
+            C.dirty[j] = 1;
+        }
+    };
     for (uint32_t b = threadIdx.x; b < nb; b += blockDim.x) {
-        if (b == b0) C.entry[b] = first;
+        if (b == b0) assign(b, first);
         if (C.marked[b]) {
             const uint32_t j = J[b];
-            if (j < nb) C.entry[j] = C.exit_[b];
+            if (j < nb) assign(j, C.exit_[b]);
             else *slice_exit = C.exit_[b];
         }
+    }
+}
+
+// Which blocks can see a changed bitmap bit: a probe walks its bucket list backwards until the first inserted
+// entry, so the entries BEHIND a flipped position, up to and including the first one that is inserted before and
+// after the change, are the only ones whose walk can reach it.
+__global__ void __launch_bounds__(256) dirty_from_bitmap_kernel(const parse_ctx C, const uint32_t* __restrict__ old_bm,
+                                                                uint64_t nwords) {
+    // one warp per 32 bitmap words; a changed word is handled by the whole warp, one lane per flipped bit
+    const uint64_t w0 = (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32;
+    const unsigned lane = threadIdx.x & 31;
+    if (w0 >= nwords) return;
+    const uint32_t* __restrict__ new_bm = C.notins;
+    const uint64_t cnt = C.a1 - C.a0;
+    uint32_t mine = 0;
+    if (w0 + lane < nwords) mine = old_bm[w0 + lane] ^ new_bm[w0 + lane];
+    unsigned todo = __ballot_sync(0xffffffffu, mine != 0);
+    while (todo) {
+        const int wl = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint32_t x = __shfl_sync(0xffffffffu, mine, wl);
+        if (!((x >> lane) & 1u)) continue;
+        const uint64_t rel = (w0 + wl) * 32 + lane;
+        if (rel >= cnt) continue;
+        if (C.skip && ((C.skip[rel >> 5] >> (rel & 31)) & 1u)) continue;
+        for (uint32_t pat = 0; pat < 5; pat++) {
+            const uint32_t e = 5u * (uint32_t)rel + pat;
+            const uint32_t b = C.tkey[e];
+            uint32_t l = C.bstart[b], h = C.bstart[b + 1];
+            if (l >= h) continue;
+            const uint32_t hi = h;
+            while (l + 1 < h) {
+                const uint32_t mid = (l + h) >> 1;
+                if (C.sval[mid] <= e) l = mid;
+                else h = mid;
+            }
+            for (uint32_t kk = l + 1; kk < hi; kk++) {
+                const uint32_t q = C.sval[kk] / 5u;
+                C.dirty[q / C.BL] = 1;
+                if (!not_inserted(old_bm, q) && !not_inserted(new_bm, q)) break;
+            }
+        }
+    }
+}
+
+// Same for a changed table entry (a resumed slice of a sharded run): the walks that fall through the whole list of
+// the bucket start at its first entries.
+__global__ void dirty_from_table_kernel(const parse_ctx C, const unsigned long long* __restrict__ old_tab,
+                                        const uint32_t* __restrict__ old_bm, uint32_t nbuckets) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nbuckets || old_tab[b] == C.Hc[b]) return;
+    const uint32_t hi = C.bstart[b + 1];
+    for (uint32_t kk = C.bstart[b]; kk < hi; kk++) {
+        const uint32_t q = C.sval[kk] / 5u;
+        C.dirty[q / C.BL] = 1;
+        if (!not_inserted(old_bm, q) && !not_inserted(C.notins, q)) break;
     }
 }
 
@@ -689,13 +756,15 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
     auto swap_keep = [&](slice_keep& K) {
         std::swap(K.v0, sc.v0); std::swap(K.v1, sc.v1); std::swap(K.tkey, sc.tkey); std::swap(K.bstart, sc.bstart);
         std::swap(K.entry, sc.entry); std::swap(K.exit_, sc.exit_); std::swap(K.marked, sc.marked); std::swap(K.ovr, sc.ovr);
+        std::swap(K.dirty, sc.dirty); std::swap(K.notins_prev, sc.notins_prev); std::swap(K.Hc_prev, sc.Hc_prev);
         std::swap(K.tr_cnt, sc.tr_cnt); std::swap(K.tr_pos, sc.tr_pos); std::swap(K.tr_src, sc.tr_src); std::swap(K.tr_len, sc.tr_len);
     };
 
     size_t slice_no = 0;
     for (uint64_t a0 = r_beg; a0 < r_end; a0 += slice_len, slice_no++) {
         const uint64_t a1 = a0 + slice_len < r_end ? a0 + slice_len : r_end;
-        if (first.i >= a1 && !first.gap && !naive) continue; // a phrase covers the whole slice: nothing is inserted
+        const bool index_only = range && range->index_only;
+        if (first.i >= a1 && !first.gap && !naive && !index_only) continue; // a phrase covers the whole slice: nothing is inserted
         slice_keep* K = nullptr;
         if (retain) {
             while (sc.keep.size() <= slice_no) sc.keep.emplace_back(new slice_keep());
@@ -764,8 +833,29 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         }
         if (K) { K->sorted = true; K->vals_in_v0 = vals == sc.v0.get(); }
         }
+        if (index_only) {
+            // speculative table of this range: last position per bucket among the positions that the phrase list
+            // alone says are inserted (everything but the inside of the phrases)
+            sc.notins.reserve(nwords);
+            CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
+            if (!naive && k1 > k0) {
+                skip_bits_kernel<<<ceil_div_u((k1 - k0) * 32, 128), 128, 0, st>>>(sc.ml.get(), sc.ml.get() + m, k0, k1, a0, a1, sc.notins, 1);
+                KERNEL_CHECK();
+            }
+            parse_ctx Ci{};
+            Ci.a0 = a0; Ci.a1 = a1; Ci.sval = vals; Ci.bstart = sc.bstart; Ci.notins = sc.notins;
+            CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 1, 0, 4, st));
+            carry_kernel<<<ceil_div_u(table_entries, 256), 256, 0, st>>>(Ci, (uint32_t)table_entries, sc.Hc.get(), sc.big, sc.changed.get() + 1);
+            KERNEL_CHECK();
+            carry_big_kernel<<<1184, 128, 0, st>>>(Ci, sc.Hc.get(), sc.big, sc.changed.get() + 1);
+            KERNEL_CHECK();
+            break;
+        }
         // per-block state
         sc.notins.reserve(nwords);
+        sc.notins_prev.reserve(nwords);
+        sc.dirty.reserve(nb + 1);
+        if (K) sc.Hc_prev.reserve(table_entries);
         sc.ovr.reserve(nb + 1);
         sc.entry.reserve((uint64_t)nb * sizeof(block_state));
         sc.exit_.reserve((uint64_t)nb * sizeof(block_state));
@@ -786,6 +876,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         C.notins = sc.notins;
         C.skip = sparse ? sc.skip.get() : nullptr;
         C.ovr = sc.ovr;
+        C.dirty = sc.dirty;
         C.ml_beg = sc.ml.get(); C.ml_end = sc.ml.get() + m; C.ml_src = sc.ml.get() + 2 * m; C.m = m;
         C.entry = reinterpret_cast<block_state*>(sc.entry.get());
         C.exit_ = reinterpret_cast<block_state*>(sc.exit_.get());
@@ -829,6 +920,23 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                     notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
                     KERNEL_CHECK();
                 }
+                // A resumed slice (sharded run, later passes) starts from a converged parse: few bits flip, and only
+                // the blocks whose probes can see a flipped bit (or a changed table entry, or a new entry state) are
+                // parsed again.  A fresh slice flips bits everywhere in its first rounds; following them costs more
+                // than it saves (measured), so there every block on the chain behind the first change is parsed.
+                if (have_parse) {
+                    if (!naive) {
+                        dirty_from_bitmap_kernel<<<ceil_div_u(nwords, 256), 256, 0, st>>>(C, sc.notins_prev, nwords);   // 8 warps x 32 words per CTA
+                        KERNEL_CHECK();
+                    }
+                } else {
+                    CUDA_CHECK(cudaMemsetAsync(sc.dirty.get(), 1, nb, st));
+                }
+                if (have_parse && round == 1) {     // resumed slice: the table in front of it may have changed too
+                    dirty_from_table_kernel<<<ceil_div_u(table_entries, 256), 256, 0, st>>>(C, sc.Hc_prev.get(), sc.notins_prev,
+                                                                                            (uint32_t)table_entries);
+                    KERNEL_CHECK();
+                }
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get(), 0, 4, st));
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 3, 0, 4, st));
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 4, 0xFF, 4, st));
@@ -844,10 +952,13 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                     fprintf(stderr, "slice %llu round %llu: %u of %u blocks changed, first %u\n", (unsigned long long)a0,
                             (unsigned long long)round, d[0], nb, d[1]);
                 }
+                if (have_parse || !chg)
+                    CUDA_CHECK(cudaMemcpyAsync(sc.notins_prev.get(), sc.notins.get(), nwords * 4, cudaMemcpyDeviceToDevice, st));
                 if (!chg) { converged = true; break; }
-                CUDA_CHECK(cudaMemcpy(&C.bmin, sc.changed.get() + 4, 4, cudaMemcpyDeviceToHost));
+                if (!have_parse) CUDA_CHECK(cudaMemcpy(&C.bmin, sc.changed.get() + 4, 4, cudaMemcpyDeviceToHost));
             }
             if (!converged) throw std::runtime_error("gap_parse: the block chain did not reach its fixed point");
+            if (K) CUDA_CHECK(cudaMemcpyAsync(sc.Hc_prev.get(), sc.Hc.get(), table_entries * 8, cudaMemcpyDeviceToDevice, st));
             // factors of the blocks on the chain, in order
             CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 2, 0, 4, st));
             count_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, sc.cnt);

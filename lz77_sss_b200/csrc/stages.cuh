@@ -108,7 +108,9 @@ void gap_bucket_ids(const uint8_t* d_text, uint64_t n, const gap_hash_params& gp
 struct slice_keep {
     dbuf<uint32_t> v0, v1, tkey, bstart, tr_cnt, tr_pos;
     dbuf<uint64_t> tr_src, tr_len;
-    dbuf<uint8_t> entry, exit_, marked, ovr;
+    dbuf<uint8_t> entry, exit_, marked, ovr, dirty;
+    dbuf<uint32_t> notins_prev;            // the bitmap the blocks were last parsed under
+    dbuf<unsigned long long> Hc_prev;      // the table in front of the slice at its last parse
     bool sorted = false, parsed = false, vals_in_v0 = true;
 };
 // sharded run: parse only [beg, end) from the entry state {i, table cursor, phrase index, gap flag} and the table
@@ -119,12 +121,15 @@ struct gap_parse_range {
     const uint64_t* d_table_in;
     uint64_t* d_table_out;
     bool retain;               // keep the slices' sorted entries and traces; later calls with the same range resume
+    bool index_only;           // only hash + sort the slices and write the speculative table of the range (no parse)
 };
 struct gap_parse_scratch {
     dbuf<uint32_t> k0, k1, v0, v1, tkey, bstart, big, notins, tr_cnt, tr_pos, changed, J, cnt;
     dbuf<uint64_t> tr_src, tr_len, ml, fsrc, flen;
     dbuf<unsigned long long> Hc;
-    dbuf<uint8_t> entry, exit_, marked, slice_exit, nbtab, ovr;
+    dbuf<uint8_t> entry, exit_, marked, slice_exit, nbtab, ovr, dirty;
+    dbuf<uint32_t> notins_prev;
+    dbuf<unsigned long long> Hc_prev;
     dbuf<uint32_t> skip, tile_off;         // sparse slices: positions without entries, compaction offsets per tile
     sort_scratch sort;
     scan_scratch scan;

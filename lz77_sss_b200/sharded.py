@@ -87,6 +87,10 @@ class CudaBackend:
     def entry_guess(self, pos):
         return self.F.shard_entry_guess(pos)
 
+    def index(self, beg, end, table_guess):
+        torch.cuda.synchronize(self.device)
+        self.F.shard_index(beg, end, table_guess.data_ptr())
+
     def parse(self, beg, end, entry, table_in, table_out):
         torch.cuda.synchronize(self.device)       # the tables were written on torch's stream
         return self.F.shard_parse(beg, end, entry, table_in.data_ptr(), table_out.data_ptr())
@@ -154,11 +158,21 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
     table_in = backend.new_table(table_entries)
     table_out = backend.new_table(table_entries)
     local = backend.new_table(table_entries)
+    # pass 0 (backends that can): index the own range and exchange guessed tables, so that the first parse of the
+    # later ranges already sees nearly the table it will end up with
+    if world > 1 and hasattr(backend, "index"):
+        if beg < end:
+            backend.index(beg, end, local)
+        guesses = comm.all_gather(local)
+        for r in range(rank):
+            torch.maximum(table_in, guesses[r], out=table_in)
     exit_state = entry
     passes = 0
     need_parse = True
     limit = max_passes if max_passes is not None else world + 2
+    import time
     while True:
+        t_a = time.perf_counter()
         if need_parse:
             if beg < end:
                 exit_state, _ = backend.parse(beg, end, entry, table_in, table_out)
@@ -167,6 +181,7 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
                 exit_state = entry
                 local.zero_()
         passes += 1
+        t_b = time.perf_counter()
         # exchange: exit states and the per-range tables (last inserted position + 1 per bucket inside the range)
         exits = [tuple(t.tolist()) for t in
                  comm.all_gather(torch.tensor([int(x) for x in exit_state], dtype=torch.int64, device=device))]
@@ -178,7 +193,8 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
         changed = tuple(new_entry) != tuple(entry) or not torch.equal(new_in, table_in)
         any_changed = comm.any(changed)
         if log is not None:
-            log.append({"pass": passes, "changed_here": bool(changed), "parsed": bool(need_parse), "exit": exit_state})
+            log.append({"pass": passes, "changed_here": bool(changed), "parsed": bool(need_parse), "exit": exit_state,
+                        "parse_ms": round((t_b - t_a) * 1e3, 2), "exchange_ms": round((time.perf_counter() - t_b) * 1e3, 2)})
         if not any_changed:
             break
         if passes >= limit:
