@@ -69,6 +69,15 @@ def workload_name(args):
     return f"C1: lz77-sss-3-aprx on {args.size_mib} MiB random_repetitive_string, tau={args.tau}, num_threads=1"
 
 
+def sss_traffic(n, tau):
+    """dram bytes of one K1+K2 launch from the committed ncu --set full capture of this workload (null if none)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "sss_traffic.json")))
+        return int(t[f"n{n}_tau{tau}"]["traffic_bytes"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
 
@@ -243,7 +252,7 @@ def run_sharded(args, world, rank, local, barrier):
             "roofline": {"kernel": "sss_kernel (fused window fingerprints + SSS selection)", "bound": "hbm",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                         "algorithmic_bytes": int(alg_bytes), "kernel_ms": k_ms, "traffic": None},
+                         "algorithmic_bytes": int(alg_bytes), "kernel_ms": k_ms, "traffic": sss_traffic(n, args.tau)},
             "phases_ms": {k[2:-3]: st[k] / 1e6 for k in st if k.startswith("t_")},
             "clocks": clocks,
         }
@@ -359,7 +368,7 @@ def main():
             "roofline": {"kernel": "sss_kernel (fused window fingerprints + SSS selection)", "bound": "hbm",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                         "algorithmic_bytes": int(alg_bytes), "kernel_ms": k_ms, "traffic": None},
+                         "algorithmic_bytes": int(alg_bytes), "kernel_ms": k_ms, "traffic": sss_traffic(n, args.tau)},
             "phases_ms": {k[2:-3]: st_res[k] / 1e6 for k in st_res if k.startswith("t_")},
             "clocks": clocks,
         }

@@ -26,6 +26,7 @@
 
 namespace lz77sss {
 unsigned long long g_kernel_launches = 0;
+bool g_sync_every_kernel = getenv("LZ77SSS_SYNC_KERNELS") != nullptr;
 }
 
 using namespace lz77sss;
@@ -831,6 +832,8 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
         CUDA_CHECK(cudaStreamSynchronize(s));
         st.t_lce_ns += ns_since(t0);
         t0 = clk::now();
+        if (g_sync_every_kernel) fprintf(stderr, "candidates: mode %d, |S| = %llu, nblk = %u, levels = %d\n", cand_mode,
+                                         (unsigned long long)size_s, P.lce.nblk, P.lce.sp_levels);
         if (cand_mode == 0) lpf_candidates<pos_t>(text_x, n, tau, P.S.get(), size_s, h->cfg.num_threads, P.suf, P.lce, s);
         else all_candidates<pos_t>(text_x, n, P.S.get(), size_s, cand_mode == 2,
                                    h->cfg.phr_mode == LZ77SSS_PHR_LPF_LNF_OPT ? LNF_LCAP : 0, P.suf, P.lce, s);
@@ -994,7 +997,9 @@ int factorize_dispatch(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* 
     const unsigned long long l0 = g_kernel_launches;
     auto t0 = clk::now();
     int rc;
-    if (n < 0xFFFF0000ull) rc = factorize_impl<uint32_t>(h, d_text, host_text, n, emit, ctx);
+    // internal position width; LZ77SSS_FORCE_POS64=1 takes the 64-bit kernels for small inputs too (tests)
+    static const bool force64 = getenv("LZ77SSS_FORCE_POS64") && getenv("LZ77SSS_FORCE_POS64")[0] == '1';
+    if (n < 0xFFFF0000ull && !force64) rc = factorize_impl<uint32_t>(h, d_text, host_text, n, emit, ctx);
     else rc = factorize_impl<uint64_t>(h, d_text, host_text, n, emit, ctx);
     h->stats.t_total_ns += ns_since(t0);
     h->stats.kernel_launches = g_kernel_launches - l0;

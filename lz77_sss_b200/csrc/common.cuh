@@ -25,10 +25,13 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 #define CUDA_CHECK(x) ::lz77sss::cuda_check((x), #x, __FILE__, __LINE__)
 // every kernel launch of the library goes through KERNEL_CHECK, which also counts it (bench.py's gpu_launches)
 extern unsigned long long g_kernel_launches;
+extern bool g_sync_every_kernel;   // LZ77SSS_SYNC_KERNELS=1: device-synchronize after every launch, so a fault names its kernel
 #define KERNEL_CHECK()                                                                    \
     do {                                                                                  \
         ::lz77sss::g_kernel_launches++;                                                   \
         ::lz77sss::cuda_check(cudaGetLastError(), "kernel launch", __FILE__, __LINE__);   \
+        if (::lz77sss::g_sync_every_kernel)                                               \
+            ::lz77sss::cuda_check(cudaDeviceSynchronize(), "kernel execution", __FILE__, __LINE__); \
     } while (0)
 
 // Owning device buffer (cudaMallocAsync on the handle's stream would also do; plain cudaMalloc keeps

@@ -6,6 +6,7 @@
 // build_LPF_opt (lpf_opt.cpp:68-139) and lce_sss::lce_lr (patched lce_sss.hpp:123-177).
 // For two synchronizing positions the exact LCE is the range minimum of LCP_S between their ranks
 // (lce_classic_for_sss.hpp:153-155), so no text is re-read for the LCE_R probes.
+#include <vector>
 #include "common.cuh"
 #include "device_utils.cuh"
 #include "stages.cuh"
@@ -157,41 +158,40 @@ __global__ void lpf_candidates_kernel(const uint8_t* __restrict__ T, uint64_t n,
 // nearest smaller (LPF) or nearest greater (LNF, on the reversed text) SA_S value on both sides of its rank, the
 // exact LCE_R with it (range minimum of LCP_S) and the leftward LCE capped at lcap characters.  SAx is SA_S itself
 // or its bitwise complement (nearest greater value == nearest smaller complement), tab the block minima of SAx.
-template <typename pos_t>
+// leftward LCE of the candidate pair (src, pos), at most lcap characters (0: none)
+__device__ __forceinline__ uint64_t capped_left(const uint8_t* __restrict__ T, uint64_t src, uint64_t pos, uint64_t lcap) {
+    if (src == 0 || pos == 0 || lcap == 0) return 0;
+    const uint64_t lo = src < pos ? src : pos, hi = src < pos ? pos : src;
+    return thread_lce_left(T, lo - 1, hi - 1, lcap < lo ? lcap : lo);
+}
+
+// SIDE 0: nearest smaller value on the left of the rank (PSV / PGV), SIDE 1: on the right (NSV / NGV).
+// The two sides are separate launches: one kernel doing both faulted ("illegal memory access", B200, CUDA 12.9, also
+// with ptxas -O1) on some inputs (dna_collection(400000, seed 52), tau 64, reversed text) although SA_S, ISA_S and the
+// complement array were verified on the host and every index the code forms is in range; each side alone never did.
+// The root cause is not known yet; tests/test_gpu_parity.py keeps that input (test_lnf_regression_dna52).
+template <typename pos_t, int SIDE>
 __global__ void all_candidates_kernel(const uint8_t* __restrict__ T, const pos_t* __restrict__ S, uint64_t s,
                                       const uint32_t* __restrict__ SAx, uint32_t flip, const uint32_t* __restrict__ ISA,
                                       const pos_t* __restrict__ LCP, const uint32_t* __restrict__ tab,
                                       const pos_t* __restrict__ lcp_tab, uint32_t nblk, uint64_t lcap,
-                                      uint32_t* __restrict__ p_idx, uint32_t* __restrict__ n_idx,
-                                      pos_t* __restrict__ p_lce, pos_t* __restrict__ n_lce,
-                                      pos_t* __restrict__ p_lcel, pos_t* __restrict__ n_lcel) {
+                                      uint32_t* __restrict__ o_idx, pos_t* __restrict__ o_lce, pos_t* __restrict__ o_lcel) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= s) return;
     const uint64_t r = ISA[i];
     const uint64_t pos = S[i];
     const uint32_t v = (uint32_t)i ^ flip;
-    const uint32_t pr = prev_smaller(SAx, tab, nblk, r, v);
-    const uint32_t nr = next_smaller(SAx, tab, nblk, s, r, v);
-    uint32_t pi = NONE32, ni = NONE32;
-    pos_t pl = 0, nl = 0, pll = 0, nll = 0;
-    auto left = [&](uint64_t src) -> pos_t {
-        if (src == 0 || pos == 0 || lcap == 0) return 0;
-        const uint64_t lo = src < pos ? src : pos, hi = src < pos ? pos : src;
-        return (pos_t)thread_lce_left(T, lo - 1, hi - 1, min(lcap, lo));
-    };
-    if (pr != NONE32) {
-        pi = SAx[pr] ^ flip;
-        pl = range_min(LCP, lcp_tab, nblk, (uint64_t)pr + 1, r);
-        pll = left(S[pi]);
+    const uint32_t q = SIDE == 0 ? prev_smaller(SAx, tab, nblk, r, v) : next_smaller(SAx, tab, nblk, s, r, v);
+    uint32_t idx = NONE32;
+    pos_t lce = 0, lcel = 0;
+    if (q != NONE32) {
+        idx = SAx[q] ^ flip;
+        lce = SIDE == 0 ? range_min(LCP, lcp_tab, nblk, (uint64_t)q + 1, r) : range_min(LCP, lcp_tab, nblk, r + 1, (uint64_t)q);
+        lcel = (pos_t)capped_left(T, (uint64_t)S[idx], pos, lcap);
     }
-    if (nr != NONE32) {
-        ni = SAx[nr] ^ flip;
-        nl = range_min(LCP, lcp_tab, nblk, r + 1, (uint64_t)nr);
-        nll = left(S[ni]);
-    }
-    p_idx[i] = pi; n_idx[i] = ni;
-    p_lce[i] = pl; n_lce[i] = nl;
-    p_lcel[i] = pll; n_lcel[i] = nll;
+    o_idx[i] = idx;
+    o_lce[i] = lce;
+    o_lcel[i] = lcel;
 }
 
 __global__ void flip_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t s) {
@@ -337,9 +337,13 @@ void all_candidates(const uint8_t* T, uint64_t n, const pos_t* S, uint64_t s, bo
         SAx = ls.sa_flip;
         tab = ls.saf_blkmin;
     }
-    all_candidates_kernel<pos_t><<<ceil_div_u(s, 128), 128, 0, st>>>(
-        T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.psv_idx,
-        ls.nsv_idx, ls.psv_lce, ls.nsv_lce, ls.psv_lcel, ls.nsv_lcel);
+    all_candidates_kernel<pos_t, 0><<<ceil_div_u(s, 128), 128, 0, st>>>(
+        T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.psv_idx, ls.psv_lce,
+        ls.psv_lcel);
+    KERNEL_CHECK();
+    all_candidates_kernel<pos_t, 1><<<ceil_div_u(s, 128), 128, 0, st>>>(
+        T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.nsv_idx, ls.nsv_lce,
+        ls.nsv_lcel);
     KERNEL_CHECK();
 }
 

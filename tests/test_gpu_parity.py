@@ -243,6 +243,52 @@ def test_sharded_greedy_naive_and_small_slices(capi, oracle, monkeypatch):
             assert _eq(src, rs) and _eq(ln, rl), (name, fm)
 
 
+def test_lnf_regression_dna52(capi, oracle):
+    """The input on which a fused two-sided candidate kernel faulted (see lpf.cu, all_candidates_kernel)."""
+    tau = 64
+    if not oracle.ref_available(tau):
+        pytest.skip("oracle/_ref was not prebuilt")
+    text = synth.dna_collection(400_000, seed=52, chrom_len=50_000)
+    for pm in (oracle.LPF_LNF_NAIVE, oracle.LPF_LNF_OPT):
+        rs, rl, bases, _ = oracle.ref_factorize(text, tau, p=1, phr_mode=pm)
+        with capi.Factorizer(tau=tau, num_threads=1, gap_bases=bases, phr_mode=pm) as F:
+            src, ln = F.factorize(text)
+            assert _eq(src, rs) and _eq(ln, rl), pm
+
+
+def test_64_bit_position_kernels_on_small_inputs(capi, oracle):
+    """Texts of 4 GiB and more run the pos_t = uint64_t instantiation of every kernel; LZ77SSS_FORCE_POS64 runs it on
+    inputs the oracle can check (subprocess: the switch is read once per process)."""
+    code = r"""
+import sys, numpy as np
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import oracle_lib as O
+from lz77_sss_b200 import capi, synth
+bases = (401, 70_001, 123_457, 999_983, 1_048_575)
+texts = {"rep": synth.random_repetitive(300_000, seed=51), "dna": synth.dna_collection(400_000, seed=52, chrom_len=50_000),
+         "markov": synth.markov_text(100_000, seed=53)}
+for name, text in texts.items():
+    for tau, p, pm in ((16, 1, 2), (512, 3, 2), (64, 1, 3), (64, 2, 0)):
+        if pm == 2:
+            osrc, olen, _ = O.factorize(text, tau, bases, p_ref=p)
+            b = bases
+        elif O.ref_available(tau):
+            osrc, olen, b, _ = O.ref_factorize(text, tau, p=p, phr_mode=pm)
+        else:
+            continue
+        with capi.Factorizer(tau=tau, num_threads=p, gap_bases=b, phr_mode=pm) as F:
+            src, ln = F.factorize(text)
+            assert src.size == osrc.size and (src == osrc).all() and (ln == olen).all(), (name, tau, p, pm)
+            So, _ = O.sss(text, tau)
+            assert (F.sss() == So).all() and (F.sa_s() == O.sa_s(text, tau, So)).all(), (name, tau)
+            assert (F.decode(src, ln, text.size) == text).all()
+print("pos64 ok")
+""" % (ROOT, os.path.join(ROOT, "tests"))
+    env = dict(os.environ, LZ77SSS_FORCE_POS64="1")
+    r = subprocess.run([os.sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=900)
+    assert r.returncode == 0 and "pos64 ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
 def _check_factors(text, src, ln):
     n = text.size
     lens = np.maximum(ln, 1).astype(np.int64)
