@@ -422,48 +422,46 @@ __global__ void spec_entry_kernel(const parse_ctx C, block_state first) {
     C.entry[b] = st;
 }
 
-// One CTA: follows the chain of blocks from the block that holds `first.i` by pointer doubling, marks the blocks
-// on it, hands every exit state to the block it lands in, and reports the state that leaves the slice.
-__global__ void __launch_bounds__(1024) link_kernel(const parse_ctx C, block_state first, uint32_t* __restrict__ J,
-                                                    int levels, block_state* __restrict__ slice_exit) {
+// Follows the chain of blocks from the block that holds `first.i` by pointer doubling, marks the blocks on it, hands
+// every exit state to the block it lands in, and reports the state that leaves the slice.  One grid-wide launch per
+// step (phase 0: successor of every block + reset of the marks; 1: J_l = J_{l-1} o J_{l-1}; 2: marked blocks mark
+// their 2^l-th successor, levels descending; 3: entries): ~2 levels launches of a few microseconds instead of one CTA
+// looping over all blocks (1.5 ms per round at 131072 blocks).
+__global__ void __launch_bounds__(256) link_phase_kernel(const parse_ctx C, block_state first, uint32_t* __restrict__ J,
+                                                         int l, int phase, block_state* __restrict__ slice_exit) {
     const uint32_t nb = C.nb, N = nb + 1;
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= N) return;
     const uint64_t stop = C.a1 < C.n_cut ? C.a1 : C.n_cut;
-    for (uint32_t b = threadIdx.x; b < N; b += blockDim.x) {
+    const uint32_t b0 = first.i < stop ? (uint32_t)((first.i - C.a0) / C.BL) : nb;
+    if (phase == 0) {
         uint32_t j = nb;
         if (b < nb) {
             const uint64_t x = C.exit_[b].i;
             if (x != NONE64 && x < stop) j = (uint32_t)((x - C.a0) / C.BL);
+            C.marked[b] = (b == b0);
         }
         J[b] = j;
-    }
-    __syncthreads();
-    for (int l = 1; l < levels; l++) {
+    } else if (phase == 1) {
         const uint32_t* src = J + (size_t)(l - 1) * N;
-        uint32_t* dst = J + (size_t)l * N;
-        for (uint32_t b = threadIdx.x; b < N; b += blockDim.x) dst[b] = src[src[b]];
-        __syncthreads();
-    }
-    const uint32_t b0 = first.i < stop ? (uint32_t)((first.i - C.a0) / C.BL) : nb;
-    for (uint32_t b = threadIdx.x; b < nb; b += blockDim.x) C.marked[b] = (b == b0);
-    __syncthreads();
-    for (int l = levels - 1; l >= 0; l--) {
-        const uint32_t* src = J + (size_t)l * N;
-        for (uint32_t b = threadIdx.x; b < nb; b += blockDim.x)
-            if (C.marked[b]) {
-                const uint32_t j = src[b];
-                if (j < nb) C.marked[j] = 1;
-            }
-        __syncthreads();
-    }
-    if (b0 == nb && threadIdx.x == 0) *slice_exit = first;     // nothing to parse in this slice
-    auto assign = [&](uint32_t j, const block_state& v) {
-        const block_state o = C.entry[j];
-        if (o.i != v.i || o.cur != v.cur || o.k != v.k || o.gap != v.gap) {
-            C.entry[j] = v;
-            C.dirty[j] = 1;
+        J[(size_t)l * N + b] = src[src[b]];
+    } else if (phase == 2) {
+        if (b < nb && C.marked[b]) {
+            const uint32_t j = J[(size_t)l * N + b];
+            if (j < nb) C.marked[j] = 1;
         }
-    };
-    for (uint32_t b = threadIdx.x; b < nb; b += blockDim.x) {
+    } else {
+        auto assign = [&](uint32_t j, const block_state& v) {
+            const block_state o = C.entry[j];
+            if (o.i != v.i || o.cur != v.cur || o.k != v.k || o.gap != v.gap) {
+                C.entry[j] = v;
+                C.dirty[j] = 1;
+            }
+        };
+        if (b == nb) {
+            if (b0 == nb) *slice_exit = first;     // nothing to parse in this slice
+            return;
+        }
         if (b == b0) assign(b, first);
         if (C.marked[b]) {
             const uint32_t j = J[b];
@@ -913,8 +911,21 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
           }
             if (K) K->parsed = true;
             for (uint64_t round = 1; round <= (uint64_t)nb + 4; round++) {
-                link_kernel<<<1, 1024, 0, st>>>(C, first, sc.J, levels, d_exit);
-                KERNEL_CHECK();
+                {
+                    const unsigned gl = ceil_div_u((uint64_t)nb + 1, 256);
+                    link_phase_kernel<<<gl, 256, 0, st>>>(C, first, sc.J, 0, 0, d_exit);
+                    KERNEL_CHECK();
+                    for (int l = 1; l < levels; l++) {
+                        link_phase_kernel<<<gl, 256, 0, st>>>(C, first, sc.J, l, 1, d_exit);
+                        KERNEL_CHECK();
+                    }
+                    for (int l = levels - 1; l >= 0; l--) {
+                        link_phase_kernel<<<gl, 256, 0, st>>>(C, first, sc.J, l, 2, d_exit);
+                        KERNEL_CHECK();
+                    }
+                    link_phase_kernel<<<gl, 256, 0, st>>>(C, first, sc.J, 0, 3, d_exit);
+                    KERNEL_CHECK();
+                }
                 CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
                 if (!naive) {
                     notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
