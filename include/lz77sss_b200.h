@@ -129,6 +129,23 @@ int lz77sss_shard_factors(lz77sss_handle* h, uint64_t* src, uint64_t* len, uint6
  * right after its final lz77sss_shard_parse: emits the remaining factors from `state` */
 int lz77sss_shard_finish(lz77sss_handle* h, const uint64_t state[4], lz77sss_emit_fn emit, void* ctx);
 
+/* ---- rabin_karp_substring<31, pos_t> (include/lz77_sss/data_structures/rabin_karp_substring.hpp:35-240), the fingerprint
+ * structure of the exact path's sample index (sample_index.hpp:139,373).  lz77sss_rks_create copies the text to the
+ * device and builds the fingerprints of all prefixes T[0..16k) modulo 2^31 - 1 for the given base (the reference draws
+ * it from std::random_device in [257, 2^31 - 2], :89-96).  Residues are canonical, so every value equals the
+ * reference's for the same base. */
+typedef struct lz77sss_rks lz77sss_rks;
+int lz77sss_rks_create(lz77sss_handle* h, const uint8_t* text, uint64_t n, uint64_t base, lz77sss_rks** out);
+void lz77sss_rks_destroy(lz77sss_rks* r);
+/* table[g] = fingerprint of T[0 .. 16 (g + 1)), g < ceil(n / 16) */
+int lz77sss_rks_table(lz77sss_rks* r, uint32_t* out, uint64_t cap, uint64_t* count);
+/* the reference's `fps` vector for sampling rate s (:131-171): fps[k] = fingerprint of T[0 .. min(k s, n)) */
+int lz77sss_rks_fps(lz77sss_rks* r, uint64_t s, uint32_t* out, uint64_t cap, uint64_t* count);
+/* batched rabin_karp_substring::substring(pos, len) (:223-239) */
+int lz77sss_rks_substring(lz77sss_rks* r, const uint64_t* pos, const uint64_t* len, uint64_t nq, uint32_t* out);
+/* re-run the build `iters` times on the resident text; mean time (CUDA events on the library's stream) */
+int lz77sss_rks_time_build(lz77sss_rks* r, int iters, double* ms_out, uint64_t* launches_out);
+
 /* lz77_sss<pos_t>::decode (algorithms/common.cpp:33-54): z factors -> n bytes into the HOST buffer out. */
 int lz77sss_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, uint64_t z, uint8_t* out, uint64_t n);
 

@@ -27,6 +27,8 @@ EXPORTS = [
     "lz77sss_get_lpf", "lz77sss_lce_batch", "lz77sss_sink_emit",
     "lz77sss_shard_prepare", "lz77sss_shard_table_entries", "lz77sss_shard_entry_guess", "lz77sss_shard_parse",
     "lz77sss_shard_factors", "lz77sss_shard_finish", "lz77sss_shard_index",
+    "lz77sss_rks_create", "lz77sss_rks_destroy", "lz77sss_rks_table", "lz77sss_rks_fps", "lz77sss_rks_substring",
+    "lz77sss_rks_time_build",
 ]
 
 
@@ -99,6 +101,13 @@ def lib():
         L.lz77sss_shard_index.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
         L.lz77sss_shard_factors.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.lz77sss_shard_finish.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
+        L.lz77sss_rks_create.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_void_p)]
+        L.lz77sss_rks_destroy.argtypes = [C.c_void_p]
+        L.lz77sss_rks_destroy.restype = None
+        L.lz77sss_rks_table.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_rks_fps.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_rks_substring.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+        L.lz77sss_rks_time_build.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -295,3 +304,51 @@ class Factorizer:
         _check(lib().lz77sss_shard_finish(self._h, st, emit, C.byref(s)))
         z = int(s.count)
         return src[:z].copy(), ln[:z].copy()
+
+
+class RabinKarpSubstring:
+    """rabin_karp_substring<31, pos_t> (rabin_karp_substring.hpp:35-240) built on the device of a Factorizer's handle."""
+
+    def __init__(self, factorizer, text, base):
+        self._F = factorizer
+        t = _u8(text)
+        self.n = t.size
+        self._r = C.c_void_p()
+        _check(lib().lz77sss_rks_create(factorizer._h, _ptr(t), t.size, int(base), C.byref(self._r)))
+
+    def close(self):
+        if self._r:
+            lib().lz77sss_rks_destroy(self._r)
+            self._r = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def table(self):
+        cnt = C.c_uint64(0)
+        _check(lib().lz77sss_rks_table(self._r, None, 0, C.byref(cnt)))
+        out = np.empty(max(1, cnt.value), dtype=np.uint32)
+        _check(lib().lz77sss_rks_table(self._r, _ptr(out), cnt.value, C.byref(cnt)))
+        return out[:cnt.value]
+
+    def fps(self, s):
+        cnt = C.c_uint64(0)
+        _check(lib().lz77sss_rks_fps(self._r, s, None, 0, C.byref(cnt)))
+        out = np.empty(max(1, cnt.value), dtype=np.uint32)
+        _check(lib().lz77sss_rks_fps(self._r, s, _ptr(out), cnt.value, C.byref(cnt)))
+        return out[:cnt.value]
+
+    def substring(self, pos, length):
+        pos = np.ascontiguousarray(pos, dtype=np.uint64)
+        length = np.ascontiguousarray(length, dtype=np.uint64)
+        out = np.empty(max(1, pos.size), dtype=np.uint32)
+        _check(lib().lz77sss_rks_substring(self._r, _ptr(pos), _ptr(length), pos.size, _ptr(out)))
+        return out[:pos.size]
+
+    def time_build(self, iters=10):
+        ms, launches = C.c_double(0), C.c_uint64(0)
+        _check(lib().lz77sss_rks_time_build(self._r, iters, C.byref(ms), C.byref(launches)))
+        return ms.value, int(launches.value)

@@ -109,6 +109,14 @@ struct lz77sss_handle {
     uint64_t table_entries = 0;
 };
 
+struct lz77sss_rks {
+    lz77sss_handle* h = nullptr;
+    dbuf<uint8_t> text;
+    uint8_t* d_text = nullptr;
+    rks_state st;
+    unsigned long long launches = 0;
+};
+
 namespace {
 
 int fail(int code, const std::string& msg) {
@@ -1317,6 +1325,101 @@ int lz77sss_shard_finish(lz77sss_handle* h, const uint64_t state[4], lz77sss_emi
         bp.gp.mask = g.table_entries - 1;
         h->stats.num_factors += emit_tail(h, h->host_text, h->n, h->ML, g, bp, state,
                                           h->cfg.fact_mode == LZ77SSS_FACT_GREEDY_NAIVE, emit, ctx);
+        return LZ77SSS_OK;
+    });
+}
+
+// ---- rabin_karp_substring<31, pos_t> (rabin_karp_substring.hpp:35-240) ----
+int lz77sss_rks_create(lz77sss_handle* h, const uint8_t* text, uint64_t n, uint64_t base, lz77sss_rks** out) {
+    if (!h || !out || (!text && n)) return fail(LZ77SSS_E_ARG, "null argument");
+    if (base < 257 || base > 0x7FFFFFFEull) return fail(LZ77SSS_E_ARG, "base must lie in [257, 2^31 - 2] (rabin_karp_substring.hpp:92-96)");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        auto R = std::make_unique<lz77sss_rks>();
+        R->h = h;
+        R->d_text = alloc_text(R->text, n, h->st);
+        if (n) CUDA_CHECK(cudaMemcpyAsync(R->d_text, text, n, cudaMemcpyHostToDevice, h->st));
+        const unsigned long long l0 = g_kernel_launches;
+        rks_build(R->d_text, n, (uint32_t)base, R->st, h->st);
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        R->launches = g_kernel_launches - l0;
+        *out = R.release();
+        return LZ77SSS_OK;
+    });
+}
+
+void lz77sss_rks_destroy(lz77sss_rks* r) {
+    if (!r) return;
+    cudaSetDevice(r->h->cfg.device);
+    delete r;
+}
+
+int lz77sss_rks_table(lz77sss_rks* r, uint32_t* out, uint64_t cap, uint64_t* count) {
+    if (!r) return fail(LZ77SSS_E_ARG, "null argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(r->h->cfg.device));
+        return copy_out<uint32_t, uint32_t>(r->st.pf.get(), r->st.ngran, out, cap, count, r->h->st);
+    });
+}
+
+int lz77sss_rks_fps(lz77sss_rks* r, uint64_t s, uint32_t* out, uint64_t cap, uint64_t* count) {
+    if (!r || s == 0) return fail(LZ77SSS_E_ARG, "bad argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(r->h->cfg.device));
+        const uint64_t cnt = (r->st.n + s - 1) / s + 1;          // div_ceil(n, s) + 1 entries (:97,131,154)
+        if (count) *count = cnt;
+        if (!out) return LZ77SSS_OK;
+        const uint64_t m = std::min(cnt, cap);
+        dbuf<uint32_t> d;
+        d.reserve(m + 1);
+        rks_fps(r->d_text, r->st, s, m, d, r->h->st);
+        CUDA_CHECK(cudaMemcpyAsync(out, d.get(), m * 4, cudaMemcpyDeviceToHost, r->h->st));
+        CUDA_CHECK(cudaStreamSynchronize(r->h->st));
+        return LZ77SSS_OK;
+    });
+}
+
+int lz77sss_rks_substring(lz77sss_rks* r, const uint64_t* pos, const uint64_t* len, uint64_t nq, uint32_t* out) {
+    if (!r || ((!pos || !len || !out) && nq)) return fail(LZ77SSS_E_ARG, "null argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(r->h->cfg.device));
+        if (!nq) return LZ77SSS_OK;
+        for (uint64_t k = 0; k < nq; k++)
+            if (pos[k] + len[k] > r->st.n || pos[k] + len[k] < pos[k]) return fail(LZ77SSS_E_ARG, "substring out of range");
+        dbuf<uint64_t> dq;
+        dbuf<uint32_t> dout;
+        dq.reserve(2 * nq);
+        dout.reserve(nq);
+        CUDA_CHECK(cudaMemcpyAsync(dq.get(), pos, nq * 8, cudaMemcpyHostToDevice, r->h->st));
+        CUDA_CHECK(cudaMemcpyAsync(dq.get() + nq, len, nq * 8, cudaMemcpyHostToDevice, r->h->st));
+        rks_substring_batch(r->d_text, r->st, dq.get(), dq.get() + nq, nq, dout, r->h->st);
+        CUDA_CHECK(cudaMemcpyAsync(out, dout.get(), nq * 4, cudaMemcpyDeviceToHost, r->h->st));
+        CUDA_CHECK(cudaStreamSynchronize(r->h->st));
+        return LZ77SSS_OK;
+    });
+}
+
+int lz77sss_rks_time_build(lz77sss_rks* r, int iters, double* ms_out, uint64_t* launches_out) {
+    if (!r || iters <= 0) return fail(LZ77SSS_E_ARG, "bad argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(r->h->cfg.device));
+        cudaEvent_t e0, e1;
+        CUDA_CHECK(cudaEventCreate(&e0));
+        CUDA_CHECK(cudaEventCreate(&e1));
+        double total = 0;
+        for (int it = -1; it < iters; it++) {
+            CUDA_CHECK(cudaEventRecord(e0, r->h->st));
+            rks_build(r->d_text, r->st.n, r->st.base, r->st, r->h->st);
+            CUDA_CHECK(cudaEventRecord(e1, r->h->st));
+            CUDA_CHECK(cudaEventSynchronize(e1));
+            float ms = 0;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+            if (it >= 0) total += ms;
+        }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        if (ms_out) *ms_out = total / iters;
+        if (launches_out) *launches_out = r->launches;
         return LZ77SSS_OK;
     });
 }

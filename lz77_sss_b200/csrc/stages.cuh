@@ -147,6 +147,18 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
 // table entries (last inserted position + 1, 0 = none) of the given buckets after gap_parse_run
 void gap_parse_query(gap_parse_scratch& sc, const uint32_t* h_buckets, uint32_t cnt, uint64_t* h_out, cudaStream_t st);
 
+// ---- rks.cu: rabin_karp_substring<31> (prefix fingerprints modulo 2^31 - 1, one per 16 bytes) ---------------------------
+struct rks_state {
+    dbuf<uint32_t> pf;           // pf[g] = fingerprint of T[0 .. 16 (g + 1))
+    dbuf<unsigned long long> status;   // per tile: (1 << 32 | aggregate) or (2 << 32 | inclusive value)
+    uint64_t n = 0, ngran = 0;
+    uint32_t base = 0;
+};
+void rks_build(const uint8_t* d_text, uint64_t n, uint32_t base, rks_state& R, cudaStream_t st);
+void rks_substring_batch(const uint8_t* d_text, const rks_state& R, const uint64_t* d_pos, const uint64_t* d_len, uint64_t nq,
+                         uint32_t* d_out, cudaStream_t st);
+void rks_fps(const uint8_t* d_text, const rks_state& R, uint64_t s, uint64_t cnt, uint32_t* d_out, cudaStream_t st);
+
 // ---- decode.cu ------------------------------------------------------------------------------------
 // parallel LZ77 decode: factors (src,len) with len == 0 meaning literal src; returns 0 or an error code
 int decode_factors(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uint8_t* d_out, uint64_t n,

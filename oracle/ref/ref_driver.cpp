@@ -110,6 +110,26 @@ int64_t refdrv_factorize_approximate(const uint8_t* text, uint64_t n, int phr_mo
     return z;
 }
 
+// rabin_karp_substring<31, uint32_t> (data_structures/rabin_karp_substring.hpp:35-240), built by the reference's own
+// constructor with p threads; the base it drew (from the pinned std::random_device) is returned so that the device
+// build can use the same one.  fps_out receives the reference's table for sampling rate s, qout[k] = substring(qpos[k], qlen[k]).
+int64_t refdrv_rks(const uint8_t* text, uint64_t n, uint64_t s, int p, uint64_t* base_out, uint32_t* fps_out,
+                   uint64_t fps_cap, const uint64_t* qpos, const uint64_t* qlen, uint64_t nq, uint32_t* qout) {
+    struct probe : rabin_karp_substring<31, uint32_t> {
+        using rabin_karp_substring<31, uint32_t>::rabin_karp_substring;
+        uint64_t base() const { return (uint64_t)this->b; }
+        const std::vector<uint32_t>& table() const { return this->fps; }
+    };
+    std::vector<char> buf(n + 64, 0);
+    std::memcpy(buf.data(), text, n);
+    probe R(buf.data(), (uint32_t)n, (uint32_t)s, (uint32_t)0, (uint16_t)p);
+    if (base_out) *base_out = R.base();
+    const auto& f = R.table();
+    for (uint64_t k = 0; k < f.size() && k < fps_cap; k++) fps_out[k] = f[k];
+    for (uint64_t k = 0; k < nq; k++) qout[k] = R.substring((uint32_t)qpos[k], (uint32_t)qlen[k]);
+    return (int64_t)f.size();
+}
+
 // lz77_sss<>::decode (algorithms/common.cpp:33-54)
 int refdrv_decode(const uint64_t* src, const uint64_t* len, uint64_t z, uint8_t* out, uint64_t n) {
     std::vector<lz77_sss<uint64_t>::factor> f(z);

@@ -185,6 +185,10 @@ def ref(tau):
         L.refdrv_factorize_approximate.argtypes = [_u8p, C.c_uint64, C.c_int, C.c_int, C.c_int, _u64p, _u64p, C.c_uint64,
                                                    C.POINTER(C.c_double)]
         L.refdrv_decode.argtypes = [_u64p, _u64p, C.c_uint64, _u8p, C.c_uint64]
+        _u32p_ = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+        L.refdrv_rks.restype = C.c_int64
+        L.refdrv_rks.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_uint64), _u32p_, C.c_uint64, _u64p, _u64p,
+                                 C.c_uint64, _u32p_]
         assert L.refdrv_tau() == tau
         _ref[tau] = L
     return _ref[tau]
@@ -209,3 +213,17 @@ def ref_decode(src, ln, n, tau=512):
     out = np.zeros(max(1, n), dtype=np.uint8)
     ref(tau).refdrv_decode(np.ascontiguousarray(src, dtype=np.uint64), np.ascontiguousarray(ln, dtype=np.uint64), len(src), out, n)
     return out[:n]
+
+
+def ref_rks(text, s, qpos, qlen, p=1, tau=512):
+    """The reference's rabin_karp_substring<31, uint32_t>: (base it drew, its fps table for rate s, substring(qpos, qlen))."""
+    t = _text(text)
+    qpos = np.ascontiguousarray(qpos, dtype=np.uint64)
+    qlen = np.ascontiguousarray(qlen, dtype=np.uint64)
+    cap = t.size // s + 3
+    fps = np.zeros(cap, dtype=np.uint32)
+    out = np.zeros(max(1, qpos.size), dtype=np.uint32)
+    base = C.c_uint64(0)
+    cnt = ref(tau).refdrv_rks(_pad1(t), t.size, s, p, C.byref(base), fps, cap, _pad1(qpos), _pad1(qlen), qpos.size, out)
+    assert 0 < cnt <= cap
+    return int(base.value), fps[:cnt].copy(), out[:qpos.size].copy()

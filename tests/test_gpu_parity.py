@@ -289,6 +289,63 @@ print("pos64 ok")
     assert r.returncode == 0 and "pos64 ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
 
 
+def _poly_prefix(text, base, upto):
+    """fingerprint of text[:upto] modulo 2^31 - 1, numpy (8 characters per step)."""
+    P = (1 << 31) - 1
+    h = 0
+    for c in text[:upto].tolist():
+        h = (h * base + c) % P
+    return h
+
+
+@pytest.mark.parametrize("n", [1, 2, 15, 16, 17, 31, 33, 1000, 16383, 16384, 16385, 70_000, 300_001])
+def test_rabin_karp_substring_against_reference(capi, oracle, n):
+    """rabin_karp_substring<31> (rabin_karp_substring.hpp:35-240): the reference's own table `fps` for several sampling
+    rates and its substring() on random queries, same base (drawn by the reference, pinned generator)."""
+    if not oracle.ref_available(512):
+        pytest.skip("oracle/_ref was not prebuilt")
+    rng = np.random.default_rng(n)
+    text = synth.random_repetitive(max(n, 64), seed=n)[:n] if n > 40 else rng.integers(0, 256, size=n).astype(np.uint8)
+    nq = 400
+    qpos = rng.integers(0, n, size=nq).astype(np.uint64)
+    qlen = np.minimum(rng.integers(0, max(2, n), size=nq).astype(np.uint64), np.uint64(n) - qpos)
+    qlen[:20] = np.minimum(rng.integers(1, 20, size=20).astype(np.uint64), np.uint64(n) - qpos[:20])
+    with capi.Factorizer(tau=512) as F:
+        for s in (16, 1, 7, 1000, 20_000):
+            base, fps, want = oracle.ref_rks(text, s, qpos, qlen, p=1 + (n % 3))
+            with capi.RabinKarpSubstring(F, text, base) as R:
+                got = R.fps(s)
+                assert _eq(got, fps), (n, s, "fps")
+                assert _eq(R.substring(qpos, qlen), want), (n, s, "substring")
+
+
+def test_rabin_karp_substring_large_prefix_scan(capi):
+    """48 MiB: more than 1024 tiles, so the single-CTA scan of the tile aggregates works on chunks; spot checks against
+    a direct evaluation and the algebra of the reference's own test (tests/test_rabin_karp_substring.cpp:74: concat)."""
+    n = 48 << 20
+    text = synth.dna_collection(n, seed=9, chrom_len=1 << 20)
+    base = 1_291_279_556
+    P = (1 << 31) - 1
+    with capi.Factorizer(tau=512) as F, capi.RabinKarpSubstring(F, text, base) as R:
+        tab = R.table()
+        assert tab.size == n // 16
+        for g in (0, 1, 1023, 1024, 5000, 70_000):
+            assert int(tab[g]) == _poly_prefix(text, base, 16 * (g + 1)), g
+        rng = np.random.default_rng(1)
+        # fp(T[a..c)) = fp(T[a..b)) * base^(c-b) + fp(T[b..c))
+        a = rng.integers(0, n - 3000, size=300).astype(np.uint64)
+        l1 = rng.integers(1, 1500, size=300).astype(np.uint64)
+        l2 = rng.integers(1, 1500, size=300).astype(np.uint64)
+        f1, f2, f12 = R.substring(a, l1), R.substring(a + l1, l2), R.substring(a, l1 + l2)
+        for k in range(300):
+            assert (int(f1[k]) * pow(base, int(l2[k]), P) + int(f2[k])) % P == int(f12[k])
+        # equal substrings of the collection have equal fingerprints: copies of the chromosome
+        far = R.substring(np.array([100, 100 + (1 << 20)], dtype=np.uint64), np.array([5, 5], dtype=np.uint64))
+        assert (text[100:105] == text[100 + (1 << 20):105 + (1 << 20)]).all() == (far[0] == far[1])
+        whole = R.substring(np.array([0], dtype=np.uint64), np.array([n], dtype=np.uint64))
+        assert int(whole[0]) == int(tab[-1])
+
+
 def _check_factors(text, src, ln):
     n = text.size
     lens = np.maximum(ln, 1).astype(np.int64)
@@ -332,4 +389,4 @@ def test_cpp_header_example_runs(capi, tmp_path):
     subprocess.run(cmd, check=True)
     env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(ROOT, "lz77_sss_b200"))
     r = subprocess.run([str(exe)], capture_output=True, text=True, env=env)
-    assert r.returncode == 0 and "decode ok" in r.stdout, r.stdout + r.stderr
+    assert r.returncode == 0 and "decode ok" in r.stdout and "rabin_karp_substring ok" in r.stdout, r.stdout + r.stderr
