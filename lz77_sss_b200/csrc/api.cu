@@ -69,7 +69,7 @@ struct pipeline {
     suffix_state<pos_t> suf;
     lce_state<pos_t> lce;
     hbuf<pos_t> hS, h_plce, h_nlce, h_plcel, h_nlcel;
-    hbuf<uint32_t> h_pidx, h_nidx;
+    hbuf<pos_t> h_psrc, h_nsrc;        // text position of the candidate's source, ~0 = none
     uint64_t s = 0;
 };
 
@@ -155,9 +155,11 @@ template <> pipeline<uint64_t>& pipe<uint64_t>(lz77sss_handle* h) { return h->p6
 // ---- host side of build_LPF_opt: the coverage chain (lpf_opt.cpp:46-145) over the device-computed candidates ----
 template <typename pos_t>
 void lpf_chain(lz77sss_handle* h, pipeline<pos_t>& P) {
+    constexpr pos_t NONEP = ~(pos_t)0;
     const uint64_t n = h->n, s = P.s;
     const uint32_t p = h->cfg.num_threads;
-    h->LPF.assign(p, {});
+    h->LPF.resize(p);
+    for (auto& v : h->LPF) v.clear();          // keeps the capacity of the last run
     const pos_t* S = P.hS.p;
     for (uint32_t i_p = 0; i_p < p; i_p++) {
         const uint64_t b = (uint64_t)i_p * (n / p);
@@ -170,8 +172,7 @@ void lpf_chain(lz77sss_handle* h, pipeline<pos_t>& P) {
             while (i + 1 < i_max && (uint64_t)S[i + 1] <= max_end) i++;
             const uint64_t lst_end = max_end, pos = S[i];
             lpf_t phr{0, 0, 0};
-            auto candidate = [&](uint32_t sidx, uint64_t lce, uint64_t lcel_max, bool is_psv) {
-                uint64_t src = S[sidx];
+            auto candidate = [&](uint64_t src, uint64_t lce, uint64_t lcel_max, bool is_psv) {
                 const uint64_t end = pos + lce;
                 if (end <= lst_end) return;
                 uint64_t beg = pos;
@@ -201,9 +202,9 @@ void lpf_chain(lz77sss_handle* h, pipeline<pos_t>& P) {
                     phr = {beg, end, src};
                 }
             };
-            if (P.h_pidx[i] != NONE32) candidate(P.h_pidx[i], P.h_plce[i], P.h_plcel[i], true);
-            if (P.h_nidx[i] != NONE32) {
-                candidate(P.h_nidx[i], P.h_nlce[i], P.h_nlcel[i], false);
+            if (P.h_psrc[i] != NONEP) candidate(P.h_psrc[i], P.h_plce[i], P.h_plcel[i], true);
+            if (P.h_nsrc[i] != NONEP) {
+                candidate(P.h_nsrc[i], P.h_nlce[i], P.h_nlcel[i], false);
                 if (phr.end - phr.beg > 1) out.push_back(phr);     // pushed only inside the NSV branch (lpf_opt.cpp:141-143)
             }
         }
@@ -214,9 +215,11 @@ void lpf_chain(lz77sss_handle* h, pipeline<pos_t>& P) {
 // then skip the synchronizing positions the phrase covers
 template <typename pos_t>
 void lpf_chain_naive(lz77sss_handle* h, pipeline<pos_t>& P) {
+    constexpr pos_t NONEP = ~(pos_t)0;
     const uint64_t n = h->n, s = P.s;
     const uint32_t p = h->cfg.num_threads;
-    h->LPF.assign(p, {});
+    h->LPF.resize(p);
+    for (auto& v : h->LPF) v.clear();          // keeps the capacity of the last run
     const pos_t* S = P.hS.p;
     for (uint32_t i_p = 0; i_p < p; i_p++) {
         const uint64_t b = (uint64_t)i_p * (n / p);
@@ -228,8 +231,8 @@ void lpf_chain_naive(lz77sss_handle* h, pipeline<pos_t>& P) {
         // the synchronizing position right behind every visited one is never visited
         for (uint64_t i = i_min; i < i_max; i++) {
             uint64_t src = 0, len = 0;
-            if (P.h_pidx[i] != NONE32 && (uint64_t)P.h_plce[i] > len) { src = S[P.h_pidx[i]]; len = P.h_plce[i]; }
-            if (P.h_nidx[i] != NONE32 && (uint64_t)P.h_nlce[i] > len) { src = S[P.h_nidx[i]]; len = P.h_nlce[i]; }
+            if (P.h_psrc[i] != NONEP && (uint64_t)P.h_plce[i] > len) { src = P.h_psrc[i]; len = P.h_plce[i]; }
+            if (P.h_nsrc[i] != NONEP && (uint64_t)P.h_nlce[i] > len) { src = P.h_nsrc[i]; len = P.h_nlce[i]; }
             const uint64_t pos = S[i];
             if (len > 0) out.push_back(lpf_t{pos, pos + len, src});
             do { i++; } while (i < i_max && (uint64_t)S[i] < pos + len);
@@ -244,6 +247,7 @@ void lpf_chain_naive(lz77sss_handle* h, pipeline<pos_t>& P) {
 constexpr uint64_t LNF_LCAP = 64;     // left extension computed with the candidates; longer ones go to the batch
 template <typename pos_t>
 void all_chain(lz77sss_handle* h, pipeline<pos_t>& P, const uint8_t* d_text, bool lnf, bool opt) {
+    constexpr pos_t NONEP = ~(pos_t)0;
     const uint64_t n = h->n, s = P.s;
     const uint32_t p = h->cfg.num_threads;
     const pos_t* S = P.hS.p;
@@ -267,9 +271,9 @@ void all_chain(lz77sss_handle* h, pipeline<pos_t>& P, const uint8_t* d_text, boo
         uint64_t lst_end[2] = {n, n}, lst_off[2] = {0, 0};
         for (uint64_t i = i_min; i < i_max; i++) {
             for (int side = 0; side < 2; side++) {
-                const uint32_t idx = side == 0 ? P.h_pidx[i] : P.h_nidx[i];
-                if (idx == NONE32) continue;
-                const uint64_t pos = S[i], src = S[idx];
+                const pos_t srcp = side == 0 ? P.h_psrc[i] : P.h_nsrc[i];
+                if (srcp == NONEP) continue;
+                const uint64_t pos = S[i], src = srcp;
                 const uint64_t off = lnf ? src - pos : pos - src;
                 if (pos < lst_end[side] && off == lst_off[side]) continue;
                 const uint64_t lce = side == 0 ? P.h_plce[i] : P.h_nlce[i];
@@ -845,23 +849,24 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
         if (cand_mode == 0) lpf_candidates<pos_t>(text_x, n, tau, P.S.get(), size_s, h->cfg.num_threads, P.suf, P.lce, s);
         else all_candidates<pos_t>(text_x, n, P.S.get(), size_s, cand_mode == 2,
                                    h->cfg.phr_mode == LZ77SSS_PHR_LPF_LNF_OPT ? LNF_LCAP : 0, P.suf, P.lce, s);
+        candidate_sources<pos_t>(P.S.get(), size_s, P.lce, s);
         CUDA_CHECK(cudaStreamSynchronize(s));
         st.t_lpf_ns += ns_since(t0);
 
         // candidates to the host
         t0 = clk::now();
         if (size_s) {
-            P.hS.reserve(size_s); P.h_pidx.reserve(size_s); P.h_nidx.reserve(size_s);
+            P.hS.reserve(size_s); P.h_psrc.reserve(size_s); P.h_nsrc.reserve(size_s);
             P.h_plce.reserve(size_s); P.h_nlce.reserve(size_s); P.h_plcel.reserve(size_s); P.h_nlcel.reserve(size_s);
             CUDA_CHECK(cudaMemcpyAsync(P.hS.p, P.S.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
-            CUDA_CHECK(cudaMemcpyAsync(P.h_pidx.p, P.lce.psv_idx.get(), size_s * 4, cudaMemcpyDeviceToHost, s));
-            CUDA_CHECK(cudaMemcpyAsync(P.h_nidx.p, P.lce.nsv_idx.get(), size_s * 4, cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(P.h_psrc.p, P.lce.psv_src.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(P.h_nsrc.p, P.lce.nsv_src.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
             CUDA_CHECK(cudaMemcpyAsync(P.h_plce.p, P.lce.psv_lce.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
             CUDA_CHECK(cudaMemcpyAsync(P.h_nlce.p, P.lce.nsv_lce.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
             CUDA_CHECK(cudaMemcpyAsync(P.h_plcel.p, P.lce.psv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
             CUDA_CHECK(cudaMemcpyAsync(P.h_nlcel.p, P.lce.nsv_lcel.get(), size_s * sizeof(pos_t), cudaMemcpyDeviceToHost, s));
             CUDA_CHECK(cudaStreamSynchronize(s));
-            st.d2h_bytes += size_s * (8 + 5 * sizeof(pos_t));
+            st.d2h_bytes += size_s * 7 * sizeof(pos_t);
         }
         st.t_d2h_ns += ns_since(t0);
     };

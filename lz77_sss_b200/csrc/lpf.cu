@@ -369,6 +369,25 @@ void lce_r_batch(const uint8_t* T, uint64_t n, uint32_t tau, const pos_t* S, uin
     KERNEL_CHECK();
 }
 
+template <typename pos_t>
+__global__ void candidate_sources_kernel(const pos_t* __restrict__ S, uint64_t s, const uint32_t* __restrict__ pidx,
+                                         const uint32_t* __restrict__ nidx, pos_t* __restrict__ psrc,
+                                         pos_t* __restrict__ nsrc) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s) return;
+    const uint32_t a = pidx[i], b = nidx[i];
+    psrc[i] = a == NONE32 ? (pos_t)~(pos_t)0 : S[a];
+    nsrc[i] = b == NONE32 ? (pos_t)~(pos_t)0 : S[b];
+}
+
+template <typename pos_t>
+void candidate_sources(const pos_t* d_S, uint64_t s, lce_state<pos_t>& ls, cudaStream_t st) {
+    if (!s) return;
+    ls.psv_src.reserve(s); ls.nsv_src.reserve(s);
+    candidate_sources_kernel<pos_t><<<ceil_div_u(s, 256), 256, 0, st>>>(d_S, s, ls.psv_idx, ls.nsv_idx, ls.psv_src, ls.nsv_src);
+    KERNEL_CHECK();
+}
+
 #define INST(pos_t)                                                                                                    \
     template void build_lce_structures<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t,              \
                                               suffix_state<pos_t>&, lce_state<pos_t>&, cudaStream_t);                  \
@@ -376,6 +395,7 @@ void lce_r_batch(const uint8_t* T, uint64_t n, uint32_t tau, const pos_t* S, uin
                                         suffix_state<pos_t>&, lce_state<pos_t>&, cudaStream_t);                        \
     template void all_candidates<pos_t>(const uint8_t*, uint64_t, const pos_t*, uint64_t, bool, uint64_t,              \
                                         suffix_state<pos_t>&, lce_state<pos_t>&, cudaStream_t);                        \
+    template void candidate_sources<pos_t>(const pos_t*, uint64_t, lce_state<pos_t>&, cudaStream_t);                 \
     template void lce_r_batch<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t, suffix_state<pos_t>&, \
                                      lce_state<pos_t>&, const uint64_t*, const uint64_t*, uint64_t, uint64_t*,         \
                                      cudaStream_t);

@@ -63,6 +63,7 @@ struct lce_state {
     uint64_t succ_nb = 0;
     // per synchronizing position: the two LPF candidates
     dbuf<uint32_t> psv_idx, nsv_idx;       // sync index of the source or NONE32
+    dbuf<pos_t> psv_src, nsv_src;          // its text position S[idx], or ~0 (candidate_sources)
     dbuf<pos_t> psv_lce, nsv_lce, psv_lcel, nsv_lcel;
     dbuf<uint32_t> sa_flip, saf_blkmin;    // ~SA and its block minima (nearest GREATER values for build_LNF_all)
     scan_scratch scan;
@@ -74,6 +75,9 @@ void build_lce_structures(const uint8_t* d_text, uint64_t n, uint32_t tau, const
 template <typename pos_t>
 void lpf_candidates(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, uint32_t p_ref,
                     suffix_state<pos_t>& ss, lce_state<pos_t>& ls, cudaStream_t st);
+// psv_src / nsv_src from psv_idx / nsv_idx: the host chains read positions, not indices into S
+template <typename pos_t>
+void candidate_sources(const pos_t* d_S, uint64_t s, lce_state<pos_t>& ls, cudaStream_t st);
 // candidates for build_LPF_all (greater = false) / build_LNF_all (greater = true, text reversed), lpf_lnf.cpp:34-249:
 // nearest smaller / greater SA_S value on both sides, exact LCE_R, leftward LCE capped at lcap
 template <typename pos_t>

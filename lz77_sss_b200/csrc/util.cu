@@ -134,16 +134,17 @@ __global__ void iota_u32_kernel(uint32_t* d, uint64_t n) {
 // One LSD pass = histogram per tile, device scan of hist[digit][tile], scatter.  The scatter ranks its tile
 // with per-warp match_any counting (stable), reorders the tile in shared memory by digit and writes every
 // digit's run with consecutive threads, so global stores are coalesced runs instead of single scattered words.
+// A pass takes a digit of up to 9 bits (NB = 256 or 512 bins): the bits of a sort are split into the fewest passes.
 constexpr int RS_NT = 256;
 constexpr int RS_NW = RS_NT / 32;
 template <typename K> struct rs_cfg { static constexpr int IPT = sizeof(K) == 4 ? 16 : 8; };
 
-template <typename K>
+template <typename K, int NB>
 __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ keys, uint64_t n, int shift,
                                                         uint32_t mask, uint32_t* __restrict__ hist, uint32_t ntiles) {
     constexpr int TILE = RS_NT * rs_cfg<K>::IPT;
-    __shared__ uint32_t cnt[256];
-    cnt[threadIdx.x] = 0;
+    __shared__ uint32_t cnt[NB];
+    for (int d = threadIdx.x; d < NB; d += RS_NT) cnt[d] = 0;
     __syncthreads();
     uint64_t base = (uint64_t)blockIdx.x * TILE;
 #pragma unroll
@@ -152,58 +153,74 @@ __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ ke
         if (i < n) atomicAdd(&cnt[(uint32_t)(keys[i] >> shift) & mask], 1u);
     }
     __syncthreads();
-    hist[(uint64_t)threadIdx.x * ntiles + blockIdx.x] = cnt[threadIdx.x];
+    for (int d = threadIdx.x; d < NB; d += RS_NT) hist[(uint64_t)d * ntiles + blockIdx.x] = cnt[d];
 }
 
-template <typename K>
-__global__ void __launch_bounds__(RS_NT) rs_scatter_kernel(const K* __restrict__ keys,
+template <typename K, int NB>
+__global__ void __launch_bounds__(RS_NT, 4) rs_scatter_kernel(const K* __restrict__ keys,
                                                            const uint32_t* __restrict__ vals,
                                                            K* __restrict__ okeys, uint32_t* __restrict__ ovals,
                                                            uint64_t n, int shift, uint32_t mask,
                                                            const uint32_t* __restrict__ offs, uint32_t ntiles) {
     constexpr int IPT = rs_cfg<K>::IPT;
     constexpr int TILE = RS_NT * IPT;
-    __shared__ uint32_t cnt[RS_NW][256];
-    __shared__ uint32_t dstart[256];      // tile-local start of every digit
-    __shared__ uint32_t goff[256];        // global offset of the tile's first item of every digit
+    constexpr int DPT = NB / RS_NT;       // digits per thread in the scan of the digit totals
+    __shared__ uint16_t cnt[RS_NW][NB];   // a warp holds at most 32 * IPT items
+    __shared__ uint16_t dstart[NB];       // tile-local start of every digit
+    __shared__ uint32_t goff[NB];         // global offset of the tile's first item of every digit
     __shared__ K skeys[TILE];
     __shared__ uint32_t svals[TILE];
     __shared__ uint32_t wsum[RS_NW];
     const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < RS_NW * 256; i += RS_NT) (&cnt[0][0])[i] = 0;
+    for (int i = threadIdx.x; i < RS_NW * NB / 2; i += RS_NT) reinterpret_cast<uint32_t*>(&cnt[0][0])[i] = 0;
     __syncthreads();
     const uint64_t tbase = (uint64_t)blockIdx.x * TILE;
     const uint64_t base = tbase + (uint64_t)w * (32 * IPT);
     const uint32_t in_tile = n - tbase < (uint64_t)TILE ? (uint32_t)(n - tbase) : (uint32_t)TILE;
+    const uint32_t in_warp = in_tile > w * (32 * IPT) ? in_tile - w * (32 * IPT) : 0;      // items of this warp
     K key[IPT];
-    uint32_t val[IPT], rank[IPT], dig[IPT];
+    uint32_t val[IPT];
+    uint32_t rank2[IPT / 2];              // rank inside the warp's items of the same digit, two per word
 #pragma unroll
     for (int k = 0; k < IPT; k++) {
-        uint64_t i = base + (uint64_t)k * 32 + lane;
-        bool valid = i < n;
-        key[k] = valid ? keys[i] : (K)~(K)0;
-        val[k] = valid ? vals[i] : 0;
-        uint32_t d = valid ? ((uint32_t)(key[k] >> shift) & mask) : 256u;   // 256 = "no item"
-        dig[k] = d;
-        unsigned peers = __match_any_sync(0xffffffffu, d);
+        const bool valid = (uint32_t)(k * 32) + lane < in_warp;
+        key[k] = valid ? keys[base + (uint64_t)k * 32 + lane] : (K)~(K)0;
+    }
+#pragma unroll
+    for (int k = 0; k < IPT; k++) {
+        const bool valid = (uint32_t)(k * 32) + lane < in_warp;
+        const uint32_t d = valid ? ((uint32_t)(key[k] >> shift) & mask) : (uint32_t)NB;   // NB = "no item"
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
         uint32_t old = 0;
         if (valid) old = cnt[w][d];
         __syncwarp();
-        if (valid && lane == (unsigned)(__ffs(peers) - 1)) cnt[w][d] = old + __popc(peers);
+        if (valid && lane == (unsigned)(__ffs(peers) - 1)) cnt[w][d] = (uint16_t)(old + __popc(peers));
         __syncwarp();
-        rank[k] = old + __popc(peers & ((1u << lane) - 1));
+        const uint32_t r = old + __popc(peers & ((1u << lane) - 1));
+        if (k & 1) rank2[k / 2] |= r << 16;
+        else rank2[k / 2] = r;
     }
+#pragma unroll
+    for (int k = 0; k < IPT; k++)          // in flight during the scan of the digit totals
+        val[k] = (uint32_t)(k * 32) + lane < in_warp ? vals[base + (uint64_t)k * 32 + lane] : 0;
     __syncthreads();
-    {   // thread d: per-warp counts of digit d -> exclusive offsets over the warps; digit total
-        const uint32_t d = threadIdx.x;
+    {   // thread t, digits DPT*t .. DPT*t+DPT-1: per-warp counts -> exclusive offsets over the warps; digit totals
+        uint32_t tot[DPT];
         uint32_t acc = 0;
 #pragma unroll
-        for (int ww = 0; ww < RS_NW; ww++) {
-            uint32_t t = cnt[ww][d];
-            cnt[ww][d] = acc;
-            acc += t;
+        for (int j = 0; j < DPT; j++) {
+            const uint32_t d = threadIdx.x * DPT + j;
+            uint32_t a = 0;
+#pragma unroll
+            for (int ww = 0; ww < RS_NW; ww++) {
+                const uint32_t t = cnt[ww][d];
+                cnt[ww][d] = (uint16_t)a;
+                a += t;
+            }
+            tot[j] = a;
+            acc += a;
         }
-        // exclusive scan of the digit totals over the 256 threads
+        // exclusive scan of the totals over the 256 threads (digit order)
         uint32_t inc = acc;
 #pragma unroll
         for (int s = 1; s < 32; s <<= 1) {
@@ -215,14 +232,22 @@ __global__ void __launch_bounds__(RS_NT) rs_scatter_kernel(const K* __restrict__
         uint32_t wb = 0;
 #pragma unroll
         for (int ww = 0; ww < RS_NW; ww++) wb += ww < (int)w ? wsum[ww] : 0u;
-        dstart[d] = wb + inc - acc;
-        goff[d] = offs[(uint64_t)d * ntiles + blockIdx.x];
+        uint32_t start = wb + inc - acc;
+#pragma unroll
+        for (int j = 0; j < DPT; j++) {
+            const uint32_t d = threadIdx.x * DPT + j;
+            dstart[d] = (uint16_t)start;
+            goff[d] = offs[(uint64_t)d * ntiles + blockIdx.x];
+            start += tot[j];
+        }
     }
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < IPT; k++) {
-        if (dig[k] < 256u) {
-            const uint32_t lp = dstart[dig[k]] + cnt[w][dig[k]] + rank[k];
+        if ((uint32_t)(k * 32) + lane < in_warp) {
+            const uint32_t d = (uint32_t)(key[k] >> shift) & mask;
+            const uint32_t r = (k & 1) ? rank2[k / 2] >> 16 : rank2[k / 2] & 0xFFFFu;
+            const uint32_t lp = (uint32_t)dstart[d] + cnt[w][d] + r;
             skeys[lp] = key[k];
             svals[lp] = val[k];
         }
@@ -246,22 +271,33 @@ void exclusive_scan_u32(uint32_t* d, uint64_t n, scan_scratch& s, cudaStream_t s
     scan_rec(d, n, s.lvl1, s.lvl2, st, d_total);
 }
 
+template <typename K, int NB>
+void radix_pass(K* keys, K* kalt, uint32_t* vals, uint32_t* valt, uint64_t n, int shift, int bits, uint32_t ntiles,
+                sort_scratch& s, cudaStream_t st) {
+    const uint32_t mask = (1u << bits) - 1;
+    rs_hist_kernel<K, NB><<<ntiles, RS_NT, 0, st>>>(keys, n, shift, mask, s.hist, ntiles);
+    KERNEL_CHECK();
+    exclusive_scan_u32(s.hist, (uint64_t)NB * ntiles, s.scan, st);
+    rs_scatter_kernel<K, NB><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.hist, ntiles);
+    KERNEL_CHECK();
+}
+
 template <typename K>
 void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
                         int bit_hi, sort_scratch& s, cudaStream_t st) {
     if (n <= 1 || bit_hi <= bit_lo) return;
     uint32_t ntiles = ceil_div_u(n, RS_NT * rs_cfg<K>::IPT);
-    s.hist.reserve((uint64_t)256 * ntiles);
-    for (int shift = bit_lo; shift < bit_hi; shift += 8) {
-        int bits = bit_hi - shift < 8 ? bit_hi - shift : 8;
-        uint32_t mask = (1u << bits) - 1;
-        rs_hist_kernel<K><<<ntiles, RS_NT, 0, st>>>(keys, n, shift, mask, s.hist, ntiles);
-        KERNEL_CHECK();
-        exclusive_scan_u32(s.hist, (uint64_t)256 * ntiles, s.scan, st);
-        rs_scatter_kernel<K><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.hist, ntiles);
-        KERNEL_CHECK();
+    s.hist.reserve((uint64_t)512 * ntiles);
+    // the fewest passes of at most 9 bits, widths as equal as possible (wider digits first)
+    const int total = bit_hi - bit_lo, passes = (total + 8) / 9;
+    int shift = bit_lo;
+    for (int p = 0; p < passes; p++) {
+        const int left = bit_hi - shift, bits = (left + (passes - p) - 1) / (passes - p);
+        if (bits > 8) radix_pass<K, 512>(keys, kalt, vals, valt, n, shift, bits, ntiles, s, st);
+        else radix_pass<K, 256>(keys, kalt, vals, valt, n, shift, bits, ntiles, s, st);
         K* tk = keys; keys = kalt; kalt = tk;
         uint32_t* tv = vals; vals = valt; valt = tv;
+        shift += bits;
     }
 }
 
