@@ -85,8 +85,9 @@ void radix_sort_pairs(uint64_t*& keys, uint64_t*& kalt, uint32_t*& vals, uint32_
                       int bit_hi, sort_scratch& s, cudaStream_t st);
 
 // same with 32-bit keys (gap index entries: bucket id -> entry id)
+// vals_are_iota: the values are 0, 1, 2, ... and need not be read (nor written by the caller) before the first pass
 void radix_sort_pairs32(uint32_t*& keys, uint32_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
-                        int bit_hi, sort_scratch& s, cudaStream_t st);
+                        int bit_hi, sort_scratch& s, cudaStream_t st, bool vals_are_iota = false);
 
 void fill_u32(uint32_t* d, uint64_t n, uint32_t v, cudaStream_t st);
 void iota_u32(uint32_t* d, uint64_t n, cudaStream_t st);

@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restr
             const uint32_t key = sOut[ge_out(o)];
             keys[e0 + o] = key;
             tkeys[e0 + o] = key;
-            vals[e0 + o] = (uint32_t)(e0 + o);
+            if (vals) vals[e0 + o] = (uint32_t)(e0 + o);
         }
         return;
     }
@@ -818,14 +818,15 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             vals = K->vals_in_v0 ? sc.v0.get() : sc.v1.get();
         } else {
         {
-            gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, vals,
+            // a dense slice has vals[e] = e: the sort generates them in its first pass
+            gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, sparse ? vals : nullptr,
                                                        sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
             KERNEL_CHECK();
         }
         if (E == 0) {                                  // no entry at all: every bucket list is empty
             CUDA_CHECK(cudaMemsetAsync(sc.bstart.get(), 0, (table_entries + 2) * 4, st));
         } else {
-        radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, sc.sort, st);
+        radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, sc.sort, st, !sparse);
         bucket_start_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
         KERNEL_CHECK();
         }

@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ ke
     for (int d = threadIdx.x; d < NB; d += RS_NT) hist[(uint64_t)d * ntiles + blockIdx.x] = cnt[d];
 }
 
-template <typename K, int NB>
+template <typename K, int NB, bool IOTA>
 __global__ void __launch_bounds__(RS_NT, 4) rs_scatter_kernel(const K* __restrict__ keys,
                                                            const uint32_t* __restrict__ vals,
                                                            K* __restrict__ okeys, uint32_t* __restrict__ ovals,
@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(RS_NT, 4) rs_scatter_kernel(const K* __restric
     }
 #pragma unroll
     for (int k = 0; k < IPT; k++)          // in flight during the scan of the digit totals
-        val[k] = (uint32_t)(k * 32) + lane < in_warp ? vals[base + (uint64_t)k * 32 + lane] : 0;
+        val[k] = (uint32_t)(k * 32) + lane >= in_warp ? 0u : IOTA ? (uint32_t)(base + (uint64_t)k * 32 + lane) : vals[base + (uint64_t)k * 32 + lane];
     __syncthreads();
     {   // thread t, digits DPT*t .. DPT*t+DPT-1: per-warp counts -> exclusive offsets over the warps; digit totals
         uint32_t tot[DPT];
@@ -271,21 +271,27 @@ void exclusive_scan_u32(uint32_t* d, uint64_t n, scan_scratch& s, cudaStream_t s
     scan_rec(d, n, s.lvl1, s.lvl2, st, d_total);
 }
 
+void iota_u32(uint32_t* d, uint64_t n, cudaStream_t st);
+
 template <typename K, int NB>
 void radix_pass(K* keys, K* kalt, uint32_t* vals, uint32_t* valt, uint64_t n, int shift, int bits, uint32_t ntiles,
-                sort_scratch& s, cudaStream_t st) {
+                sort_scratch& s, cudaStream_t st, bool iota) {
     const uint32_t mask = (1u << bits) - 1;
     rs_hist_kernel<K, NB><<<ntiles, RS_NT, 0, st>>>(keys, n, shift, mask, s.hist, ntiles);
     KERNEL_CHECK();
     exclusive_scan_u32(s.hist, (uint64_t)NB * ntiles, s.scan, st);
-    rs_scatter_kernel<K, NB><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.hist, ntiles);
+    if (iota) rs_scatter_kernel<K, NB, true><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.hist, ntiles);
+    else rs_scatter_kernel<K, NB, false><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.hist, ntiles);
     KERNEL_CHECK();
 }
 
 template <typename K>
 void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
-                        int bit_hi, sort_scratch& s, cudaStream_t st) {
-    if (n <= 1 || bit_hi <= bit_lo) return;
+                        int bit_hi, sort_scratch& s, cudaStream_t st, bool iota) {
+    if (n <= 1 || bit_hi <= bit_lo) {
+        if (iota) iota_u32(vals, n, st);
+        return;
+    }
     uint32_t ntiles = ceil_div_u(n, RS_NT * rs_cfg<K>::IPT);
     s.hist.reserve((uint64_t)512 * ntiles);
     // the fewest passes of at most 9 bits, widths as equal as possible (wider digits first)
@@ -293,8 +299,8 @@ void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, ui
     int shift = bit_lo;
     for (int p = 0; p < passes; p++) {
         const int left = bit_hi - shift, bits = (left + (passes - p) - 1) / (passes - p);
-        if (bits > 8) radix_pass<K, 512>(keys, kalt, vals, valt, n, shift, bits, ntiles, s, st);
-        else radix_pass<K, 256>(keys, kalt, vals, valt, n, shift, bits, ntiles, s, st);
+        if (bits > 8) radix_pass<K, 512>(keys, kalt, vals, valt, n, shift, bits, ntiles, s, st, iota && p == 0);
+        else radix_pass<K, 256>(keys, kalt, vals, valt, n, shift, bits, ntiles, s, st, iota && p == 0);
         K* tk = keys; keys = kalt; kalt = tk;
         uint32_t* tv = vals; vals = valt; valt = tv;
         shift += bits;
@@ -303,11 +309,11 @@ void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, ui
 
 void radix_sort_pairs(uint64_t*& keys, uint64_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
                       int bit_hi, sort_scratch& s, cudaStream_t st) {
-    radix_sort_pairs_t<uint64_t>(keys, kalt, vals, valt, n, bit_lo, bit_hi, s, st);
+    radix_sort_pairs_t<uint64_t>(keys, kalt, vals, valt, n, bit_lo, bit_hi, s, st, false);
 }
 void radix_sort_pairs32(uint32_t*& keys, uint32_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
-                        int bit_hi, sort_scratch& s, cudaStream_t st) {
-    radix_sort_pairs_t<uint32_t>(keys, kalt, vals, valt, n, bit_lo, bit_hi, s, st);
+                        int bit_hi, sort_scratch& s, cudaStream_t st, bool vals_are_iota) {
+    radix_sort_pairs_t<uint32_t>(keys, kalt, vals, valt, n, bit_lo, bit_hi, s, st, vals_are_iota);
 }
 
 void fill_u32(uint32_t* d, uint64_t n, uint32_t v, cudaStream_t st) {
