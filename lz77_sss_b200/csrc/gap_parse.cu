@@ -473,7 +473,8 @@ __global__ void __launch_bounds__(256) link_phase_kernel(const parse_ctx C, bloc
 
 // Which blocks can see a changed bitmap bit: a probe walks its bucket list backwards until the first inserted
 // entry, so the entries BEHIND a flipped position, up to and including the first one that is inserted before and
-// after the change, are the only ones whose walk can reach it.
+// after the change, are the only ones whose walk can reach it; of those, only the ones that are inserted in one of
+// the two parses can be probes (advance_and_get_occ inserts the position it probes).
 __global__ void __launch_bounds__(256) dirty_from_bitmap_kernel(const parse_ctx C, const uint32_t* __restrict__ old_bm,
                                                                 uint64_t nwords) {
     // one warp per 32 bitmap words; a changed word is handled by the whole warp, one lane per flipped bit
@@ -506,11 +507,20 @@ __global__ void __launch_bounds__(256) dirty_from_bitmap_kernel(const parse_ctx 
             }
             for (uint32_t kk = l + 1; kk < hi; kk++) {
                 const uint32_t q = C.sval[kk] / 5u;
-                C.dirty[q / C.BL] = 1;
-                if (!not_inserted(old_bm, q) && !not_inserted(new_bm, q)) break;
+                // a probe inserts its position: a position that neither parse inserts is not probed by either
+                const bool oi = !not_inserted(old_bm, q), ni = !not_inserted(new_bm, q);
+                if (oi || ni) C.dirty[q / C.BL] = 1;
+                if (oi && ni) break;
             }
         }
     }
+}
+
+// The bitmap only reflects the probes of blocks that are on the chain: a block that joins the chain is parsed again
+// whatever its flag says.
+__global__ void joined_chain_kernel(const parse_ctx C, const uint8_t* __restrict__ marked_prev) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < C.nb && C.marked[b] && !marked_prev[b]) C.dirty[b] = 1;
 }
 
 // Same for a changed table entry (a resumed slice of a sharded run): the walks that fall through the whole list of
@@ -522,8 +532,9 @@ __global__ void dirty_from_table_kernel(const parse_ctx C, const unsigned long l
     const uint32_t hi = C.bstart[b + 1];
     for (uint32_t kk = C.bstart[b]; kk < hi; kk++) {
         const uint32_t q = C.sval[kk] / 5u;
-        C.dirty[q / C.BL] = 1;
-        if (!not_inserted(old_bm, q) && !not_inserted(C.notins, q)) break;
+        const bool oi = !not_inserted(old_bm, q), ni = !not_inserted(C.notins, q);
+        if (oi || ni) C.dirty[q / C.BL] = 1;
+        if (oi && ni) break;
     }
 }
 
@@ -741,6 +752,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         CUDA_CHECK(cudaMemsetAsync(sc.Hc.get(), 0, table_entries * 8, st));
     sc.changed.reserve(8);
     const bool dbg_rounds = getenv("LZ77SSS_DEBUG_ROUNDS") != nullptr;
+    const uint64_t track_div = getenv("LZ77SSS_TRACK_DIV") ? strtoull(getenv("LZ77SSS_TRACK_DIV"), nullptr, 10) : 16;
     sc.slice_exit.reserve(sizeof(block_state));
 
     block_state first;
@@ -859,6 +871,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         sc.entry.reserve((uint64_t)nb * sizeof(block_state));
         sc.exit_.reserve((uint64_t)nb * sizeof(block_state));
         sc.marked.reserve(nb + 1);
+        sc.marked_prev.reserve(nb + 1);
         sc.tr_cnt.reserve(nb);
         sc.tr_pos.reserve((uint64_t)nb * BL);
         sc.tr_src.reserve((uint64_t)nb * BL);
@@ -911,7 +924,9 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             sc.rounds++;
           }
             if (K) K->parsed = true;
+            bool track = have_parse;    // follow single changes (resumed slices from the start, fresh ones once few are left)
             for (uint64_t round = 1; round <= (uint64_t)nb + 4; round++) {
+                if (track) CUDA_CHECK(cudaMemcpyAsync(sc.marked_prev.get(), sc.marked.get(), nb, cudaMemcpyDeviceToDevice, st));
                 {
                     const unsigned gl = ceil_div_u((uint64_t)nb + 1, 256);
                     link_phase_kernel<<<gl, 256, 0, st>>>(C, first, sc.J, 0, 0, d_exit);
@@ -935,8 +950,11 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 // A resumed slice (sharded run, later passes) starts from a converged parse: few bits flip, and only
                 // the blocks whose probes can see a flipped bit (or a changed table entry, or a new entry state) are
                 // parsed again.  A fresh slice flips bits everywhere in its first rounds; following them costs more
-                // than it saves (measured), so there every block on the chain behind the first change is parsed.
-                if (have_parse) {
+                // than it saves (measured), so there every block on the chain behind the first change is parsed
+                // until a round changes fewer than 1/16 of the blocks; from then on the changes are followed.
+                if (track) {
+                    joined_chain_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, sc.marked_prev.get());
+                    KERNEL_CHECK();
                     if (!naive) {
                         dirty_from_bitmap_kernel<<<ceil_div_u(nwords, 256), 256, 0, st>>>(C, sc.notins_prev, nwords);   // 8 warps x 32 words per CTA
                         KERNEL_CHECK();
@@ -964,10 +982,18 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                     fprintf(stderr, "slice %llu round %llu: %u of %u blocks changed, first %u\n", (unsigned long long)a0,
                             (unsigned long long)round, d[0], nb, d[1]);
                 }
-                if (have_parse || !chg)
-                    CUDA_CHECK(cudaMemcpyAsync(sc.notins_prev.get(), sc.notins.get(), nwords * 4, cudaMemcpyDeviceToDevice, st));
+                CUDA_CHECK(cudaMemcpyAsync(sc.notins_prev.get(), sc.notins.get(), nwords * 4, cudaMemcpyDeviceToDevice, st));
                 if (!chg) { converged = true; break; }
-                if (!have_parse) CUDA_CHECK(cudaMemcpy(&C.bmin, sc.changed.get() + 4, 4, cudaMemcpyDeviceToHost));
+                if (!track) {
+                    uint32_t d[2];                      // blocks whose trace or exit changed, the first of them
+                    CUDA_CHECK(cudaMemcpy(d, sc.changed.get() + 3, 8, cudaMemcpyDeviceToHost));
+                    if ((uint64_t)d[0] * track_div <= nb) {    // few changes left: follow them (blocks in front of the old
+                        track = true;                   // bmin are still flagged and are parsed once more)
+                        C.bmin = 0;
+                    } else {
+                        C.bmin = d[1];
+                    }
+                }
             }
             if (!converged) throw std::runtime_error("gap_parse: the block chain did not reach its fixed point");
             if (K) CUDA_CHECK(cudaMemcpyAsync(sc.Hc_prev.get(), sc.Hc.get(), table_entries * 8, cudaMemcpyDeviceToDevice, st));

@@ -132,6 +132,7 @@ struct gap_parse_scratch {
     dbuf<uint64_t> tr_src, tr_len, ml, fsrc, flen;
     dbuf<unsigned long long> Hc;
     dbuf<uint8_t> entry, exit_, marked, slice_exit, nbtab, ovr, dirty;
+    dbuf<uint8_t> marked_prev;             // the chain of the round before (a block that joins the chain is parsed again)
     dbuf<uint32_t> notins_prev;
     dbuf<unsigned long long> Hc_prev;
     dbuf<uint32_t> skip, tile_off;         // sparse slices: positions without entries, compaction offsets per tile
