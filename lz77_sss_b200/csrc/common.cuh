@@ -78,7 +78,8 @@ void exclusive_scan_u32(uint32_t* d, uint64_t n, scan_scratch& s, cudaStream_t s
 // stable LSD radix sort of (key64, val32) pairs on bits [bit_lo, bit_hi) of the key.
 // Result ends in (keys, vals) (ping-pong handled inside; kalt/valt are scratch of the same size).
 struct sort_scratch {
-    dbuf<uint32_t> hist;
+    dbuf<uint32_t> hist, offs;  // hist[tile][digit] and the global offsets made of it
+    dbuf<uint32_t> csum, cpre;  // per chunk of tiles: column sums; column prefixes and, behind them, the digit bases
     scan_scratch scan;
 };
 void radix_sort_pairs(uint64_t*& keys, uint64_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,

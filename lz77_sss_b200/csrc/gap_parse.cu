@@ -500,6 +500,22 @@ __global__ void __launch_bounds__(256) dirty_from_bitmap_kernel(const parse_ctx 
             uint32_t l = C.bstart[b], h = C.bstart[b + 1];
             if (l >= h) continue;
             const uint32_t hi = h;
+            // e is in the list and buckets are hash values, so the entries of a list are spread evenly over time:
+            // interpolate a few times, then bisect what is left
+            {
+                uint32_t lo = l, up = h - 1;
+                uint32_t vlo = C.sval[lo], vup = C.sval[up];
+                for (int it = 0; it < 4 && up - lo > 8 && vlo < e && e < vup; it++) {
+                    uint32_t mid = lo + (uint32_t)(((uint64_t)(e - vlo) * (up - lo)) / (vup - vlo));
+                    if (mid <= lo) mid = lo + 1;
+                    if (mid >= up) mid = up - 1;
+                    const uint32_t vm = C.sval[mid];
+                    if (vm <= e) { lo = mid; vlo = vm; }
+                    else { up = mid; vup = vm; }
+                }
+                if (vup <= e) lo = up;
+                l = lo; h = up + 1;
+            }
             while (l + 1 < h) {
                 const uint32_t mid = (l + h) >> 1;
                 if (C.sval[mid] <= e) l = mid;
@@ -987,7 +1003,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 if (!track) {
                     uint32_t d[2];                      // blocks whose trace or exit changed, the first of them
                     CUDA_CHECK(cudaMemcpy(d, sc.changed.get() + 3, 8, cudaMemcpyDeviceToHost));
-                    if ((uint64_t)d[0] * track_div <= nb) {    // few changes left: follow them (blocks in front of the old
+                    if (!sparse && (uint64_t)d[0] * track_div <= nb) {    // few changes left: follow them (blocks in front of the old
                         track = true;                   // bmin are still flagged and are parsed once more)
                         C.bmin = 0;
                     } else {

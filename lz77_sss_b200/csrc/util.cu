@@ -131,7 +131,8 @@ __global__ void iota_u32_kernel(uint32_t* d, uint64_t n) {
 }
 
 // ---------------- radix sort ----------------------------------------------------------------
-// One LSD pass = histogram per tile, device scan of hist[digit][tile], scatter.  The scatter ranks its tile
+// One LSD pass = histogram per tile (hist[tile][digit], rows written and read coalesced), a column scan over the tiles
+// (chunk sums, one CTA over the chunks and the digits, chunk apply), scatter.  The scatter ranks its tile
 // with per-warp match_any counting (stable), reorders the tile in shared memory by digit and writes every
 // digit's run with consecutive threads, so global stores are coalesced runs instead of single scattered words.
 // A pass takes a digit of up to 9 bits (NB = 256 or 512 bins): the bits of a sort are split into the fewest passes.
@@ -153,7 +154,7 @@ __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ ke
         if (i < n) atomicAdd(&cnt[(uint32_t)(keys[i] >> shift) & mask], 1u);
     }
     __syncthreads();
-    for (int d = threadIdx.x; d < NB; d += RS_NT) hist[(uint64_t)d * ntiles + blockIdx.x] = cnt[d];
+    for (int d = threadIdx.x; d < NB; d += RS_NT) hist[(uint64_t)blockIdx.x * NB + d] = cnt[d];
 }
 
 template <typename K, int NB, bool IOTA>
@@ -237,7 +238,7 @@ __global__ void __launch_bounds__(RS_NT, 4) rs_scatter_kernel(const K* __restric
         for (int j = 0; j < DPT; j++) {
             const uint32_t d = threadIdx.x * DPT + j;
             dstart[d] = (uint16_t)start;
-            goff[d] = offs[(uint64_t)d * ntiles + blockIdx.x];
+            goff[d] = offs[(uint64_t)blockIdx.x * NB + d];
             start += tot[j];
         }
     }
@@ -271,6 +272,56 @@ void exclusive_scan_u32(uint32_t* d, uint64_t n, scan_scratch& s, cudaStream_t s
     scan_rec(d, n, s.lvl1, s.lvl2, st, d_total);
 }
 
+// hist[tile][digit] -> global start of (digit, tile): digits major, tiles minor.  Thread d owns column d.
+constexpr int RS_ROWS = 128;             // tiles per chunk
+template <int NB>
+__global__ void __launch_bounds__(NB) rs_colsum_kernel(const uint32_t* __restrict__ hist, uint32_t ntiles,
+                                                      uint32_t* __restrict__ csum) {
+    const uint32_t r0 = blockIdx.x * RS_ROWS, r1 = min(r0 + RS_ROWS, ntiles);
+    uint32_t acc = 0;
+#pragma unroll 8
+    for (uint32_t r = r0; r < r1; r++) acc += hist[(uint64_t)r * NB + threadIdx.x];
+    csum[(uint64_t)blockIdx.x * NB + threadIdx.x] = acc;
+}
+template <int NB>
+__global__ void __launch_bounds__(NB) rs_colbase_kernel(const uint32_t* __restrict__ csum, uint32_t nchunks,
+                                                       uint32_t* __restrict__ cpre) {
+    __shared__ uint32_t wsum[NB / 32];
+    uint32_t run = 0;
+#pragma unroll 16
+    for (uint32_t c = 0; c < nchunks; c++) {
+        const uint32_t t = csum[(uint64_t)c * NB + threadIdx.x];
+        cpre[(uint64_t)c * NB + threadIdx.x] = run;
+        run += t;
+    }
+    // exclusive scan of the digit totals
+    const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t inc = run;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, inc, s);
+        if (lane >= (unsigned)s) inc += y;
+    }
+    if (lane == 31) wsum[w] = inc;
+    __syncthreads();
+    uint32_t wb = 0;
+    for (unsigned ww = 0; ww < w; ww++) wb += wsum[ww];
+    cpre[(uint64_t)nchunks * NB + threadIdx.x] = wb + inc - run;
+}
+template <int NB>
+__global__ void __launch_bounds__(NB) rs_colapply_kernel(const uint32_t* __restrict__ hist, uint32_t ntiles,
+                                                        const uint32_t* __restrict__ cpre, uint32_t nchunks,
+                                                        uint32_t* __restrict__ offs) {
+    const uint32_t r0 = blockIdx.x * RS_ROWS, r1 = min(r0 + RS_ROWS, ntiles);
+    uint32_t run = cpre[(uint64_t)nchunks * NB + threadIdx.x] + cpre[(uint64_t)blockIdx.x * NB + threadIdx.x];
+#pragma unroll 16
+    for (uint32_t r = r0; r < r1; r++) {
+        const uint32_t t = hist[(uint64_t)r * NB + threadIdx.x];
+        offs[(uint64_t)r * NB + threadIdx.x] = run;
+        run += t;
+    }
+}
+
 void iota_u32(uint32_t* d, uint64_t n, cudaStream_t st);
 
 template <typename K, int NB>
@@ -279,9 +330,17 @@ void radix_pass(K* keys, K* kalt, uint32_t* vals, uint32_t* valt, uint64_t n, in
     const uint32_t mask = (1u << bits) - 1;
     rs_hist_kernel<K, NB><<<ntiles, RS_NT, 0, st>>>(keys, n, shift, mask, s.hist, ntiles);
     KERNEL_CHECK();
-    exclusive_scan_u32(s.hist, (uint64_t)NB * ntiles, s.scan, st);
-    if (iota) rs_scatter_kernel<K, NB, true><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.hist, ntiles);
-    else rs_scatter_kernel<K, NB, false><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.hist, ntiles);
+    const uint32_t nchunks = ceil_div_u(ntiles, RS_ROWS);
+    s.csum.reserve((uint64_t)nchunks * NB);
+    s.cpre.reserve((uint64_t)(nchunks + 1) * NB);
+    rs_colsum_kernel<NB><<<nchunks, NB, 0, st>>>(s.hist, ntiles, s.csum);
+    KERNEL_CHECK();
+    rs_colbase_kernel<NB><<<1, NB, 0, st>>>(s.csum, nchunks, s.cpre);
+    KERNEL_CHECK();
+    rs_colapply_kernel<NB><<<nchunks, NB, 0, st>>>(s.hist, ntiles, s.cpre, nchunks, s.offs);
+    KERNEL_CHECK();
+    if (iota) rs_scatter_kernel<K, NB, true><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.offs, ntiles);
+    else rs_scatter_kernel<K, NB, false><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.offs, ntiles);
     KERNEL_CHECK();
 }
 
@@ -294,6 +353,7 @@ void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, ui
     }
     uint32_t ntiles = ceil_div_u(n, RS_NT * rs_cfg<K>::IPT);
     s.hist.reserve((uint64_t)512 * ntiles);
+    s.offs.reserve((uint64_t)512 * ntiles);
     // the fewest passes of at most 9 bits, widths as equal as possible (wider digits first)
     const int total = bit_hi - bit_lo, passes = (total + 8) / 9;
     int shift = bit_lo;
