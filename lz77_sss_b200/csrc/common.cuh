@@ -87,8 +87,10 @@ void radix_sort_pairs(uint64_t*& keys, uint64_t*& kalt, uint32_t*& vals, uint32_
 
 // same with 32-bit keys (gap index entries: bucket id -> entry id)
 // vals_are_iota: the values are 0, 1, 2, ... and need not be read (nor written by the caller) before the first pass
+// first_keys: the unsorted keys live in this read-only array (keys is then only a ping-pong buffer)
 void radix_sort_pairs32(uint32_t*& keys, uint32_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
-                        int bit_hi, sort_scratch& s, cudaStream_t st, bool vals_are_iota = false);
+                        int bit_hi, sort_scratch& s, cudaStream_t st, bool vals_are_iota = false,
+                        const uint32_t* first_keys = nullptr);
 
 void fill_u32(uint32_t* d, uint64_t n, uint32_t v, cudaStream_t st);
 void iota_u32(uint32_t* d, uint64_t n, cudaStream_t st);

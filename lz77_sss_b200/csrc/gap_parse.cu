@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restr
     if (!skip) {
         for (uint32_t o = tid; o < 5 * in_tile; o += 160) {
             const uint32_t key = sOut[ge_out(o)];
-            keys[e0 + o] = key;
+            if (keys) keys[e0 + o] = key;
             tkeys[e0 + o] = key;
             if (vals) vals[e0 + o] = (uint32_t)(e0 + o);
         }
@@ -201,15 +201,32 @@ __global__ void tile_need_kernel(const uint32_t* __restrict__ skip, uint64_t cnt
 }
 
 // bstart[b] = first sorted index whose key is >= b, for b in [0, nkeys]  (nkeys = table_entries + 1 keys incl. invalid)
-__global__ void bucket_start_kernel(const uint32_t* __restrict__ skey, uint64_t E, uint32_t nkeys,
-                                    uint32_t* __restrict__ bstart) {
-    const uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= E) return;
-    const uint32_t key = skey[k];
-    const int64_t prev = k ? (int64_t)skey[k - 1] : -1;
-    for (int64_t b = prev + 1; b <= (int64_t)key; b++) bstart[b] = (uint32_t)k;
-    if (k == E - 1)
-        for (uint32_t b = key + 1; b <= nkeys; b++) bstart[b] = (uint32_t)E;
+__global__ void __launch_bounds__(256) bucket_start_kernel(const uint32_t* __restrict__ skey, uint64_t E, uint32_t nkeys,
+                                                           uint32_t* __restrict__ bstart) {
+    // a thread takes 4 consecutive keys (one 16-byte load; the sort buffers are 16-byte aligned); the key in front of
+    // them comes from the lane below
+    const uint64_t k0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const unsigned lane = threadIdx.x & 31;
+    uint32_t key[4] = {0, 0, 0, 0};
+    if (k0 + 3 < E) {
+        const uint4 v = *reinterpret_cast<const uint4*>(skey + k0);
+        key[0] = v.x; key[1] = v.y; key[2] = v.z; key[3] = v.w;
+    } else {
+        for (int j = 0; j < 4; j++)
+            if (k0 + j < E) key[j] = skey[k0 + j];
+    }
+    uint32_t below = __shfl_up_sync(0xffffffffu, key[3], 1);
+    if (lane == 0 && k0 > 0 && k0 < E) below = skey[k0 - 1];
+    int64_t prev = k0 ? (int64_t)below : -1;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const uint64_t k = k0 + j;
+        if (k >= E) break;
+        for (int64_t b = prev + 1; b <= (int64_t)key[j]; b++) bstart[b] = (uint32_t)k;
+        if (k == E - 1)
+            for (uint32_t b = key[j] + 1; b <= nkeys; b++) bstart[b] = (uint32_t)E;
+        prev = key[j];
+    }
 }
 
 struct block_state {
@@ -846,16 +863,17 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             vals = K->vals_in_v0 ? sc.v0.get() : sc.v1.get();
         } else {
         {
-            // a dense slice has vals[e] = e: the sort generates them in its first pass
-            gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, sparse ? vals : nullptr,
+            // a dense slice has vals[e] = e (the sort generates them in its first pass) and keys = tkey (its first
+            // pass reads tkey)
+            gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, sparse ? keys : nullptr, sc.tkey, sparse ? vals : nullptr,
                                                        sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
             KERNEL_CHECK();
         }
         if (E == 0) {                                  // no entry at all: every bucket list is empty
             CUDA_CHECK(cudaMemsetAsync(sc.bstart.get(), 0, (table_entries + 2) * 4, st));
         } else {
-        radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, sc.sort, st, !sparse);
-        bucket_start_kernel<<<ceil_div_u(E, 256), 256, 0, st>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
+        radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, sc.sort, st, !sparse, sparse ? nullptr : sc.tkey.get());
+        bucket_start_kernel<<<ceil_div_u(E, 1024), 256, 0, st>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
         KERNEL_CHECK();
         }
         if (K) { K->sorted = true; K->vals_in_v0 = vals == sc.v0.get(); }

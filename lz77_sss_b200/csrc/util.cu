@@ -346,9 +346,10 @@ void radix_pass(K* keys, K* kalt, uint32_t* vals, uint32_t* valt, uint64_t n, in
 
 template <typename K>
 void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
-                        int bit_hi, sort_scratch& s, cudaStream_t st, bool iota) {
+                        int bit_hi, sort_scratch& s, cudaStream_t st, bool iota, const K* first_keys = nullptr) {
     if (n <= 1 || bit_hi <= bit_lo) {
         if (iota) iota_u32(vals, n, st);
+        if (first_keys && n) CUDA_CHECK(cudaMemcpyAsync(keys, first_keys, n * sizeof(K), cudaMemcpyDeviceToDevice, st));
         return;
     }
     uint32_t ntiles = ceil_div_u(n, RS_NT * rs_cfg<K>::IPT);
@@ -359,8 +360,9 @@ void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, ui
     int shift = bit_lo;
     for (int p = 0; p < passes; p++) {
         const int left = bit_hi - shift, bits = (left + (passes - p) - 1) / (passes - p);
-        if (bits > 8) radix_pass<K, 512>(keys, kalt, vals, valt, n, shift, bits, ntiles, s, st, iota && p == 0);
-        else radix_pass<K, 256>(keys, kalt, vals, valt, n, shift, bits, ntiles, s, st, iota && p == 0);
+        K* in = p == 0 && first_keys ? const_cast<K*>(first_keys) : keys;     // only read
+        if (bits > 8) radix_pass<K, 512>(in, kalt, vals, valt, n, shift, bits, ntiles, s, st, iota && p == 0);
+        else radix_pass<K, 256>(in, kalt, vals, valt, n, shift, bits, ntiles, s, st, iota && p == 0);
         K* tk = keys; keys = kalt; kalt = tk;
         uint32_t* tv = vals; vals = valt; valt = tv;
         shift += bits;
@@ -372,8 +374,8 @@ void radix_sort_pairs(uint64_t*& keys, uint64_t*& kalt, uint32_t*& vals, uint32_
     radix_sort_pairs_t<uint64_t>(keys, kalt, vals, valt, n, bit_lo, bit_hi, s, st, false);
 }
 void radix_sort_pairs32(uint32_t*& keys, uint32_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
-                        int bit_hi, sort_scratch& s, cudaStream_t st, bool vals_are_iota) {
-    radix_sort_pairs_t<uint32_t>(keys, kalt, vals, valt, n, bit_lo, bit_hi, s, st, vals_are_iota);
+                        int bit_hi, sort_scratch& s, cudaStream_t st, bool vals_are_iota, const uint32_t* first_keys) {
+    radix_sort_pairs_t<uint32_t>(keys, kalt, vals, valt, n, bit_lo, bit_hi, s, st, vals_are_iota, first_keys);
 }
 
 void fill_u32(uint32_t* d, uint64_t n, uint32_t v, cudaStream_t st) {
