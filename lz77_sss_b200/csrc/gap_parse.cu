@@ -314,7 +314,7 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
 }
 
 template <typename pos_t>
-__global__ void __launch_bounds__(128) parse_kernel(const parse_ctx C, const lce_view<pos_t> V) {
+__global__ void __launch_bounds__(128, 16) parse_kernel(const parse_ctx C, const lce_view<pos_t> V) {
     const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     const unsigned lane = threadIdx.x & 31;
     if (b >= C.nb || b < C.bmin || !C.marked[b] || !C.dirty[b]) return;
