@@ -143,15 +143,31 @@ template <typename K> struct rs_cfg { static constexpr int IPT = sizeof(K) == 4 
 template <typename K, int NB>
 __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ keys, uint64_t n, int shift,
                                                         uint32_t mask, uint32_t* __restrict__ hist, uint32_t ntiles) {
-    constexpr int TILE = RS_NT * rs_cfg<K>::IPT;
+    constexpr int TILE = RS_NT * rs_cfg<K>::IPT;          // 16 KiB of keys for both key types
+    constexpr int VPT = TILE * (int)sizeof(K) / 16 / RS_NT;   // 16-byte vectors per thread
+    constexpr int KPV = 16 / (int)sizeof(K);              // keys per vector
     __shared__ uint32_t cnt[NB];
     for (int d = threadIdx.x; d < NB; d += RS_NT) cnt[d] = 0;
     __syncthreads();
-    uint64_t base = (uint64_t)blockIdx.x * TILE;
+    const uint64_t base = (uint64_t)blockIdx.x * TILE;
+    if (base + TILE <= n) {                               // full tile: coalesced 16-byte loads, all issued up front
+        const uint4* src = reinterpret_cast<const uint4*>(keys + base);
+        uint4 v[VPT];
 #pragma unroll
-    for (int k = 0; k < rs_cfg<K>::IPT; k++) {
-        uint64_t i = base + (uint64_t)k * RS_NT + threadIdx.x;
-        if (i < n) atomicAdd(&cnt[(uint32_t)(keys[i] >> shift) & mask], 1u);
+        for (int k = 0; k < VPT; k++) v[k] = src[k * RS_NT + threadIdx.x];
+#pragma unroll
+        for (int k = 0; k < VPT; k++) {
+            K kk[KPV];
+            memcpy(kk, &v[k], 16);
+#pragma unroll
+            for (int j = 0; j < KPV; j++) atomicAdd(&cnt[(uint32_t)(kk[j] >> shift) & mask], 1u);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < rs_cfg<K>::IPT; k++) {
+            uint64_t i = base + (uint64_t)k * RS_NT + threadIdx.x;
+            if (i < n) atomicAdd(&cnt[(uint32_t)(keys[i] >> shift) & mask], 1u);
+        }
     }
     __syncthreads();
     for (int d = threadIdx.x; d < NB; d += RS_NT) hist[(uint64_t)blockIdx.x * NB + d] = cnt[d];
