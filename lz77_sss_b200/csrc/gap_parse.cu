@@ -785,7 +785,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         CUDA_CHECK(cudaMemsetAsync(sc.Hc.get(), 0, table_entries * 8, st));
     sc.changed.reserve(8);
     const bool dbg_rounds = getenv("LZ77SSS_DEBUG_ROUNDS") != nullptr;
-    const uint64_t track_div = getenv("LZ77SSS_TRACK_DIV") ? strtoull(getenv("LZ77SSS_TRACK_DIV"), nullptr, 10) : 16;
+    const uint64_t track_div = getenv("LZ77SSS_TRACK_DIV") ? strtoull(getenv("LZ77SSS_TRACK_DIV"), nullptr, 10) : 64;
     sc.slice_exit.reserve(sizeof(block_state));
 
     block_state first;
@@ -985,7 +985,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 // the blocks whose probes can see a flipped bit (or a changed table entry, or a new entry state) are
                 // parsed again.  A fresh slice flips bits everywhere in its first rounds; following them costs more
                 // than it saves (measured), so there every block on the chain behind the first change is parsed
-                // until a round changes fewer than 1/16 of the blocks; from then on the changes are followed.
+                // until a round changes fewer than 1/64 of the blocks; from then on the changes are followed.
                 if (track) {
                     joined_chain_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, sc.marked_prev.get());
                     KERNEL_CHECK();
