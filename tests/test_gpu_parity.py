@@ -381,6 +381,22 @@ def test_c2_quarter_gib_dna_properties(capi):
         assert (F.decode(src, ln, text.size) == text).all()
 
 
+def test_change_tracking_is_invisible(capi, monkeypatch):
+    """A fresh slice re-parses every block behind the first change until few blocks change, then follows single changes
+    (gap_parse.cu, dirty_from_bitmap_kernel).  When it switches is an internal choice: never, early and the default
+    must give the same factors, here on 32768 blocks."""
+    text = synth.dna_collection(64 << 20, seed=12, chrom_len=4 << 20)
+    bases = (401, 70_001, 123_457, 999_983, 1_048_575)
+    got = []
+    for div in ("1000000000000", "64", "1"):
+        monkeypatch.setenv("LZ77SSS_TRACK_DIV", div)
+        with capi.Factorizer(tau=512, num_threads=1, gap_bases=bases) as F:
+            got.append(F.factorize(text))
+    for src, ln in got[1:]:
+        assert _eq(src, got[0][0]) and _eq(ln, got[0][1])
+    _check_factors(text, *got[0])
+
+
 def test_cpp_header_example_runs(capi, tmp_path):
     exe = tmp_path / "example"
     cmd = ["/usr/bin/g++", "-std=c++20", "-O1", "-I" + os.path.join(ROOT, "include"),
