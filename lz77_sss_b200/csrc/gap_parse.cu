@@ -492,16 +492,18 @@ __global__ void __launch_bounds__(256) link_phase_kernel(const parse_ctx C, bloc
 // entry, so the entries BEHIND a flipped position, up to and including the first one that is inserted before and
 // after the change, are the only ones whose walk can reach it; of those, only the ones that are inserted in one of
 // the two parses can be probes (advance_and_get_occ inserts the position it probes).
+constexpr unsigned DB_WPW = 4;
 __global__ void __launch_bounds__(256) dirty_from_bitmap_kernel(const parse_ctx C, const uint32_t* __restrict__ old_bm,
                                                                 uint64_t nwords) {
-    // one warp per 32 bitmap words; a changed word is handled by the whole warp, one lane per flipped bit
-    const uint64_t w0 = (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32;
+    // one warp per DB_WPW bitmap words (flips cluster: few words per warp spread them over more warps); a changed word
+    // is handled by the whole warp, one lane per flipped bit
+    const uint64_t w0 = (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * DB_WPW;
     const unsigned lane = threadIdx.x & 31;
     if (w0 >= nwords) return;
     const uint32_t* __restrict__ new_bm = C.notins;
     const uint64_t cnt = C.a1 - C.a0;
     uint32_t mine = 0;
-    if (w0 + lane < nwords) mine = old_bm[w0 + lane] ^ new_bm[w0 + lane];
+    if (lane < DB_WPW && w0 + lane < nwords) mine = old_bm[w0 + lane] ^ new_bm[w0 + lane];
     unsigned todo = __ballot_sync(0xffffffffu, mine != 0);
     while (todo) {
         const int wl = __ffs(todo) - 1;
@@ -990,7 +992,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                     joined_chain_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, sc.marked_prev.get());
                     KERNEL_CHECK();
                     if (!naive) {
-                        dirty_from_bitmap_kernel<<<ceil_div_u(nwords, 256), 256, 0, st>>>(C, sc.notins_prev, nwords);   // 8 warps x 32 words per CTA
+                        dirty_from_bitmap_kernel<<<ceil_div_u(nwords, 8 * DB_WPW), 256, 0, st>>>(C, sc.notins_prev, nwords);   // 8 warps x DB_WPW words per CTA
                         KERNEL_CHECK();
                     }
                 } else {
