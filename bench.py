@@ -13,9 +13,17 @@ A "step" = one complete factorization of that text.  Metric: input MiB/s factori
              CUDA-event time on the library's stream, against the measured HBM copy peak
   cpu_baseline : the reference's own CPU code (oracle/_ref) on a bounded prefix of the same text
 
-N > 1 (torchrun): every rank factorizes its own text of the same shape (seed 2+rank); no data-path collective
-exists yet for a single sharded text, so this is "independent texts per GPU" weak scaling.
-`--impl reference` times the reference's CPU implementation (rank 0 only).
+  parity_checked : outside the timed region the factor stream (count and SHA-256 of the src/len arrays) is compared with
+          the reference arm's output on the SAME text, tau, num_threads and gap-index bases
+
+num_threads is the reference's LOGICAL partition count of build_LPF_opt (it changes the factor stream, not the device
+work); both arms use the same value, the number of host threads the reference arm runs on, so the two lines describe
+the same configuration (`--threads` overrides it for both).
+
+N > 1 (torchrun): the SAME text sharded over the N GPUs (lz77_sss_b200/sharded.py; strong scaling, NCCL all-gathers of
+shards, tables and exit states); `--independent` keeps one text per GPU (weak scaling, no collective).
+`--impl reference` times the reference's own CPU implementation (oracle/_ref) on the whole text (rank 0 only); its
+line carries the reference's own phase split (`reference_phases_ms`, from its RESULT line).
 """
 from __future__ import annotations
 
@@ -47,11 +55,19 @@ def parse():
     ap.add_argument("--tau", type=int, default=512)
     ap.add_argument("--size-mib", type=int, default=1024)
     ap.add_argument("--workload", default="dna", choices=["dna", "rep"])
-    ap.add_argument("--cpu-sample-mib", type=int, default=64)
+    ap.add_argument("--cpu-sample-mib", type=int, default=0, help="0 = the whole text (same configuration as the GPU arm)")
+    ap.add_argument("--threads", type=int, default=0,
+                    help="num_threads of BOTH arms (the reference's thread count = the logical LPF partition count); "
+                         "0 = min(host cores, 64)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--independent", action="store_true",
                     help="N > 1: every rank factorizes its own text (weak scaling) instead of sharding one text")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.threads <= 0:
+        a.threads = max(1, min(os.cpu_count() or 1, 64))
+    if a.cpu_sample_mib <= 0 or a.cpu_sample_mib > a.size_mib:
+        a.cpu_sample_mib = a.size_mib
+    return a
 
 
 def make_text(args, rank):
@@ -65,8 +81,14 @@ def make_text(args, rank):
 def workload_name(args):
     if args.workload == "dna":
         return (f"C2: lz77-sss-3-aprx on {args.size_mib} MiB synthetic chr19-like DNA (64 mutated copies of one "
-                f"chromosome), tau={args.tau}, num_threads=1")
-    return f"C1: lz77-sss-3-aprx on {args.size_mib} MiB random_repetitive_string, tau={args.tau}, num_threads=1"
+                f"chromosome), tau={args.tau}, num_threads={args.threads}")
+    return f"C1: lz77-sss-3-aprx on {args.size_mib} MiB random_repetitive_string, tau={args.tau}, num_threads={args.threads}"
+
+
+def config_dict(args):
+    """Identical for both arms: what is factorized and with which parameters."""
+    return {"workload": workload_name(args), "n_bytes": args.size_mib * MIB, "tau": args.tau, "num_threads": args.threads,
+            "l2": f"input ({args.size_mib} MiB) is larger than L2 (126 MB); no explicit flush"}
 
 
 def sss_traffic(n, tau):
@@ -115,17 +137,44 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference_run(text, tau, threads):
-    """The reference's own factorize_approximate<greedy, lpf_opt, tau> (oracle/_ref), timed as lz77_sss.hpp:314-353."""
+def stream_hash(src, ln):
+    import hashlib
+    h = hashlib.sha256()
+    h.update(np.ascontiguousarray(src, dtype=np.uint64).tobytes())
+    h.update(np.ascontiguousarray(ln, dtype=np.uint64).tobytes())
+    return h.hexdigest()
+
+
+REF_PHASES = ("lce_t", "nsv_psv", "lpf", "phrase_info", "init_gap_idx", "factorize")
+
+
+def cpu_reference_run(text, tau, threads, keep=False):
+    """The reference's own factorize_approximate<greedy, lpf_opt, tau> (oracle/_ref), timed as lz77_sss.hpp:314-353.
+    Returns a dict: seconds, kind, cores, phases_ms (the reference's own RESULT line), and with keep the factor
+    stream's count / hash / bases for the parity check."""
     import oracle_lib as O
     if O.ref_available(tau):
-        _, _, _, sec = O.ref_factorize(text, tau, p=threads)
-        return sec, "reference"
+        src, ln, bases, sec, ph = O.ref_factorize_logged(text, tau, p=threads)
+        out = {"sec": sec, "kind": "reference", "cores": threads,
+               "phases_ms": {k: ph[k] / 1e6 for k in REF_PHASES if k in ph}}
+        if keep:
+            out.update(z=int(src.size), hash=stream_hash(src, ln), bases=[int(b) for b in bases])
+        return out
     # the reference library was not prebuilt for this tau: time the oracle's sequential restatement instead
     from lz77_sss_b200 import capi
     t0 = time.perf_counter()
-    O.factorize(text, tau, capi.DEFAULT_GAP_BASES, p_ref=1)
-    return time.perf_counter() - t0, "port"
+    src, ln, _ = O.factorize(text, tau, capi.DEFAULT_GAP_BASES, p_ref=threads)
+    out = {"sec": time.perf_counter() - t0, "kind": "port", "cores": 1, "phases_ms": {}}
+    if keep:
+        out.update(z=int(src.size), hash=stream_hash(src, ln), bases=list(capi.DEFAULT_GAP_BASES))
+    return out
+
+
+def shim_share(phases_ms):
+    """lce_t (build_lce: synchronizing set, its suffix order, LCP, RMQ) runs oracle/shim + oracle/core code, because the
+    `lce` submodule that holds it is absent from the reference tree; every other phase is the reference's own code."""
+    tot = sum(phases_ms.values())
+    return (phases_ms.get("lce_t", 0.0) / tot) if tot else None
 
 
 def run_reference(args):
@@ -134,23 +183,23 @@ def run_reference(args):
         return
     text = make_text(args, 0)
     sample = text[: args.cpu_sample_mib * MIB]
-    cores = os.cpu_count() or 1
-    times = []
-    kind = "reference"
+    times, phases, r = [], {}, None
     for it in range(args.warmup + args.steps):
-        sec, kind = cpu_reference_run(sample, args.tau, cores if kind == "reference" else 1)
+        r = cpu_reference_run(sample, args.tau, args.threads)
         if it >= args.warmup:
-            times.append(sec)
+            times.append(r["sec"])
+            for k, v in r["phases_ms"].items():
+                phases[k] = phases.get(k, 0.0) + v / args.steps
     ms = 1e3 * sum(times) / len(times)
     val = (sample.size / MIB) / (ms / 1e3)
-    used = cores if kind == "reference" else 1
+    what = "the whole text" if sample.size == text.size else f"first {sample.size // MIB} MiB of the text"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "MiB/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload_name(args), "sample": f"first {sample.size // MIB} MiB of the text per step"},
-        "cpu_baseline": {"value": val, "unit": "MiB/s", "cores": used, "kind": kind,
-                         "sample": f"first {sample.size // MIB} MiB of the workload text, num_threads={used}"},
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic", "config": config_dict(args),
+        "cpu_baseline": {"value": val, "unit": "MiB/s", "cores": r["cores"], "kind": r["kind"],
+                         "sample": f"{what}, num_threads={args.threads}, {args.steps} timed runs"},
+        "reference_phases_ms": phases, "reference_shim_share": shim_share(phases),
         "e2e": {"value": val, "unit": "MiB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -170,7 +219,7 @@ def run_sharded(args, world, rank, local, barrier):
     pinned = torch.empty(max(1, se - sb), dtype=torch.uint8).pin_memory()
     pinned.numpy()[:se - sb] = text[sb:se]
     per = sh_ranges[0][1]
-    F = capi.Factorizer(tau=args.tau, num_threads=1, gap_bases=capi.DEFAULT_GAP_BASES, device=local)
+    F = capi.Factorizer(tau=args.tau, num_threads=args.threads, gap_bases=capi.DEFAULT_GAP_BASES, device=local)
     be = sharded.CudaBackend(F, dev)
     buf = torch.zeros(sharded.FRONT_PAD + per * world + sharded.TEXT_PAD, dtype=torch.uint8, device=dev)
     body = buf[sharded.FRONT_PAD:sharded.FRONT_PAD + per * world]
@@ -240,12 +289,12 @@ def run_sharded(args, world, rank, local, barrier):
             "metric": METRIC, "value": (n / MIB) / (ms_res / 1e3), "unit": "MiB/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_res, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": {"workload": workload_name(args), "n_bytes": int(n), "tau": args.tau, "num_threads": 1,
-                       "parallelism": f"one text sharded over {world} GPUs: shards all-gathered (NCCL), replicated SSS/SA_S/LPF "
-                                      f"front, gap index + greedy emission split by text range, tables and exit states "
-                                      f"all-gathered between passes ({stats['passes']} passes)",
-                       "l2": "input (1 GiB) is larger than L2 (126 MB); no explicit flush", "factors": stats["z"],
-                       "size_sss": int(st["size_sss"])},
+            "config": config_dict(args),
+            "parallelism": f"one text sharded over {world} GPUs: shards all-gathered (NCCL), replicated SSS/SA_S/LPF "
+                           f"front, gap index + greedy emission split by text range, tables and exit states "
+                           f"all-gathered between passes ({stats['passes']} passes); every rank also holds the whole text in host memory",
+            "factors": stats["z"], "size_sss": int(st["size_sss"]),
+            "cpu_baseline": None, "cpu_baseline_note": "timed at N = 1 only (bench.py --gpus 1 and --impl reference)",
             "e2e": {"value": (n / MIB) / (ms_e2e / 1e3), "unit": "MiB/s", "h2d_bytes_per_step": int(hb[0].item()),
                     "d2h_bytes_per_step": int(hb[1].item()), "ms_per_step": ms_e2e},
             "gpu_launches": int(lt.item()),
@@ -294,7 +343,7 @@ def main():
     pinned = torch.empty(n, dtype=torch.uint8).pin_memory()          # plumbing: pinned host memory for the e2e leg
     pinned.numpy()[:] = text
     host_ptr = pinned.data_ptr()
-    F = capi.Factorizer(tau=args.tau, num_threads=1, gap_bases=capi.DEFAULT_GAP_BASES, device=local)
+    F = capi.Factorizer(tau=args.tau, num_threads=args.threads, gap_bases=capi.DEFAULT_GAP_BASES, device=local)
     cap = n // 8 + 1024
     src = np.empty(cap, dtype=np.uint64)
     ln = np.empty(cap, dtype=np.uint64)
@@ -361,12 +410,10 @@ def main():
         achieved = alg_bytes / (k_ms / 1e3) / 1e9
         out = {
             "metric": METRIC, "value": value, "unit": "MiB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_res, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-            "data": "synthetic",
-            "config": {"workload": workload_name(args), "n_bytes": int(n), "tau": args.tau, "num_threads": 1,
-                       "parallelism": "single GPU" if world == 1 else f"{world} independent texts, one per GPU (no sharded single-text path yet)",
-                       "l2": "input (1 GiB) is larger than L2 (126 MB); no explicit flush", "factors": int(z),
-                       "size_sss": int(st_res["size_sss"])},
+            "ms_per_step": ms_res, "higher_is_better": True, "scaling": "strong" if world == 1 else "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config_dict(args),
+            "parallelism": "single GPU" if world == 1 else f"{world} independent texts, one per GPU (--independent)",
+            "factors": int(z), "size_sss": int(st_res["size_sss"]),
             "e2e": {"value": e2e, "unit": "MiB/s", "h2d_bytes_per_step": int(st_e2e["h2d_bytes"]),
                     "d2h_bytes_per_step": int(st_e2e["d2h_bytes"]), "ms_per_step": ms_e2e},
             "gpu_launches": int(launches_timed),
@@ -384,12 +431,23 @@ def main():
                                      "achieved": rks_gbs, "peak": peak, "unit": "GB/s", "frac": rks_gbs / peak,
                                      "algorithmic_bytes": int(rks_bytes), "kernel_ms": rks_ms}]
         if not args.no_cpu_baseline:
+            # the reference on the same text, tau and num_threads: its time (cpu_baseline) and, outside every timed
+            # region, its factor stream against the CUDA path's for the bases the reference drew (parity_checked)
             sample = text[: args.cpu_sample_mib * MIB]
-            cores = os.cpu_count() or 1
-            sec, kind = cpu_reference_run(sample, args.tau, cores)
-            used = cores if kind == "reference" else 1
-            out["cpu_baseline"] = {"value": (sample.size / MIB) / sec, "unit": "MiB/s", "cores": used, "kind": kind,
-                                   "sample": f"first {sample.size // MIB} MiB of the workload text, num_threads={used}, one run"}
+            r = cpu_reference_run(sample, args.tau, args.threads, keep=True)
+            what = "the whole text" if sample.size == n else f"first {sample.size // MIB} MiB of the workload text"
+            out["cpu_baseline"] = {"value": (sample.size / MIB) / r["sec"], "unit": "MiB/s", "cores": r["cores"], "kind": r["kind"],
+                                   "sample": f"{what}, num_threads={args.threads}, one run",
+                                   "phases_ms": r["phases_ms"], "shim_share": shim_share(r["phases_ms"])}
+            with capi.Factorizer(tau=args.tau, num_threads=args.threads, gap_bases=r["bases"], device=local) as F2:
+                gsrc, gln = F2.factorize(sample, cap=cap)
+            ok = int(gsrc.size) == r["z"] and stream_hash(gsrc, gln) == r["hash"]
+            out["parity_checked"] = bool(ok)
+            out["parity"] = {"against": f"oracle/_ref ({r['kind']}) on {what}", "factors": int(gsrc.size), "reference_factors": r["z"],
+                             "sha256_equal": bool(ok)}
+            if not ok:
+                print(json.dumps(out))
+                raise SystemExit("bench.py: the factor stream differs from the reference's")
     barrier()
     if rank == 0:
         print(json.dumps(out))

@@ -3,8 +3,20 @@
 // Built once per tau (-DREF_TAU=...) into oracle/_ref/libref_tau<tau>.so, because the reference makes
 // tau a template parameter (lz77_sss.hpp:176-186) and its misc/utils.hpp defines non-inline
 // functions (one translation unit per library).
+// LZ77_SSS_BENCH makes the reference append its own `RESULT key=value` line (phase times in ns: lce_t, nsv_psv,
+// lpf, phrase_info, init_gap_idx, factorize, ...; lz77_sss.hpp:298-311,357-365, misc/utils.hpp:642-648) to
+// `result_file` when parameters::log is set.  The three globals are the ones bench/lz77_sss_bench.cpp:29-31 defines.
+#define LZ77_SSS_BENCH
+#include <fstream>
+#include <string>
+std::string text_name;
+std::string result_file_path;
+std::ofstream result_file;
 #include <lz77_sss/lz77_sss.hpp>
 #include <omp.h>
+#include <unistd.h>
+#include <iostream>
+#include <sstream>
 #include <cstdint>
 #include <cstring>
 #include <random>
@@ -25,7 +37,7 @@ struct sink_t {
 
 template <typename pos_t, uint64_t tau>
 int64_t run_approximate(const uint8_t* text, uint64_t n, int phr_mode, int fact_mode,
-                        int num_threads, sink_t& sink, double* seconds) {
+                        int num_threads, sink_t& sink, double* seconds, bool log = false) {
     // every reference driver pads the input with zero bytes (cli/lz77_sss_3_aprx.cpp:66,
     // bench/lz77_sss_bench_tau.cpp:72)
     std::vector<char> buf(n + 4 * 4096, 0);
@@ -37,7 +49,7 @@ int64_t run_approximate(const uint8_t* text, uint64_t n, int phr_mode, int fact_
         }
         sink.z++;
     };
-    parameters prm { .num_threads = (uint16_t)num_threads, .log = false };
+    parameters prm { .num_threads = (uint16_t)num_threads, .log = log };
     char* T = buf.data();
     pos_t N = (pos_t)n;
     using L = lz77_sss<pos_t>;
@@ -107,6 +119,40 @@ int64_t refdrv_factorize_approximate(const uint8_t* text, uint64_t n, int phr_mo
         int builds = (phr_mode == lpf_lnf_naive || phr_mode == lpf_lnf_opt) ? 1 : 1;
         for (int i = 0; i < 5 * builds; i++) draw(mirror());   // advance past the bases that run consumed
     }
+    return z;
+}
+
+// Same run with parameters::log = true: the reference's console log is discarded, its RESULT line (phase times in
+// nanoseconds) is returned in result_out.  Timed region as above.
+int64_t refdrv_factorize_approximate_logged(const uint8_t* text, uint64_t n, int phr_mode, int fact_mode, int num_threads,
+                                            uint64_t* src, uint64_t* len, uint64_t cap, double* seconds,
+                                            char* result_out, uint64_t result_cap) {
+    if (n == 0) return -2;
+    char path[] = "/tmp/refdrv_result_XXXXXX";
+    int fd = mkstemp(path);
+    if (fd < 0) return -3;
+    close(fd);
+    text_name = "synthetic";
+    result_file_path = path;
+    result_file.open(path, std::ios_base::trunc);
+    std::ostringstream devnull;
+    std::streambuf* old = std::cout.rdbuf(devnull.rdbuf());
+    sink_t s { src, len, cap, 0 };
+    int64_t z;
+    if (n <= 0xFFFFFFFFull) z = run_approximate<uint32_t, REF_TAU>(text, n, phr_mode, fact_mode, num_threads, s, seconds, true);
+    else z = run_approximate<uint64_t, REF_TAU>(text, n, phr_mode, fact_mode, num_threads, s, seconds, true);
+    std::cout.rdbuf(old);
+    result_file.close();
+    result_file_path = "";
+    if (z >= 0 && fact_mode != skip_phrases)
+        for (int i = 0; i < 5; i++) draw(mirror());
+    if (result_out && result_cap) {
+        std::ifstream in(path);
+        std::string line((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
+        std::strncpy(result_out, line.c_str(), result_cap - 1);
+        result_out[result_cap - 1] = 0;
+    }
+    unlink(path);
     return z;
 }
 

@@ -184,6 +184,9 @@ def ref(tau):
         L.refdrv_factorize_approximate.restype = C.c_int64
         L.refdrv_factorize_approximate.argtypes = [_u8p, C.c_uint64, C.c_int, C.c_int, C.c_int, _u64p, _u64p, C.c_uint64,
                                                    C.POINTER(C.c_double)]
+        L.refdrv_factorize_approximate_logged.restype = C.c_int64
+        L.refdrv_factorize_approximate_logged.argtypes = [_u8p, C.c_uint64, C.c_int, C.c_int, C.c_int, _u64p, _u64p, C.c_uint64,
+                                                          C.POINTER(C.c_double), C.c_char_p, C.c_uint64]
         L.refdrv_decode.argtypes = [_u64p, _u64p, C.c_uint64, _u8p, C.c_uint64]
         _u32p_ = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
         L.refdrv_rks.restype = C.c_int64
@@ -207,6 +210,40 @@ def ref_factorize(text, tau, p=1, phr_mode=LPF_OPT, fact_mode=GREEDY, sss_base=D
     z = L.refdrv_factorize_approximate(t, t.size, phr_mode, fact_mode, p, src, ln, cap, C.byref(sec))
     assert 0 <= z <= cap, z
     return src[:z].copy(), ln[:z].copy(), bases, sec.value
+
+
+def ref_require():
+    """LZ77SSS_REQUIRE_REF=1: a missing oracle/_ref build is a failure, not a skip (the driver's GPU box gets the prebuilt
+    files with the snapshot)."""
+    return os.environ.get("LZ77SSS_REQUIRE_REF", "") == "1"
+
+
+def ref_factorize_logged(text, tau, p=1, phr_mode=LPF_OPT, fact_mode=GREEDY, sss_base=DEFAULT_SSS_BASE, qmax=DEFAULT_QMAX):
+    """The reference's factorize_approximate with parameters::log = true.  Returns (src, len, bases, seconds, phases):
+    phases = the key=value pairs of the reference's own RESULT line (times in ns; lz77_sss.hpp:298-311,357-365)."""
+    t = _text(text)
+    L = ref(tau)
+    L.refdrv_set_sss_params(sss_base, qmax)
+    bases = np.zeros(5, dtype=np.uint64)
+    L.refdrv_peek_next_bases(bases)
+    cap = t.size + 1
+    src = np.zeros(cap, dtype=np.uint64); ln = np.zeros(cap, dtype=np.uint64)
+    sec = C.c_double(0)
+    buf = C.create_string_buffer(4096)
+    z = L.refdrv_factorize_approximate_logged(t, t.size, phr_mode, fact_mode, p, src, ln, cap, C.byref(sec), buf, 4096)
+    assert 0 <= z <= cap, z
+    phases = {}
+    for tok in buf.value.decode().split():
+        if "=" in tok:
+            k, v = tok.split("=", 1)
+            try:
+                phases[k] = int(v)
+            except ValueError:
+                try:
+                    phases[k] = float(v)
+                except ValueError:
+                    phases[k] = v
+    return src[:z].copy(), ln[:z].copy(), bases, sec.value, phases
 
 
 def ref_decode(src, ln, n, tau=512):

@@ -23,6 +23,16 @@ def _eq(a, b):
     return a.size == b.size and (a == b).all()
 
 
+def _need_ref(oracle, tau):
+    """oracle/_ref (the reference's own headers, built in the CPU container) travels with the snapshot; without it the
+    test is skipped, or fails when LZ77SSS_REQUIRE_REF=1."""
+    if oracle.ref_available(tau):
+        return
+    if oracle.ref_require():
+        pytest.fail(f"oracle/_ref/libref_tau{tau}.so is missing and LZ77SSS_REQUIRE_REF=1")
+    pytest.skip("oracle/_ref was not prebuilt")
+
+
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
 def test_golden_vectors(capi, path):
     g = np.load(path)
@@ -62,8 +72,7 @@ def test_golden_vectors_all_modes(capi, path):
 def test_modes_against_reference_build(capi, oracle, fm, pm):
     """Fresh inputs against oracle/_ref (the reference's own headers), where that build travelled to this box."""
     tau = 64
-    if not oracle.ref_available(tau):
-        pytest.skip("oracle/_ref was not prebuilt")
+    _need_ref(oracle, tau)
     for name, text in _texts().items():
         if name in ("zeros", "period3"):
             continue      # no LPF phrase or no gap: pattern lengths undefined in the reference (SURVEY.md A7)
@@ -233,8 +242,7 @@ def test_sharded_single_text_equals_sequential(capi, oracle, world):
 def test_sharded_greedy_naive_and_small_slices(capi, oracle, monkeypatch):
     monkeypatch.setenv("LZ77SSS_SLICE_LEN", "30000")      # several slices per range: the resumed passes walk them all
     tau = 64
-    if not oracle.ref_available(tau):
-        pytest.skip("oracle/_ref was not prebuilt")
+    _need_ref(oracle, tau)
     for name in ("rep", "dna", "xx"):
         text = _texts()[name]
         for fm in (oracle.GREEDY, oracle.GREEDY_NAIVE):
@@ -246,8 +254,7 @@ def test_sharded_greedy_naive_and_small_slices(capi, oracle, monkeypatch):
 def test_lnf_regression_dna52(capi, oracle):
     """The input on which a fused two-sided candidate kernel faulted (see lpf.cu, all_candidates_kernel)."""
     tau = 64
-    if not oracle.ref_available(tau):
-        pytest.skip("oracle/_ref was not prebuilt")
+    _need_ref(oracle, tau)
     text = synth.dna_collection(400_000, seed=52, chrom_len=50_000)
     for pm in (oracle.LPF_LNF_NAIVE, oracle.LPF_LNF_OPT):
         rs, rl, bases, _ = oracle.ref_factorize(text, tau, p=1, phr_mode=pm)
@@ -302,8 +309,7 @@ def _poly_prefix(text, base, upto):
 def test_rabin_karp_substring_against_reference(capi, oracle, n):
     """rabin_karp_substring<31> (rabin_karp_substring.hpp:35-240): the reference's own table `fps` for several sampling
     rates and its substring() on random queries, same base (drawn by the reference, pinned generator)."""
-    if not oracle.ref_available(512):
-        pytest.skip("oracle/_ref was not prebuilt")
+    _need_ref(oracle, 512)
     rng = np.random.default_rng(n)
     text = synth.random_repetitive(max(n, 64), seed=n)[:n] if n > 40 else rng.integers(0, 256, size=n).astype(np.uint8)
     nq = 400
@@ -360,6 +366,57 @@ def _check_factors(text, src, ln):
         s, l, p = int(src[k]), int(ln[k]), int(pos[k])
         l = min(l, 4096)
         assert (text[s:s + l] == text[p:p + l]).all()
+
+
+def _stream_hash(src, ln):
+    import hashlib
+    h = hashlib.sha256()
+    h.update(np.ascontiguousarray(src, dtype=np.uint64).tobytes())
+    h.update(np.ascontiguousarray(ln, dtype=np.uint64).tobytes())
+    return h.hexdigest()
+
+
+def _bit_exact_against_reference(capi, oracle, text, tau, p):
+    """factor stream of the CUDA path == factor stream of the reference's own code (oracle/_ref), same tau, same
+    num_threads, same gap-index bases.  p > 1 only where the reference itself factorizes sequentially: its parallel gap
+    path (lz77_sss.hpp:470-474, taken for rel_len_gaps > 0.2) is not run-to-run deterministic."""
+    _need_ref(oracle, tau)
+    rs, rl, bases, sec = oracle.ref_factorize(text, tau, p=p)
+    with capi.Factorizer(tau=tau, num_threads=p, gap_bases=bases) as F:
+        src, ln = F.factorize(text)
+        st = F.stats()
+        if p > 1:
+            assert (text.size - st["len_lpf_phr"]) / text.size <= 0.2, "the reference takes its racy parallel gap path here"
+        assert src.size == rs.size, (src.size, rs.size)
+        assert _eq(src, rs) and _eq(ln, rl)
+        assert _stream_hash(src, ln) == _stream_hash(rs, rl)
+        assert (F.decode(src, ln, text.size) == text).all()
+    return st, sec
+
+
+def test_c1_64mib_bit_exact_against_reference(capi, oracle):
+    """BASELINE config C1 at its full size: 64 MiB random_repetitive_string, tau = 512, the factor STREAM (not only its
+    properties) against the reference build."""
+    text = synth.random_repetitive(64 << 20, seed=1)
+    _bit_exact_against_reference(capi, oracle, text, 512, 1)
+
+
+def test_c2_first_256mib_bit_exact_against_reference(capi, oracle):
+    """The first 256 MiB of the bench text (BASELINE config C2), num_threads = 1: one full emission slice with carried
+    state, 2^24 table entries, 131072 parse blocks."""
+    text = synth.dna_collection(256 << 20, seed=2, chrom_len=16 << 20)
+    st, _ = _bit_exact_against_reference(capi, oracle, text, 512, 1)
+    assert st["parse_slices"] >= 1
+
+
+def test_c2_1gib_bit_exact_against_reference(capi, oracle):
+    """The whole bench text (1 GiB, 4 emission slices with the table carried between them), at the thread count the
+    reference arm of bench.py uses: the reference factorizes sequentially there (rel_len_gaps = 0.12)."""
+    text = synth.dna_collection(1 << 30, seed=2, chrom_len=16 << 20)
+    p = min(os.cpu_count() or 1, 64)
+    st, sec = _bit_exact_against_reference(capi, oracle, text, 512, p)
+    assert st["parse_slices"] == 4
+    print(f"reference: {sec:.2f} s at {p} threads")
 
 
 def test_c1_64mib_properties(capi):

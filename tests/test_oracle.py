@@ -103,3 +103,62 @@ def test_decode_rejects_bad_stream(oracle):
     ln = np.array([0, 3, 2], dtype=np.uint64)
     out = np.zeros(6, dtype=np.uint8)
     assert oracle.core().oracle_decode(src, ln, 3, out, 6) != 0
+
+
+REF_SRC = "/root/reference/include"
+
+
+def test_reference_own_gtest_passes_against_the_shim():
+    """the reference's own tests/test_lz77_sss.cpp (8 approximate, 4 naive-exact, 2 with-samples,
+    2 without-samples mode combinations; decode(factorize(T)) == T), compiled where it lies against oracle/shim with the
+    reference's debug asserts ON (`make -C oracle reftests`).  Only in the container that holds /root/reference."""
+    import subprocess
+    if not os.path.isdir(REF_SRC):
+        pytest.skip("no /root/reference on this machine")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.run(["make", "-s", "-C", os.path.join(root, "oracle"), "reftests"], check=True)
+    env = dict(os.environ, LZ77_SSS_TEST_ITERATIONS="150")
+    r = subprocess.run([os.path.join(root, "oracle", "_ref", "test-lz77-sss")], capture_output=True, text=True, env=env, timeout=900)
+    assert r.returncode == 0 and "[  PASSED  ] 4 tests." in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_reference_debug_asserts_hold_on_the_golden_inputs():
+    """The reference build WITHOUT -DNDEBUG (`make -C oracle refdbg`): its own asserts execute on the golden texts in every
+    phrase and factorize mode — lce_sss.hpp:167,173 (lce_lr == naive LCE: the shim's S is tau-synchronizing),
+    lpf_opt.cpp:91-97 (LPF phrases are real matches), greedy.cpp:81-89,119-125 (every emitted factor matches the text) —
+    and the streams equal the -DNDEBUG build's.  A failed assert aborts the subprocess."""
+    import subprocess
+    import sys
+    if not os.path.isdir(REF_SRC):
+        pytest.skip("no /root/reference on this machine")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.run(["make", "-s", "-j4", "-C", os.path.join(root, "oracle"), "refdbg"], check=True)
+    code = r"""
+import ctypes as C, glob, os, sys, numpy as np
+sys.path.insert(0, %r); sys.path.insert(0, os.path.join(%r, "tests"))
+import oracle_lib as O
+u8 = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS"); u64 = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+runs = 0
+for tau in (16, 64, 512):
+    L = C.CDLL(os.path.join(O.ORACLE_DIR, "_ref", f"libref_dbg_tau{tau}.so"))
+    L.refdrv_factorize_approximate.restype = C.c_int64
+    L.refdrv_factorize_approximate.argtypes = [u8, C.c_uint64, C.c_int, C.c_int, C.c_int, u64, u64, C.c_uint64, C.POINTER(C.c_double)]
+    for path in sorted(glob.glob(os.path.join(%r, "tests", "golden", "*.npz"))):
+        if os.path.basename(path).startswith("modes_"):
+            continue
+        text = np.ascontiguousarray(np.load(path)["text"])[:120_000]
+        for fm in (0, 1, 2):
+            for pm in (0, 1, 2, 3):
+                for p in (1, 3):
+                    cap = text.size + 1
+                    s = np.zeros(cap, np.uint64); l = np.zeros(cap, np.uint64)
+                    z = L.refdrv_factorize_approximate(text, text.size, pm, fm, p, s, l, cap, None)
+                    assert z > 0
+                    # same call order on both libraries: their pinned base generators advance in lockstep
+                    rs, rl, _, _ = O.ref_factorize(text, tau, p=p, phr_mode=pm, fact_mode=fm)
+                    assert z == rs.size and (s[:z] == rs).all() and (l[:z] == rl).all(), (tau, path, fm, pm, p)
+                    runs += 1
+print("asserts held in", runs, "runs")
+""" % (root, root, root)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0 and "asserts held" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
