@@ -388,6 +388,13 @@ def main():
     st_e2e = F.stats()
     clocks = sampler.stop()
 
+    # one more, untimed, step with the per-kernel event timing on: the kernels that make up a step
+    F.kernel_profile(True)
+    step_resident()
+    F.kernel_profile(False)
+    prof_rows = F.kernel_profile_rows()
+    st_prof = F.stats()
+
     # the dominant streaming kernel (K1+K2), CUDA events on the library's own stream
     k_ms, s_size = F.time_sss_kernel(d_text, n, iters=10)
     # the other streaming kernel of the path: the prefix-fingerprint table of rabin_karp_substring<31> (row a19)
@@ -430,6 +437,18 @@ def main():
             out["other_kernels"] = [{"kernel": "rks_build_kernel (rabin_karp_substring<31> prefix fingerprints)", "bound": "hbm",
                                      "achieved": rks_gbs, "peak": peak, "unit": "GB/s", "frac": rks_gbs / peak,
                                      "algorithmic_bytes": int(rks_bytes), "kernel_ms": rks_ms}]
+        out.setdefault("other_kernels", [])
+        for r in prof_rows:         # live CUDA-event times of one profiled step; frac only where the kernel has a byte count
+            row = {"kernel": r["kernel"], "launches_per_step": r["launches"], "ms_per_step": r["ms"],
+                   "share_of_step": r["ms"] / (st_prof["t_total_ns"] / 1e6) if st_prof["t_total_ns"] else None}
+            if r["bytes"]:
+                gbs = r["bytes"] / (r["ms"] / 1e3) / 1e9
+                row.update(bound="hbm", achieved=gbs, peak=peak, unit="GB/s", frac=gbs / peak, algorithmic_bytes=r["bytes"])
+            else:
+                row.update(bound="latency (dependent loads)", achieved=None, frac=None)
+            out["other_kernels"].append(row)
+        out["index"] = {k: int(st_res[k]) for k in ("parse_slices", "sparse_slices", "sparse_fallbacks", "repair_entries",
+                                                    "parse_rounds", "gap_positions_hashed")}
         if not args.no_cpu_baseline:
             # the reference on the same text, tau and num_threads: its time (cpu_baseline) and, outside every timed
             # region, its factor stream against the CUDA path's for the bases the reference drew (parity_checked)

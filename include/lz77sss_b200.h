@@ -67,6 +67,7 @@ typedef struct lz77sss_stats {
     uint64_t h2d_bytes, d2h_bytes;   /* bytes copied host->device / device->host inside the call */
     uint64_t parse_rounds, parse_slices;   /* device emission: block-parse rounds over all slices, slices */
     uint64_t sparse_slices, sparse_fallbacks;  /* slices parsed with gap-only index entries / redone with all positions */
+    uint64_t repair_entries;               /* index entries added while parsing (positions under gap factors that ran over phrases) */
 } lz77sss_stats;
 
 /* factor callback: lz77_sss<pos_t>::factor {src,len} by value, in text order, on the calling thread
@@ -146,8 +147,16 @@ int lz77sss_rks_substring(lz77sss_rks* r, const uint64_t* pos, const uint64_t* l
 /* re-run the build `iters` times on the resident text; mean time (CUDA events on the library's stream) */
 int lz77sss_rks_time_build(lz77sss_rks* r, int iters, double* ms_out, uint64_t* launches_out);
 
-/* lz77_sss<pos_t>::decode (algorithms/common.cpp:33-54): z factors -> n bytes into the HOST buffer out. */
+/* lz77_sss<pos_t>::decode (algorithms/common.cpp:33-54): z factors -> n bytes into the HOST buffer out; any n < 2^63
+ * that fits the device (6 bytes of state per output byte below 4 GiB, 9 bytes above).  A malformed stream is
+ * LZ77SSS_E_ARG; chains that do not resolve are LZ77SSS_E_INTERNAL (never silently wrong output). */
 int lz77sss_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, uint64_t z, uint8_t* out, uint64_t n);
+
+/* Decode timing for bench.py: the factors are uploaded once, the decode kernels run `iters` times on the device (mean time
+ * by CUDA events on the library's stream, the output stays in HBM); d_expect (DEVICE pointer from
+ * lz77sss_device_text_alloc, or NULL) is compared with the decoded bytes on the device: *equal_out = 1 iff identical. */
+int lz77sss_time_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, uint64_t z, uint64_t n, int iters,
+                        double* ms_out, int* rounds_out, uint64_t* launches_out, const uint8_t* d_expect, int* equal_out);
 
 /* ---- stage-level entry points (used by the parity tests and by bench.py's kernel timing) ---- */
 /* Only the synchronizing set of a host text (stage K1+K2). count_out = |S|; S_out may be NULL. */
@@ -156,6 +165,13 @@ int lz77sss_build_sss(lz77sss_handle* h, const uint8_t* text, uint64_t n, uint64
 /* Re-run the K1+K2 kernel `iters` times on a device-resident text and return the mean kernel time (CUDA events). */
 int lz77sss_time_sss_kernel(lz77sss_handle* h, const uint8_t* d_text, uint64_t n, int iters, double* ms_out,
                             uint64_t* count_out);
+/* Per-kernel timing of the kernels that make up a step (bench.py's `other_kernels`): while enabled, the radix scatter,
+ * the gap-index hash kernel and the parse rounds are bracketed by CUDA events on the library's stream (one
+ * synchronization per launch, so a profiled call is not a timed call).  Rows accumulate over calls:
+ * name, total milliseconds, launches, algorithmic bytes (0 where the kernel is latency-bound by design). */
+int lz77sss_kernel_profile(lz77sss_handle* h, int enable);
+int lz77sss_kernel_profile_get(lz77sss_handle* h, uint32_t idx, char* name, uint32_t name_cap, double* ms, uint64_t* launches,
+                               uint64_t* bytes);
 /* Introspection of the last factorization on this handle (arrays of |S| entries unless noted). */
 int lz77sss_get_stats(lz77sss_handle* h, lz77sss_stats* out);
 int lz77sss_get_sss(lz77sss_handle* h, uint64_t* out, uint64_t cap, uint64_t* count);

@@ -28,7 +28,7 @@ EXPORTS = [
     "lz77sss_shard_prepare", "lz77sss_shard_table_entries", "lz77sss_shard_entry_guess", "lz77sss_shard_parse",
     "lz77sss_shard_factors", "lz77sss_shard_finish", "lz77sss_shard_index",
     "lz77sss_rks_create", "lz77sss_rks_destroy", "lz77sss_rks_table", "lz77sss_rks_fps", "lz77sss_rks_substring",
-    "lz77sss_rks_time_build",
+    "lz77sss_rks_time_build", "lz77sss_time_decode", "lz77sss_kernel_profile", "lz77sss_kernel_profile_get",
 ]
 
 
@@ -44,7 +44,7 @@ class Stats(C.Structure):
                [(k, C.c_uint64) for k in ("roll_threshold", "table_entries", "ctx_levels", "doubling_rounds",
                                           "gap_positions_hashed", "t_h2d_ns", "t_sss_ns", "t_sort_ns", "t_lce_ns",
                                           "t_lpf_ns", "t_d2h_ns", "t_chain_ns", "t_gap_hash_ns", "t_emit_ns", "t_total_ns",
-                                          "kernel_launches", "h2d_bytes", "d2h_bytes", "parse_rounds", "parse_slices", "sparse_slices", "sparse_fallbacks")]
+                                          "kernel_launches", "h2d_bytes", "d2h_bytes", "parse_rounds", "parse_slices", "sparse_slices", "sparse_fallbacks", "repair_entries")]
 
     def as_dict(self):
         d = {}
@@ -108,6 +108,11 @@ def lib():
         L.lz77sss_rks_fps.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.lz77sss_rks_substring.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.lz77sss_rks_time_build.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+        L.lz77sss_time_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_double),
+                                          C.POINTER(C.c_int), C.POINTER(C.c_uint64), C.c_void_p, C.POINTER(C.c_int)]
+        L.lz77sss_kernel_profile.argtypes = [C.c_void_p, C.c_int]
+        L.lz77sss_kernel_profile_get.argtypes = [C.c_void_p, C.c_uint32, C.c_char_p, C.c_uint32, C.POINTER(C.c_double),
+                                                 C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -210,6 +215,15 @@ class Factorizer:
         _check(lib().lz77sss_decode(self._h, _ptr(src), _ptr(ln), src.size, _ptr(out), n))
         return out
 
+    def time_decode(self, src, ln, n, iters=5, d_expect=None):
+        """Device-resident decode timing: (mean ms, pointer-jumping rounds, kernel launches per decode, output == d_expect)."""
+        src = np.ascontiguousarray(src, dtype=np.uint64)
+        ln = np.ascontiguousarray(ln, dtype=np.uint64)
+        ms, rounds, launches, eq = C.c_double(0), C.c_int(0), C.c_uint64(0), C.c_int(-1)
+        _check(lib().lz77sss_time_decode(self._h, _ptr(src), _ptr(ln), src.size, n, iters, C.byref(ms), C.byref(rounds),
+                                         C.byref(launches), d_expect, C.byref(eq)))
+        return ms.value, rounds.value, int(launches.value), (None if d_expect is None else bool(eq.value))
+
     # --- stage-level -----------------------------------------------------------------------------
     def build_sss(self, text):
         t = _u8(text)
@@ -223,6 +237,21 @@ class Factorizer:
         ms, cnt = C.c_double(0), C.c_uint64(0)
         _check(lib().lz77sss_time_sss_kernel(self._h, d_text, n, iters, C.byref(ms), C.byref(cnt)))
         return ms.value, int(cnt.value)
+
+    def kernel_profile(self, enable):
+        _check(lib().lz77sss_kernel_profile(self._h, int(enable)))
+
+    def kernel_profile_rows(self):
+        rows = []
+        idx = 0
+        while True:
+            name = C.create_string_buffer(128)
+            ms, launches, nbytes = C.c_double(0), C.c_uint64(0), C.c_uint64(0)
+            if lib().lz77sss_kernel_profile_get(self._h, idx, name, 128, C.byref(ms), C.byref(launches), C.byref(nbytes)) != 0:
+                break
+            rows.append({"kernel": name.value.decode(), "ms": ms.value, "launches": int(launches.value), "bytes": int(nbytes.value)})
+            idx += 1
+        return rows
 
     def stats(self):
         st = Stats()

@@ -27,6 +27,30 @@
 namespace lz77sss {
 unsigned long long g_kernel_launches = 0;
 bool g_sync_every_kernel = getenv("LZ77SSS_SYNC_KERNELS") != nullptr;
+bool g_prof_on = false;
+namespace {
+struct prof_row { std::string name; double ms = 0; uint64_t launches = 0, bytes = 0; };
+std::vector<prof_row> g_prof;
+cudaEvent_t g_prof_e0 = nullptr, g_prof_e1 = nullptr;
+}
+void prof_begin(cudaStream_t st) {
+    if (!g_prof_e0) {
+        CUDA_CHECK(cudaEventCreate(&g_prof_e0));
+        CUDA_CHECK(cudaEventCreate(&g_prof_e1));
+    }
+    CUDA_CHECK(cudaEventRecord(g_prof_e0, st));
+}
+void prof_end(cudaStream_t st, const char* name, uint64_t bytes) {
+    CUDA_CHECK(cudaEventRecord(g_prof_e1, st));
+    CUDA_CHECK(cudaEventSynchronize(g_prof_e1));
+    float ms = 0;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, g_prof_e0, g_prof_e1));
+    for (auto& r : g_prof)
+        if (r.name == name) { r.ms += ms; r.launches++; r.bytes += bytes; return; }
+    prof_row r;
+    r.name = name; r.ms = ms; r.launches = 1; r.bytes = bytes;
+    g_prof.push_back(r);
+}
 }
 
 using namespace lz77sss;
@@ -97,6 +121,9 @@ struct lz77sss_handle {
     std::vector<uint8_t*> user_texts;
     // device emission
     gap_parse_scratch gp;
+    decode_scratch dec;
+    dbuf<uint64_t> dec_src, dec_len;
+    dbuf<uint8_t> dec_out;
     std::vector<uint64_t> f_src, f_len;
     uint64_t slice_len = 1ull << 28;
     uint32_t block_len = 2048;
@@ -986,6 +1013,7 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     st.parse_slices = h->gp.slices;
     st.sparse_slices = h->gp.sparse_slices;
     st.sparse_fallbacks = h->gp.sparse_fallbacks;
+    st.repair_entries = h->gp.repair_entries;
     st.t_gap_hash_ns = ns_since(t0);
 
     t0 = clk::now();
@@ -1435,17 +1463,50 @@ int lz77sss_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, 
         CUDA_CHECK(cudaSetDevice(h->cfg.device));
         if (n == 0) return LZ77SSS_OK;
         if (z == 0) return fail(LZ77SSS_E_ARG, "no factors");
-        dbuf<uint64_t> d_src, d_len;
-        dbuf<uint8_t> d_out;
-        d_src.reserve(z); d_len.reserve(z); d_out.reserve(n);
-        CUDA_CHECK(cudaMemcpyAsync(d_src.get(), src, z * 8, cudaMemcpyHostToDevice, h->st));
-        CUDA_CHECK(cudaMemcpyAsync(d_len.get(), len, z * 8, cudaMemcpyHostToDevice, h->st));
+        h->dec_src.reserve(z); h->dec_len.reserve(z); h->dec_out.reserve(n);
+        CUDA_CHECK(cudaMemcpyAsync(h->dec_src.get(), src, z * 8, cudaMemcpyHostToDevice, h->st));
+        CUDA_CHECK(cudaMemcpyAsync(h->dec_len.get(), len, z * 8, cudaMemcpyHostToDevice, h->st));
         int rounds = 0;
-        int rc = decode_factors(d_src, d_len, z, d_out, n, h->st, &rounds);
-        if (rc == -3) return fail(LZ77SSS_E_UNSUPPORTED, "decode: n >= 2^32 not built yet");
+        int rc = decode_factors(h->dec_src, h->dec_len, z, h->dec_out, n, h->st, &rounds, h->dec);
+        if (rc == -4) return fail(LZ77SSS_E_INTERNAL, "decode: the copy chains did not resolve");
         if (rc) return fail(LZ77SSS_E_ARG, "decode: malformed factor stream (lengths do not add up to n or a source is not earlier text)");
-        CUDA_CHECK(cudaMemcpyAsync(out, d_out.get(), n, cudaMemcpyDeviceToHost, h->st));
+        CUDA_CHECK(cudaMemcpyAsync(out, h->dec_out.get(), n, cudaMemcpyDeviceToHost, h->st));
         CUDA_CHECK(cudaStreamSynchronize(h->st));
+        return LZ77SSS_OK;
+    });
+}
+
+int lz77sss_time_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, uint64_t z, uint64_t n, int iters,
+                        double* ms_out, int* rounds_out, uint64_t* launches_out, const uint8_t* d_expect, int* equal_out) {
+    if (!h || !src || !len || iters <= 0 || !n || !z) return fail(LZ77SSS_E_ARG, "bad argument");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        h->dec_src.reserve(z); h->dec_len.reserve(z); h->dec_out.reserve(n);
+        CUDA_CHECK(cudaMemcpyAsync(h->dec_src.get(), src, z * 8, cudaMemcpyHostToDevice, h->st));
+        CUDA_CHECK(cudaMemcpyAsync(h->dec_len.get(), len, z * 8, cudaMemcpyHostToDevice, h->st));
+        cudaEvent_t e0, e1;
+        CUDA_CHECK(cudaEventCreate(&e0));
+        CUDA_CHECK(cudaEventCreate(&e1));
+        double total = 0;
+        int rounds = 0;
+        unsigned long long l0 = 0;
+        for (int it = -1; it < iters; it++) {     // one untimed warm-up
+            l0 = g_kernel_launches;
+            CUDA_CHECK(cudaEventRecord(e0, h->st));
+            const int rc = decode_factors(h->dec_src, h->dec_len, z, h->dec_out, n, h->st, &rounds, h->dec);
+            CUDA_CHECK(cudaEventRecord(e1, h->st));
+            CUDA_CHECK(cudaEventSynchronize(e1));
+            if (rc) return fail(rc == -4 ? LZ77SSS_E_INTERNAL : LZ77SSS_E_ARG, "decode failed");
+            float ms = 0;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+            if (it >= 0) total += ms;
+        }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        if (ms_out) *ms_out = total / iters;
+        if (rounds_out) *rounds_out = rounds;
+        if (launches_out) *launches_out = g_kernel_launches - l0;
+        if (d_expect && equal_out) *equal_out = device_equal(h->dec_out.get(), d_expect, n, h->st) ? 1 : 0;
         return LZ77SSS_OK;
     });
 }
@@ -1502,6 +1563,25 @@ int lz77sss_time_sss_kernel(lz77sss_handle* h, const uint8_t* d_text, uint64_t n
         if (count_out) *count_out = size_s;
         return LZ77SSS_OK;
     });
+}
+
+int lz77sss_kernel_profile(lz77sss_handle* h, int enable) {
+    if (!h) return fail(LZ77SSS_E_ARG, "null argument");
+    g_prof_on = enable != 0;
+    if (enable) g_prof.clear();
+    return LZ77SSS_OK;
+}
+
+int lz77sss_kernel_profile_get(lz77sss_handle* h, uint32_t idx, char* name, uint32_t name_cap, double* ms, uint64_t* launches,
+                               uint64_t* bytes) {
+    if (!h || !name || !name_cap) return fail(LZ77SSS_E_ARG, "null argument");
+    if (idx >= g_prof.size()) return fail(LZ77SSS_E_ARG, "no such profile row");
+    const auto& r = g_prof[idx];
+    snprintf(name, name_cap, "%s", r.name.c_str());
+    if (ms) *ms = r.ms;
+    if (launches) *launches = r.launches;
+    if (bytes) *bytes = r.bytes;
+    return LZ77SSS_OK;
 }
 
 int lz77sss_get_stats(lz77sss_handle* h, lz77sss_stats* out) {

@@ -34,6 +34,14 @@ extern bool g_sync_every_kernel;   // LZ77SSS_SYNC_KERNELS=1: device-synchronize
             ::lz77sss::cuda_check(cudaDeviceSynchronize(), "kernel execution", __FILE__, __LINE__); \
     } while (0)
 
+// Optional per-kernel timing of the heavy kernels (lz77sss_kernel_profile): CUDA events around the launch on its own
+// stream, one synchronization per launch while enabled (so a profiled run is not a timed run).
+extern bool g_prof_on;
+void prof_begin(cudaStream_t st);
+void prof_end(cudaStream_t st, const char* name, uint64_t algorithmic_bytes);
+#define PROF_BEGIN(st) do { if (::lz77sss::g_prof_on) ::lz77sss::prof_begin(st); } while (0)
+#define PROF_END(st, name, bytes) do { if (::lz77sss::g_prof_on) ::lz77sss::prof_end(st, name, bytes); } while (0)
+
 // Owning device buffer (cudaMallocAsync on the handle's stream would also do; plain cudaMalloc keeps
 // the allocation pattern visible and the buffers are reused across calls of one handle).
 template <typename T>

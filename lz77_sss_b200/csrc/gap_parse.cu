@@ -94,6 +94,7 @@ __global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restr
     const uint64_t t0 = (uint64_t)blockIdx.x * GE_TILE;                   // tile start, slice-relative
     const uint64_t g0 = a0 + t0;                                          // text position of the tile
     const uint32_t in_tile = cnt - t0 < (uint64_t)GE_TILE ? (uint32_t)(cnt - t0) : (uint32_t)GE_TILE;
+    if (skip && tile_off[blockIdx.x + 1] == tile_off[blockIdx.x]) return;   // sparse slice: no position of this tile needs entries
     // stage GE_TILE + GE_HALO text bytes (the device text is zero-padded behind n); g0 is 16-byte aligned
     // whenever a0 is (slices start at multiples of the slice length); fall back to byte loads otherwise
     if ((g0 & 15) == 0) {
@@ -247,7 +248,11 @@ struct parse_ctx {
     const uint64_t* Hc;        // last inserted position + 1 per bucket (0 = none), state before the slice
     const uint32_t* notins;    // bit = 1: position of the slice is NOT inserted
     const uint32_t* skip;      // sparse slice: bit = 1: the position has no entries (nullptr: every position has)
-    uint8_t* ovr;              // per block: its parse needed entries that a sparse slice does not have
+    const uint64_t* rk;        // sparse slice: entries added after the sort (repair list), (bucket << 32 | entry id) ascending
+    uint32_t R;                // number of entries in the repair list
+    uint32_t* req;             // sparse slice: req[0] = number of repair requests of this round, then (beg, end) pairs
+    uint32_t req_cap;          //   (slice-relative positions that a parse needs entries for)
+    uint8_t* ovr;              // per block: its parse needed entries that a sparse slice does not have (yet)
     uint8_t* dirty;            // per block: an input of its parse (entry state, a bitmap bit or a table entry that one
                                // of its probes can have read) changed since it was parsed
     const uint64_t* ml_beg;
@@ -268,14 +273,44 @@ __device__ __forceinline__ bool not_inserted(const uint32_t* __restrict__ bm, ui
     return (bm[rel >> 5] >> (rel & 31)) & 1u;
 }
 
-// longest_prev_occ (factorize/common.cpp:33-61) at position i, all 32 lanes; lanes 0..4 own patterns 4..0
+// sparse slice: a parse needs entries for the positions [s, e) of the text (clipped to the slice)
+__device__ __forceinline__ void file_request(const parse_ctx& C, uint64_t s, uint64_t e) {
+    if (e > C.a1) e = C.a1;
+    if (s >= e) return;
+    const uint32_t k = atomicAdd(C.req, 1u);
+    if (k < C.req_cap) {
+        C.req[2 + 2 * k] = (uint32_t)(s - C.a0);
+        C.req[3 + 2 * k] = (uint32_t)(e - C.a0);
+    }
+}
+// does any position of [s, e) (text positions inside the slice) lack entries?  All 32 lanes.
+__device__ __forceinline__ bool warp_any_skip(const parse_ctx& C, uint64_t s, uint64_t e) {
+    if (e > C.a1) e = C.a1;
+    if (s >= e) return false;
+    const unsigned lane = threadIdx.x & 31;
+    const uint64_t rs = s - C.a0, re = e - C.a0;
+    const uint64_t w0 = rs >> 5, w1 = (re - 1) >> 5;
+    bool any = false;
+    for (uint64_t w = w0 + lane; w <= w1 && !any; w += 32) {
+        uint32_t m = 0xFFFFFFFFu;
+        if (w == w0) m &= 0xFFFFFFFFu << (rs & 31);
+        if (w == w1) m &= 0xFFFFFFFFu >> (31 - ((re - 1) & 31));
+        any = (C.skip[w] & m) != 0;
+    }
+    return __any_sync(0xffffffffu, any);
+}
+
+// longest_prev_occ (factorize/common.cpp:33-61) at position i, all 32 lanes; lanes 0..4 own patterns 4..0.
+// "H[b] when i is probed" = the largest inserted position among the entries of bucket b in front of the probe's own
+// entry: the bucket's list of the sorted index and, on a sparse slice, of the repair list, else the carried table.
 template <typename pos_t>
 __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>& V, uint64_t i, uint64_t& f_src,
                                       uint64_t& f_len, bool& bad) {
     const unsigned lane = threadIdx.x & 31;
     const uint32_t rel = (uint32_t)(i - C.a0);
-    if (C.skip && ((C.skip[rel >> 5] >> (rel & 31)) & 1u)) {       // only a wrong speculation or an overrun gets here
-        bad = true;
+    if (C.skip && ((C.skip[rel >> 5] >> (rel & 31)) & 1u)) {       // a wrong speculation, or the position a gap factor that
+        bad = true;                                                 // ran over whole phrases lands on: ask for its entries
+        if (lane == 0) file_request(C, i, i + 1);
         f_src = V.T[i];
         f_len = 0;
         return;
@@ -285,20 +320,44 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
         const uint32_t e = 5u * rel + lane;
         const uint32_t b = C.tkey[e];
         const uint32_t lo = C.bstart[b];
-        uint32_t l = lo, h = C.bstart[b + 1];        // the own entry by binary search (entries ascend inside a bucket)
-        while (l + 1 < h) {
+        uint32_t l = lo, h = C.bstart[b + 1];        // entries in front of the own one: [lo, l) after the search
+        while (l < h) {
             const uint32_t mid = (l + h) >> 1;
-            if (C.sval[mid] <= e) l = mid;
+            if (C.sval[mid] < e) l = mid + 1;
             else h = mid;
         }
+        bool found = false;
         uint32_t kk = l;
-        while (true) {
-            if (kk == lo) { occ = C.Hc[b] - 1; break; }
+        while (kk > lo) {
             kk--;
             const uint32_t q = C.sval[kk] / 5u;
-            if (q == rel) { occ = i; break; }                     // an earlier pattern of this position wrote the bucket
-            if (!not_inserted(C.notins, q)) { occ = C.a0 + q; break; }
+            if (q == rel) { occ = i; found = true; break; }       // an earlier pattern of this position wrote the bucket
+            if (!not_inserted(C.notins, q)) { occ = C.a0 + q; found = true; break; }
         }
+        if (C.R) {
+            const uint64_t key = ((uint64_t)b << 32) | e;
+            uint32_t rl = 0, rh = C.R;
+            while (rl < rh) {
+                const uint32_t mid = (rl + rh) >> 1;
+                if (C.rk[mid] < key) rl = mid + 1;
+                else rh = mid;
+            }
+            while (rl > 0) {
+                rl--;
+                const uint64_t v = C.rk[rl];
+                if ((uint32_t)(v >> 32) != b) break;
+                const uint32_t q = (uint32_t)v / 5u;
+                uint64_t o2 = NONE64;
+                if (q == rel) o2 = i;
+                else if (!not_inserted(C.notins, q)) o2 = C.a0 + q;
+                if (o2 != NONE64) {
+                    if (!found || o2 > occ) occ = o2;
+                    found = true;
+                    break;
+                }
+            }
+        }
+        if (!found) occ = C.Hc[b] - 1;
     }
     const uint8_t ci = V.T[i];
     const bool valid = lane < 5 && occ != NONE64 && occ < i && V.T[occ] == ci;
@@ -342,7 +401,12 @@ __global__ void __launch_bounds__(128, 16) parse_kernel(const parse_ctx C, const
                     o_len -= i2 - pb;
                     i2 = pb;
                 } else {
-                    bad = true;                     // positions inside a phrase get inserted: a sparse slice lacks them
+                    // the positions of the phrases the factor ran over get inserted, and the position it lands on is probed
+                    // if it lies inside a phrase (greedy.cpp:68-77,111-117): a sparse slice may lack their entries
+                    if (C.skip && warp_any_skip(C, pb, i2 + 1)) {
+                        bad = true;
+                        if (lane == 0) file_request(C, pb, i2 + 1);
+                    }
                     while (C.ml_end[k] <= i2) k++;
                 }
             }
@@ -540,12 +604,34 @@ __global__ void __launch_bounds__(256) dirty_from_bitmap_kernel(const parse_ctx 
                 if (C.sval[mid] <= e) l = mid;
                 else h = mid;
             }
-            for (uint32_t kk = l + 1; kk < hi; kk++) {
+            // (the entries of a position of the repair list are not in this list: start at the first entry behind e)
+            for (uint32_t kk = C.sval[l] <= e ? l + 1 : l; kk < hi; kk++) {
                 const uint32_t q = C.sval[kk] / 5u;
                 // a probe inserts its position: a position that neither parse inserts is not probed by either
                 const bool oi = !not_inserted(old_bm, q), ni = !not_inserted(new_bm, q);
                 if (oi || ni) C.dirty[q / C.BL] = 1;
                 if (oi && ni) break;
+            }
+        }
+        if (C.R) {                                   // the same walk over the repair list
+            for (uint32_t pat = 0; pat < 5; pat++) {
+                const uint32_t e = 5u * (uint32_t)rel + pat;
+                const uint32_t b = C.tkey[e];
+                const uint64_t key = ((uint64_t)b << 32) | e;
+                uint32_t rl = 0, rh = C.R;
+                while (rl < rh) {
+                    const uint32_t mid = (rl + rh) >> 1;
+                    if (C.rk[mid] <= key) rl = mid + 1;
+                    else rh = mid;
+                }
+                for (; rl < C.R; rl++) {
+                    const uint64_t v = C.rk[rl];
+                    if ((uint32_t)(v >> 32) != b) break;
+                    const uint32_t q = (uint32_t)v / 5u;
+                    const bool oi = !not_inserted(old_bm, q), ni = !not_inserted(new_bm, q);
+                    if (oi || ni) C.dirty[q / C.BL] = 1;
+                    if (oi && ni) break;
+                }
             }
         }
     }
@@ -632,6 +718,66 @@ __global__ void clear_range_kernel(uint32_t* __restrict__ bm, uint64_t s, uint64
         if (w == w1) m &= 0xFFFFFFFFu >> (31 - ((e - 1) & 31));
         bm[w] &= ~m;
     }
+}
+
+// Sparse slice: entries for the positions the parses asked for (one warp per request).  A position is claimed by clearing
+// its skip bit; its five fingerprints are computed from scratch (L steps each: requests are few and short), the bucket ids
+// go to the time-order array like those of the sorted index, and (bucket << 32 | entry id) is appended to the repair list.
+__global__ void __launch_bounds__(128) repair_entries_kernel(const uint8_t* __restrict__ T, uint64_t n, const ghp5 hp, uint64_t a0,
+                                                             const uint32_t* __restrict__ req, uint32_t nreq,
+                                                             uint32_t* __restrict__ skip, uint32_t* __restrict__ tkey,
+                                                             uint64_t* __restrict__ rk, uint32_t* __restrict__ rcount,
+                                                             uint32_t rcap, uint32_t* __restrict__ first_pos) {
+    const uint32_t w = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const unsigned lane = threadIdx.x & 31;
+    if (w >= nreq) return;
+    const uint32_t s = req[2 + 2 * w], e = req[3 + 2 * w];
+    if (lane == 0) atomicMin(first_pos, s);
+    for (uint32_t p = s + lane; p < e; p += 32) {
+        const uint32_t bit = 1u << (p & 31);
+        if (!(skip[p >> 5] & bit)) continue;
+        if (!(atomicAnd(&skip[p >> 5], ~bit) & bit)) continue;        // another request claimed it
+        const uint64_t pos = a0 + p;
+        uint32_t key[5];
+#pragma unroll
+        for (int x = 0; x < 5; x++) {
+            const uint64_t L = hp.L[x];
+            key[4 - x] = hp.invalid_key;
+            if (pos + L < n) {
+                m107 fp;
+                fp.lo = fp.hi = 0;
+                for (uint64_t j = 0; j < L; j++) {
+                    m107 c;
+                    c.lo = T[pos + j]; c.hi = 0;
+                    fp = muladd107(fp, hp.base[x], c);
+                }
+                key[4 - x] = (uint32_t)(fp.lo & hp.mask);
+            }
+        }
+        const uint32_t slot = atomicAdd(rcount, 5u);
+#pragma unroll
+        for (int j = 0; j < 5; j++) {
+            tkey[5ull * p + j] = key[j];
+            if (slot + j < rcap) rk[slot + j] = ((uint64_t)key[j] << 32) | (5u * p + j);
+        }
+    }
+}
+
+// blocks from fb on are parsed again (their probes may see the new entries of the repair list)
+__global__ void dirty_from_block_kernel(uint8_t* __restrict__ dirty, uint32_t fb, uint32_t nb) {
+    const uint32_t b = fb + blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < nb) dirty[b] = 1;
+}
+
+// the repair list's share of the carried table
+__global__ void carry_repair_kernel(const parse_ctx C, uint32_t nbuckets, unsigned long long* __restrict__ Hc) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= C.R) return;
+    const uint64_t v = C.rk[k];
+    const uint32_t b = (uint32_t)(v >> 32);
+    if (b >= nbuckets) return;
+    const uint32_t q = (uint32_t)v / 5u;
+    if (!not_inserted(C.notins, q)) atomicMax(&Hc[b], (unsigned long long)(C.a0 + q + 1));
 }
 
 // carry the table over the slice: last inserted position per bucket.  One thread per bucket walks its list
@@ -774,9 +920,11 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
     sc.entries_sorted = 0;
     sc.sparse_slices = 0;
     sc.sparse_fallbacks = 0;
-    // Sparse slices pay only when no gap factor runs over a whole phrase; on the bench texts such overruns occur in
-    // every slice and the dense redo makes the attempt a loss, so it is opt-in (LZ77SSS_SPARSE_GAP_INDEX=1).
-    const bool sparse_ok = getenv("LZ77SSS_SPARSE_GAP_INDEX") != nullptr;
+    sc.repair_entries = 0;
+    // Sparse slices (entries only for the positions the reference can insert when no gap factor runs over a whole
+    // phrase; the positions such factors do run over are added to a small repair list while the parse iterates) are the
+    // default; LZ77SSS_SPARSE_GAP_INDEX=0 indexes every position of every slice.
+    const bool sparse_ok = !(getenv("LZ77SSS_SPARSE_GAP_INDEX") && getenv("LZ77SSS_SPARSE_GAP_INDEX")[0] == '0');
 
     sc.ml.reserve(3 * m);
     CUDA_CHECK(cudaMemcpyAsync(sc.ml.get(), h_ml, 3 * m * 8, cudaMemcpyHostToDevice, st));
@@ -826,8 +974,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         const uint32_t ntiles = ceil_div_u(cnt, GE_TILE);
         sc.slices++;
         // Attempt 0 (sparse): entries only for the positions that can be inserted or probed when no gap factor runs
-        // over a whole phrase (greedy.cpp:68-77), i.e. the gaps and the phrase starts.  If the converged parse
-        // did overrun (or the gaps are most of the slice anyway), attempt 1 redoes the slice with every position.
+        // over a whole phrase (greedy.cpp:68-77), i.e. the gaps and the phrase starts.  A parse that does run over a
+        // phrase asks for the entries of the positions it covers; they are hashed into the repair list, which the
+        // probes search next to the sorted index, and the blocks behind them are parsed again.  Attempt 1 (every
+        // position) is taken when the gaps are most of the slice anyway, or when the repair list outgrows its bound.
         // phrases that overlap the slice (the sentinel is not one of them)
         const uint64_t k0 = std::upper_bound(h_ml + m, h_ml + m + (m - 1), a0) - (h_ml + m);
         const uint64_t k1 = std::lower_bound(h_ml, h_ml + (m - 1), a1) - h_ml;
@@ -867,9 +1017,13 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         {
             // a dense slice has vals[e] = e (the sort generates them in its first pass) and keys = tkey (its first
             // pass reads tkey)
+            PROF_BEGIN(st);
             gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, sparse ? keys : nullptr, sc.tkey, sparse ? vals : nullptr,
                                                        sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
             KERNEL_CHECK();
+            // algorithmic bytes: the slice's text once, the bucket ids of its indexed positions in time order, and on a
+            // sparse slice the compacted (bucket, entry id) pairs for the sort
+            PROF_END(st, "gap_entries_kernel (5 rolling fingerprints mod 2^107-1)", cnt + (sparse ? E * 12 : 5 * cnt * 4));
         }
         if (E == 0) {                                  // no entry at all: every bucket list is empty
             CUDA_CHECK(cudaMemsetAsync(sc.bstart.get(), 0, (table_entries + 2) * 4, st));
@@ -923,6 +1077,22 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         C.Hc = reinterpret_cast<const uint64_t*>(sc.Hc.get());
         C.notins = sc.notins;
         C.skip = sparse ? sc.skip.get() : nullptr;
+        C.rk = nullptr; C.R = 0; C.req = nullptr; C.req_cap = 0;
+        uint32_t rcap = 0;
+        uint64_t *rk_cur = nullptr, *rk_alt = nullptr;
+        uint32_t *rv_cur = nullptr, *rv_alt = nullptr;
+        if (sparse) {
+            C.req_cap = std::max<uint32_t>(1u << 16, 4 * nb);
+            sc.req.reserve(2 + 2 * (uint64_t)C.req_cap);
+            C.req = sc.req;
+            rcap = (uint32_t)std::min<uint64_t>(1ull << 30, std::max<uint64_t>(1ull << 20, E / 2));
+            sc.rk0.reserve(rcap + 8); sc.rk1.reserve(rcap + 8); sc.rv0.reserve(rcap + 8); sc.rv1.reserve(rcap + 8);
+            rk_cur = sc.rk0; rk_alt = sc.rk1; rv_cur = sc.rv0; rv_alt = sc.rv1;
+            CUDA_CHECK(cudaMemsetAsync(sc.req.get(), 0, 8, st));
+        }
+        bool give_up_sparse = false;
+        uint64_t repair_total = 0;
+        uint32_t pending_fb = 0xFFFFFFFFu;          // blocks from here on see new repair entries in the next round
         C.ovr = sc.ovr;
         C.dirty = sc.dirty;
         C.ml_beg = sc.ml.get(); C.ml_end = sc.ml.get() + m; C.ml_src = sc.ml.get() + 2 * m; C.m = m;
@@ -934,6 +1104,33 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         block_state* d_exit = reinterpret_cast<block_state*>(sc.slice_exit.get());
         const unsigned gw = ceil_div_u((uint64_t)nb * 32, 128);
 
+        // sparse slice, after a parse round: hash the requested positions into the repair list and sort it
+        auto repair = [&]() -> bool {               // true: entries were added
+            uint32_t nreq = 0;
+            CUDA_CHECK(cudaMemcpyAsync(&nreq, sc.req.get(), 4, cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            if (!nreq) return false;
+            if (nreq > C.req_cap) { give_up_sparse = true; return false; }
+            CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 5, 0xFF, 4, st));
+            CUDA_CHECK(cudaMemcpyAsync(sc.changed.get() + 6, &C.R, 4, cudaMemcpyHostToDevice, st));
+            repair_entries_kernel<<<ceil_div_u((uint64_t)nreq * 32, 128), 128, 0, st>>>(d_text, n, hp, a0, sc.req, nreq, sc.skip, sc.tkey,
+                                                                                      rk_cur, sc.changed.get() + 6, rcap, sc.changed.get() + 5);
+            KERNEL_CHECK();
+            uint32_t r2[2];
+            CUDA_CHECK(cudaMemcpyAsync(r2, sc.changed.get() + 5, 8, cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaMemsetAsync(sc.req.get(), 0, 4, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            if (r2[1] > rcap) { give_up_sparse = true; return false; }
+            if (r2[1] == C.R) return false;
+            const uint32_t r_before = C.R;
+            C.R = r2[1];
+            radix_sort_pairs(rk_cur, rk_alt, rv_cur, rv_alt, C.R, 0, 32 + key_bits, sc.sort, st);
+            C.rk = rk_cur;
+            repair_total += C.R - r_before;
+            const uint32_t fb = r2[0] / BL;
+            if (fb < pending_fb) pending_fb = fb;
+            return true;
+        };
         const uint64_t stop = a1 < n_cut ? a1 : n_cut;
         bool converged = false;
         if (first.i < stop) {
@@ -955,9 +1152,12 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
                 KERNEL_CHECK();
             }
+            PROF_BEGIN(st);
             parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
             KERNEL_CHECK();
+            PROF_END(st, "parse_kernel (block-speculative greedy parse, latency-bound)", 0);
             sc.rounds++;
+            if (sparse) repair();
           }
             if (K) K->parsed = true;
             bool track = have_parse;    // follow single changes (resumed slices from the start, fresh ones once few are left)
@@ -992,11 +1192,21 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                     joined_chain_kernel<<<ceil_div_u(nb, 256), 256, 0, st>>>(C, sc.marked_prev.get());
                     KERNEL_CHECK();
                     if (!naive) {
+                        PROF_BEGIN(st);
                         dirty_from_bitmap_kernel<<<ceil_div_u(nwords, 8 * DB_WPW), 256, 0, st>>>(C, sc.notins_prev, nwords);   // 8 warps x DB_WPW words per CTA
                         KERNEL_CHECK();
+                        PROF_END(st, "dirty_from_bitmap_kernel (change tracking, latency-bound)", 0);
                     }
                 } else {
                     CUDA_CHECK(cudaMemsetAsync(sc.dirty.get(), 1, nb, st));
+                }
+                if (pending_fb != 0xFFFFFFFFu) {    // new repair entries: every block behind the first of them
+                    if (pending_fb < nb) {
+                        dirty_from_block_kernel<<<ceil_div_u(nb - pending_fb, 256), 256, 0, st>>>(sc.dirty, pending_fb, nb);
+                        KERNEL_CHECK();
+                    }
+                    if (pending_fb < C.bmin) C.bmin = pending_fb;
+                    pending_fb = 0xFFFFFFFFu;
                 }
                 if (have_parse && round == 1) {     // resumed slice: the table in front of it may have changed too
                     dirty_from_table_kernel<<<ceil_div_u(table_entries, 256), 256, 0, st>>>(C, sc.Hc_prev.get(), sc.notins_prev,
@@ -1006,8 +1216,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get(), 0, 4, st));
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 3, 0, 4, st));
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 4, 0xFF, 4, st));
+                PROF_BEGIN(st);
                 parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
                 KERNEL_CHECK();
+                PROF_END(st, "parse_kernel (block-speculative greedy parse, latency-bound)", 0);
                 sc.rounds++;
                 uint32_t chg = 0;
                 CUDA_CHECK(cudaMemcpyAsync(&chg, sc.changed.get(), 4, cudaMemcpyDeviceToHost, st));
@@ -1019,17 +1231,23 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                             (unsigned long long)round, d[0], nb, d[1]);
                 }
                 CUDA_CHECK(cudaMemcpyAsync(sc.notins_prev.get(), sc.notins.get(), nwords * 4, cudaMemcpyDeviceToDevice, st));
-                if (!chg) { converged = true; break; }
+                const bool repaired = sparse && repair();
+                if (give_up_sparse) break;
+                if (!chg && !repaired) { converged = true; break; }
                 if (!track) {
                     uint32_t d[2];                      // blocks whose trace or exit changed, the first of them
                     CUDA_CHECK(cudaMemcpy(d, sc.changed.get() + 3, 8, cudaMemcpyDeviceToHost));
-                    if (!sparse && (uint64_t)d[0] * track_div <= nb) {    // few changes left: follow them (blocks in front of the old
+                    if ((uint64_t)d[0] * track_div <= nb) {    // few changes left: follow them (blocks in front of the old
                         track = true;                   // bmin are still flagged and are parsed once more)
                         C.bmin = 0;
                     } else {
                         C.bmin = d[1];
                     }
                 }
+            }
+            if (give_up_sparse) {                       // the repair list outgrew its bound: index every position
+                sc.sparse_fallbacks++;
+                continue;
             }
             if (!converged) throw std::runtime_error("gap_parse: the block chain did not reach its fixed point");
             if (K) CUDA_CHECK(cudaMemcpyAsync(sc.Hc_prev.get(), sc.Hc.get(), table_entries * 8, cudaMemcpyDeviceToDevice, st));
@@ -1044,10 +1262,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             block_state ex;
             CUDA_CHECK(cudaMemcpyAsync(&ex, d_exit, sizeof ex, cudaMemcpyDeviceToHost, st));
             CUDA_CHECK(cudaStreamSynchronize(st));
-            if (sparse && overrun) {                    // the parse used positions that have no entries: redo dense
-                sc.sparse_fallbacks++;
-                continue;
-            }
+            if (sparse && overrun)                      // a converged parse has every entry it asked for
+                throw std::logic_error("gap_parse: a block of the converged parse still lacks index entries");
             if (zs) {
                 sc.fsrc.reserve(zs); sc.flen.reserve(zs);
                 gather_kernel<<<gw, 128, 0, st>>>(C, sc.cnt, sc.fsrc, sc.flen);
@@ -1072,6 +1288,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             KERNEL_CHECK();
             carry_big_kernel<<<1184, 128, 0, st>>>(C, sc.Hc.get(), sc.big, sc.changed.get() + 1);
             KERNEL_CHECK();
+            if (C.R) {
+                carry_repair_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(C, (uint32_t)table_entries, sc.Hc.get());
+                KERNEL_CHECK();
+            }
             first = ex;
         } else {
             // nothing to parse here, but positions up to first.i may have been inserted by a gap factor
@@ -1096,7 +1316,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             carry_big_kernel<<<1184, 128, 0, st>>>(C, sc.Hc.get(), sc.big, sc.changed.get() + 1);
             KERNEL_CHECK();
         }
-        if (sparse) sc.sparse_slices++;
+        if (sparse) { sc.sparse_slices++; sc.repair_entries += repair_total; }
         break;
       }
     }

@@ -136,6 +136,9 @@ struct gap_parse_scratch {
     dbuf<uint32_t> notins_prev;
     dbuf<unsigned long long> Hc_prev;
     dbuf<uint32_t> skip, tile_off;         // sparse slices: positions without entries, compaction offsets per tile
+    dbuf<uint64_t> rk0, rk1;               // sparse slices: repair list (bucket << 32 | entry id), ping-pong for its sort
+    dbuf<uint32_t> rv0, rv1, req;          // (unused payload of that sort), repair requests of a parse round
+    uint64_t repair_entries = 0;           // entries added to repair lists over all slices
     sort_scratch sort;
     scan_scratch scan;
     uint64_t rounds = 0, slices = 0, entries_sorted = 0, sparse_slices = 0, sparse_fallbacks = 0;
@@ -166,7 +169,15 @@ void rks_fps(const uint8_t* d_text, const rks_state& R, uint64_t s, uint64_t cnt
 
 // ---- decode.cu ------------------------------------------------------------------------------------
 // parallel LZ77 decode: factors (src,len) with len == 0 meaning literal src; returns 0 or an error code
+// returns 0, -1 (lengths do not add up to n), -2 (a source is not earlier text), -4 (no convergence)
+struct decode_scratch {
+    dbuf<uint8_t> start, ptr, tile_done;   // start / ptr hold 32- or 64-bit words depending on n
+    dbuf<uint16_t> res;
+    dbuf<uint64_t> tsum;
+    dbuf<unsigned long long> cnt;
+};
 int decode_factors(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uint8_t* d_out, uint64_t n,
-                   cudaStream_t st, int* rounds);
+                   cudaStream_t st, int* rounds, decode_scratch& sc);
+bool device_equal(const uint8_t* d_a, const uint8_t* d_b, uint64_t n, cudaStream_t st);
 
 }  // namespace lz77sss

@@ -355,9 +355,13 @@ void radix_pass(K* keys, K* kalt, uint32_t* vals, uint32_t* valt, uint64_t n, in
     KERNEL_CHECK();
     rs_colapply_kernel<NB><<<nchunks, NB, 0, st>>>(s.hist, ntiles, s.cpre, nchunks, s.offs);
     KERNEL_CHECK();
+    PROF_BEGIN(st);
     if (iota) rs_scatter_kernel<K, NB, true><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.offs, ntiles);
     else rs_scatter_kernel<K, NB, false><<<ntiles, RS_NT, 0, st>>>(keys, vals, kalt, valt, n, shift, mask, s.offs, ntiles);
     KERNEL_CHECK();
+    // algorithmic bytes: keys and payloads read once and written once (generated payloads are not read)
+    PROF_END(st, sizeof(K) == 4 ? "rs_scatter_kernel<u32> (radix pass of the gap index)" : "rs_scatter_kernel<u64> (radix pass of the SSS suffix sort)",
+             n * (2 * sizeof(K) + (iota ? 4 : 8)));
 }
 
 template <typename K>

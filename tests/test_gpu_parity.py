@@ -168,15 +168,20 @@ def test_short_inputs_end_of_text_rules(capi, oracle, n):
                 assert (F.decode(src, ln, n) == text).all()
 
 
-@pytest.mark.parametrize("env", [{"LZ77SSS_SPARSE_GAP_INDEX": "1"}, {"LZ77SSS_SLICE_LEN": "40000", "LZ77SSS_BLOCK_LEN": "64"},
-                                 {"LZ77SSS_SPARSE_GAP_INDEX": "1", "LZ77SSS_SLICE_LEN": "100000"}],
-                         ids=["sparse", "small_slices", "sparse_small_slices"])
+@pytest.mark.parametrize("env", [{}, {"LZ77SSS_SPARSE_GAP_INDEX": "0"}, {"LZ77SSS_SLICE_LEN": "40000", "LZ77SSS_BLOCK_LEN": "64"},
+                                 {"LZ77SSS_SPARSE_GAP_INDEX": "0", "LZ77SSS_SLICE_LEN": "100000"},
+                                 {"LZ77SSS_TRACK_DIV": "1", "LZ77SSS_BLOCK_LEN": "256"},
+                                 {"LZ77SSS_TRACK_DIV": "1000000000000", "LZ77SSS_SLICE_LEN": "150000"}],
+                         ids=["default_sparse", "dense", "sparse_small_slices", "dense_small_slices", "sparse_track_from_round_1",
+                              "sparse_never_track"])
 def test_emission_variants_give_the_same_factors(capi, oracle, env, monkeypatch):
-    """Slicing, block length and the sparse gap index (entries only for gaps and phrase starts, dense redo when a
-    gap factor overruns a phrase) are internal choices: the factor stream must not depend on them."""
+    """Slicing, block length, change tracking and the sparse gap index (entries only for gaps and phrase starts; the
+    positions under gap factors that run over whole phrases are added to a repair list while the parse iterates) are
+    internal choices: the factor stream must not depend on them."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     bases = (401, 70_001, 123_457, 999_983, 1_048_575)
+    repaired = sparse = 0
     for name, text in _texts().items():
         if name in ("zeros", "period3"):
             continue
@@ -190,6 +195,14 @@ def test_emission_variants_give_the_same_factors(capi, oracle, env, monkeypatch)
             with capi.Factorizer(tau=tau, num_threads=1, gap_bases=bases, fact_mode=fm) as F:
                 src, ln = F.factorize(text)
                 assert _eq(src, osrc) and _eq(ln, olen), (name, tau, fm, env)
+                st = F.stats()
+                repaired += st["repair_entries"]
+                sparse += st["sparse_slices"]
+                assert st["sparse_fallbacks"] == 0, (name, tau, fm, env)
+    if env.get("LZ77SSS_SPARSE_GAP_INDEX") == "0":
+        assert sparse == 0 and repaired == 0
+    else:
+        assert sparse > 0 and repaired > 0, "the sparse index and its repair list were not exercised"
 
 
 def _sharded_virtual(capi, text, world, tau, bases, fact_mode=None, env_slice=None):
@@ -436,6 +449,40 @@ def test_c2_quarter_gib_dna_properties(capi):
         src, ln = F.factorize(text)
         _check_factors(text, src, ln)
         assert (F.decode(src, ln, text.size) == text).all()
+
+
+def test_decode_handmade_streams(capi, oracle):
+    """decode (algorithms/common.cpp:33-54) on streams the factorizer would not produce: self-overlapping copies (runs and
+    longer periods), deep chains (every factor copies the one before it), and malformed streams, which must be refused."""
+    rng = np.random.default_rng(77)
+    cases = []
+    cases.append((np.array([97, 0], np.uint64), np.array([0, 999], np.uint64)))                         # a^1000
+    cases.append((np.array([97, 98, 99, 0], np.uint64), np.array([0, 0, 0, 5000], np.uint64)))          # (abc)^k
+    src, ln = [65, 66, 67, 68], [0, 0, 0, 0]                                                            # chain of depth 3000
+    pos = 4
+    for _ in range(3000):
+        src.append(pos - 4); ln.append(4); pos += 4
+    cases.append((np.array(src, np.uint64), np.array(ln, np.uint64)))
+    src, ln, pos = [], [], 0                                                                            # random mixture
+    for _ in range(20000):
+        if pos < 10 or rng.random() < 0.2:
+            src.append(int(rng.integers(0, 256))); ln.append(0); pos += 1
+        else:
+            l = int(rng.integers(1, 300)); s = int(rng.integers(0, pos))
+            src.append(s); ln.append(l); pos += l
+    cases.append((np.array(src, np.uint64), np.array(ln, np.uint64)))
+    with capi.Factorizer(tau=512) as F:
+        for src, ln in cases:
+            n = int(np.maximum(ln, 1).sum())
+            want = oracle.decode(src, ln, n)
+            assert (F.decode(src, ln, n) == want).all()
+            ms, rounds, launches, eq = F.time_decode(src, ln, n, iters=1)
+            assert rounds <= 16 and launches > 0
+        for src, ln, n in ((np.array([65, 5], np.uint64), np.array([0, 3], np.uint64), 4),      # source not earlier text
+                           (np.array([65, 0], np.uint64), np.array([0, 3], np.uint64), 5),      # lengths do not add up
+                           (np.array([65, 1], np.uint64), np.array([0, 3], np.uint64), 4)):     # source == own position
+            with pytest.raises(capi.Lz77SssError):
+                F.decode(src, ln, n)
 
 
 def test_change_tracking_is_invisible(capi, monkeypatch):
