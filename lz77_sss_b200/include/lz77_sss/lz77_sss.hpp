@@ -11,7 +11,12 @@
 //    (rolling_hash.hpp:30-39,127-130).  lz77_sss_b200::options().gap_bases does the same when left at 0 and can be
 //    pinned for reproducible factor streams (the parity tests do).
 //  * the input needs no zero padding; it is only read in [0, n).
-//  * implemented: factorize_approximate<greedy, lpf_opt, tau> and decode.  Other modes throw (scope: DESIGN.md).
+//  * implemented: factorize_approximate for all three factorize modes x four phrase modes, and decode (any n).
+//    factorize_exact has the reference's template list but throws: the exact path is not built (scope: DESIGN.md).
+//  * LZ77_SSS_BENCH: like the reference (lz77_sss.hpp:298-311,357-365), a translation unit that defines LZ77_SSS_BENCH
+//    and the globals text_name / result_file_path / result_file before including this header gets one
+//    `RESULT key=value ...` line per logged factorization, with the reference's keys; the phase keys carry the
+//    device pipeline's times under the reference's names (mapping at write_result below).
 #pragma once
 #include <algorithm>
 #include <array>
@@ -26,6 +31,22 @@
 #include <vector>
 
 #include <lz77sss_b200.h>
+
+#ifdef LZ77_SSS_BENCH
+#include <fstream>
+extern std::string text_name;             // defined by the bench program, like bench/lz77_sss_bench.cpp:29-31
+extern std::string result_file_path;
+extern std::ofstream result_file;
+#endif
+
+// the range structures of the exact path are template template parameters of factorize_exact (lz77_sss.hpp:188-196);
+// the names exist so that the reference's call sites compile
+template <typename sidx_t> struct decomposed_static_weighted_square_grid {};
+template <typename sidx_t> struct decomposed_static_weighted_kd_tree {};
+template <typename sidx_t> struct decomposed_semi_dynamic_square_grid {};
+template <typename sidx_t> struct static_weighted_square_grid {};
+template <typename sidx_t> struct static_weighted_kd_tree {};
+template <typename sidx_t> struct semi_dynamic_square_grid {};
 
 enum phrase_mode { lpf_naive, lpf_lnf_naive, lpf_opt, lpf_lnf_opt };      // lz77_sss.hpp:47-52
 enum factorize_mode { greedy_naive, greedy, skip_phrases };               // lz77_sss.hpp:54-58
@@ -60,7 +81,15 @@ public:
     static constexpr phrase_mode default_phr_mode = lpf_opt;
     static constexpr factorize_mode default_fact_mode = greedy;
     static constexpr transform_mode default_transf_mode = without_samples;
-    static constexpr uint64_t default_tau = 512;
+    template <typename sidx_t> using default_range_ds_t = decomposed_static_weighted_square_grid<sidx_t>;
+    static constexpr uint64_t default_tau = 512;                          // lz77_sss.hpp:82-94
+    static constexpr uint64_t max_delta = 256;
+    static constexpr uint64_t rks_sample_rate = 16;
+    static constexpr uint64_t num_patt_lens = 5;
+    static constexpr uint64_t min_rh_index_size = 1 << 20;
+    static constexpr uint64_t max_rh_index_size = 1 << 30;
+    static constexpr double min_rel_rh_index_size = 0.1;
+    static constexpr uint64_t num_par_sect_per_thr = 16;
 
     struct factor {                                                       // lz77_sss.hpp:129-174
         pos_t src;
@@ -102,14 +131,18 @@ public:
         };
         lz77_sss_b200::check(lz77sss_factorize_approximate(h.h, reinterpret_cast<const uint8_t*>(input), input_size,
                                                           +tramp, &output));
+#ifdef LZ77_SSS_BENCH
+        if (params.log) write_result(h, input_size, tau, (uint32_t)phr_mode, (uint32_t)fact_mode);
+#endif
     }
 
     template <factorize_mode fact_mode = default_fact_mode, phrase_mode phr_mode = default_phr_mode,
-              transform_mode transf_mode = default_transf_mode, uint64_t tau = default_tau, typename char_t,
+              transform_mode transf_mode = default_transf_mode,
+              template <typename> typename range_ds_t = default_range_ds_t, uint64_t tau = default_tau, typename char_t,
               typename output_fnc_t>
-    static void factorize_exact(char_t*, pos_t, output_fnc_t, parameters = {}) {
+    static void factorize_exact(char_t*, pos_t, output_fnc_t, parameters = {}) {       // lz77_sss.hpp:188-200
         static_assert(fact_mode != skip_phrases);                         // lz77_sss.hpp:319
-        throw std::runtime_error("lz77sss_b200: factorize_exact is not built yet (DESIGN.md scope table)");
+        throw std::runtime_error("lz77sss_b200: factorize_exact is not built (DESIGN.md scope table)");
     }
 
     template <std::input_iterator fact_it_t, typename out_it_t>
@@ -130,7 +163,29 @@ public:
     }
 
 private:
+    struct handle;
+#ifdef LZ77_SSS_BENCH
+    // the reference's RESULT line (lz77_sss.hpp:298-311,357-365; phase keys of SURVEY.md §5).  Phase mapping of the device
+    // pipeline: lce_t = synchronizing set + suffix order + LCP/range-minimum structures (build_lce), nsv_psv = 0 (the
+    // nearest-smaller searches run inside the candidate kernel), lpf = candidates + their copy + the coverage chain,
+    // phrase_info = 0 (inside lpf), init_gap_idx = 0 (the index is built slice by slice inside factorize), factorize =
+    // gap index + parse + callbacks; h2d = upload of the text.  Times in nanoseconds, throughput in the reference's unit.
+    static void write_result(handle& h, uint64_t n, uint64_t tau, uint32_t phr_mode, uint32_t fact_mode) {
+        if (result_file_path == "") return;
+        lz77sss_stats st;
+        lz77_sss_b200::check(lz77sss_get_stats(h.h, &st));
+        const double ratio = n / (double)st.num_factors;
+        result_file << "RESULT text_name=" << text_name << " n=" << n << " alg=lz77_sss_b200 num_threads=" << h.num_threads
+                    << " tau=" << tau << " phr_mode=" << phr_mode << " fact_mode=" << fact_mode << " transf_mode=0"
+                    << " h2d=" << st.t_h2d_ns << " lce_t=" << st.t_sss_ns + st.t_sort_ns + st.t_lce_ns << " nsv_psv=0"
+                    << " lpf=" << st.t_lpf_ns + st.t_d2h_ns + st.t_chain_ns << " phrase_info=0 init_gap_idx=0"
+                    << " factorize=" << st.t_gap_hash_ns + st.t_emit_ns << " num_factors=" << st.num_factors
+                    << " comp_ratio=" << ratio << " time=" << st.t_total_ns
+                    << " throughput=" << 1000.0 * n / (double)st.t_total_ns << " mem_peak=0" << std::endl;
+    }
+#endif
     struct handle {
+        uint32_t num_threads = 0;
         lz77sss_handle* h = nullptr;
         handle(uint64_t tau, parameters params, uint32_t phr_mode, uint32_t fact_mode) {
             auto& o = lz77_sss_b200::options();
@@ -139,6 +194,7 @@ private:
             c.tau = (uint32_t)tau;
             // num_threads == 0: the reference takes omp_get_max_threads() (lz77_sss.hpp:289-291)
             c.num_threads = params.num_threads ? params.num_threads : std::max(1u, std::thread::hardware_concurrency());
+            num_threads = c.num_threads;
             c.pos_bits = sizeof(pos_t) * 8;
             c.phr_mode = phr_mode;
             c.fact_mode = fact_mode;

@@ -13,6 +13,8 @@ std::string text_name;
 std::string result_file_path;
 std::ofstream result_file;
 #include <lz77_sss/lz77_sss.hpp>
+#include <lz77_sss/misc/huffman.hpp>
+#include <lz77_sss/misc/vbyte.hpp>
 #include <omp.h>
 #include <unistd.h>
 #include <iostream>
@@ -174,6 +176,75 @@ int64_t refdrv_rks(const uint8_t* text, uint64_t n, uint64_t s, int p, uint64_t*
     for (uint64_t k = 0; k < f.size() && k < fps_cap; k++) fps_out[k] = f[k];
     for (uint64_t k = 0; k < nq; k++) qout[k] = R.substring((uint32_t)qpos[k], (uint32_t)qlen[k]);
     return (int64_t)f.size();
+}
+
+// lz77_sss<pos_t>::factorize_exact<greedy, lpf_opt, transf_mode> (lz77_sss.hpp:188-200) with the default range structure, as
+// cli/lz77_sss_exact_smpl.cpp:46-56 and cli/lz77_sss_exact.cpp call it.  transf_mode: 0 naive, 1 with_samples,
+// 2 without_samples.  Only built for tau = 64 and 512 (compile time).
+int64_t refdrv_factorize_exact(const uint8_t* text, uint64_t n, int transf_mode, int num_threads, uint64_t* src,
+                               uint64_t* len, uint64_t cap, double* seconds) {
+#if REF_TAU == 64 || REF_TAU == 512
+    if (n == 0 || n > 0xFFFFFFFFull) return -2;
+    std::vector<char> buf(n + 4 * 4096, 0);
+    std::memcpy(buf.data(), text, n);
+    sink_t sink { src, len, cap, 0 };
+    auto out = [&](lz77_sss<uint32_t>::factor f) {
+        if (sink.z < sink.cap) { sink.src[sink.z] = f.src; sink.len[sink.z] = f.len; }
+        sink.z++;
+    };
+    parameters prm { .num_threads = (uint16_t)num_threads, .log = false };
+    using L = lz77_sss<uint32_t>;
+    auto t0 = std::chrono::steady_clock::now();
+    if (transf_mode == 0) L::template factorize_exact<greedy, lpf_opt, naive, L::template default_range_ds_t, REF_TAU>(buf.data(), (uint32_t)n, out, prm);
+    else if (transf_mode == 1) L::template factorize_exact<greedy, lpf_opt, with_samples, L::template default_range_ds_t, REF_TAU>(buf.data(), (uint32_t)n, out, prm);
+    else if (transf_mode == 2) L::template factorize_exact<greedy, lpf_opt, without_samples, L::template default_range_ds_t, REF_TAU>(buf.data(), (uint32_t)n, out, prm);
+    else return -1;
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    for (int i = 0; i < 5; i++) draw(mirror());        // the approximation inside drew the five gap-index bases
+    return (int64_t)sink.z;
+#else
+    (void)text; (void)n; (void)transf_mode; (void)num_threads; (void)src; (void)len; (void)cap; (void)seconds;
+    return -3;
+#endif
+}
+
+// The reference's own file formats (misc/huffman.hpp:321-436, misc/vbyte.hpp:64-101), used as cli/lz77_sss_3_aprx.cpp:73-84
+// and cli/lz77_sss_decode.cpp:61-66 use them.
+int refdrv_huff_write(const uint64_t* src, const uint64_t* len, uint64_t z, uint64_t n, const char* path) {
+    std::ofstream out(path, std::ios::binary);
+    if (!out.good()) return -1;
+    huff_writer writer(out, n);
+    for (uint64_t i = 0; i < z; i++) writer.add(lz77_sss<uint64_t>::factor{src[i], len[i]});
+    writer.finish();
+    return 0;
+}
+int64_t refdrv_huff_read(const char* path, uint64_t* src, uint64_t* len, uint64_t cap, uint64_t* n_out) {
+    std::ifstream in(path, std::ios::binary);
+    if (!in.good()) return -1;
+    uint64_t n = 0;
+    in.read((char*)&n, 5);
+    bit_reader reader(in);
+    huffman len_huff, dist_huff;
+    using factor = lz77_sss<uint64_t>::factor;
+    huff_factor_iterator<factor> it(reader, len_huff, dist_huff, n);
+    uint64_t z = 0;
+    for (uint64_t pos = 0; pos < n;) {
+        const factor f = *it++;
+        if (z < cap) { src[z] = f.src; len[z] = f.len; }
+        z++;
+        pos += f.length();
+    }
+    if (n_out) *n_out = n;
+    return (int64_t)z;
+}
+int refdrv_vbyte_write(const uint64_t* vals, uint64_t cnt, int bits, const char* path) {
+    std::ofstream out(path, std::ios::binary);
+    if (!out.good()) return -1;
+    for (uint64_t i = 0; i < cnt; i++) {
+        if (bits == 32) encode_vbyte<uint32_t>(out, (uint32_t)vals[i]);
+        else encode_vbyte<uint64_t>(out, vals[i]);
+    }
+    return 0;
 }
 
 // lz77_sss<>::decode (algorithms/common.cpp:33-54)

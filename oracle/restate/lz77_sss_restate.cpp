@@ -545,6 +545,55 @@ int64_t oracle_factorize_approximate(const uint8_t* text, uint64_t n, uint64_t t
 }
 
 // lz77_sss<pos_t>::decode (algorithms/common.cpp:33-54)
+// Independent exact LZ77 (row f4 of SURVEY.md §8; the role of include/lz77/kkp2.hpp:68-143 in lz77-sss-bench): suffix array by
+// prefix doubling, then for every phrase start the nearest suffixes with a smaller text position on both sides in suffix
+// order; the longer of the two common prefixes is the longest previous factor.  Literals as {byte, 0}.  For small inputs.
+int64_t oracle_lz77_exact(const uint8_t* T, uint64_t n, uint64_t* src_out, uint64_t* len_out, uint64_t cap) {
+    if (n == 0) return 0;
+    std::vector<uint32_t> sa(n), rk(n), tmp(n);
+    for (uint64_t i = 0; i < n; i++) { sa[i] = (uint32_t)i; rk[i] = T[i]; }
+    for (uint64_t h = 1;; h *= 2) {
+        auto key = [&](uint32_t i) { return std::make_pair(rk[i], i + h < n ? (int64_t)rk[i + h] : (int64_t)-1); };
+        std::sort(sa.begin(), sa.end(), [&](uint32_t a, uint32_t b) { return key(a) < key(b); });
+        tmp[sa[0]] = 0;
+        for (uint64_t r = 1; r < n; r++) tmp[sa[r]] = tmp[sa[r - 1]] + (key(sa[r - 1]) < key(sa[r]) ? 1 : 0);
+        rk.swap(tmp);
+        if (rk[sa[n - 1]] == n - 1) break;
+    }
+    // psv[i] / nsv[i]: text position of the nearest suffix in front of / behind suffix i in suffix order that starts earlier
+    const uint32_t NONE = 0xFFFFFFFFu;
+    std::vector<uint32_t> psv(n, NONE), nsv(n, NONE), st;
+    for (uint64_t r = 0; r < n; r++) {
+        while (!st.empty() && st.back() > sa[r]) st.pop_back();
+        if (!st.empty()) psv[sa[r]] = st.back();
+        st.push_back(sa[r]);
+    }
+    st.clear();
+    for (uint64_t r = n; r-- > 0;) {
+        while (!st.empty() && st.back() > sa[r]) st.pop_back();
+        if (!st.empty()) nsv[sa[r]] = st.back();
+        st.push_back(sa[r]);
+    }
+    auto lce = [&](uint64_t a, uint64_t b) {
+        uint64_t l = 0;
+        while (b + l < n && T[a + l] == T[b + l]) l++;
+        return l;
+    };
+    uint64_t z = 0;
+    for (uint64_t i = 0; i < n;) {
+        uint64_t best = 0, from = 0;
+        if (psv[i] != NONE) { best = lce(psv[i], i); from = psv[i]; }
+        if (nsv[i] != NONE) { const uint64_t l = lce(nsv[i], i); if (l > best) { best = l; from = nsv[i]; } }
+        if (z < cap) {
+            src_out[z] = best ? from : T[i];
+            len_out[z] = best;
+        }
+        z++;
+        i += best ? best : 1;
+    }
+    return (int64_t)z;
+}
+
 int oracle_decode(const uint64_t* src, const uint64_t* len, uint64_t z, uint8_t* out, uint64_t n) {
     uint64_t pos = 0, k = 0;
     while (pos < n) {

@@ -192,6 +192,12 @@ def ref(tau):
         L.refdrv_rks.restype = C.c_int64
         L.refdrv_rks.argtypes = [_u8p, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_uint64), _u32p_, C.c_uint64, _u64p, _u64p,
                                  C.c_uint64, _u32p_]
+        L.refdrv_factorize_exact.restype = C.c_int64
+        L.refdrv_factorize_exact.argtypes = [_u8p, C.c_uint64, C.c_int, C.c_int, _u64p, _u64p, C.c_uint64, C.POINTER(C.c_double)]
+        L.refdrv_huff_write.argtypes = [_u64p, _u64p, C.c_uint64, C.c_uint64, C.c_char_p]
+        L.refdrv_huff_read.restype = C.c_int64
+        L.refdrv_huff_read.argtypes = [C.c_char_p, _u64p, _u64p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.refdrv_vbyte_write.argtypes = [_u64p, C.c_uint64, C.c_int, C.c_char_p]
         assert L.refdrv_tau() == tau
         _ref[tau] = L
     return _ref[tau]
@@ -264,3 +270,51 @@ def ref_rks(text, s, qpos, qlen, p=1, tau=512):
     cnt = ref(tau).refdrv_rks(_pad1(t), t.size, s, p, C.byref(base), fps, cap, _pad1(qpos), _pad1(qlen), qpos.size, out)
     assert 0 < cnt <= cap
     return int(base.value), fps[:cnt].copy(), out[:qpos.size].copy()
+
+
+def ref_huff_write(src, ln, n, path, tau=512):
+    """The reference's huff_writer (misc/huffman.hpp:321-383) on a factor stream."""
+    src = np.ascontiguousarray(src, dtype=np.uint64)
+    ln = np.ascontiguousarray(ln, dtype=np.uint64)
+    assert ref(tau).refdrv_huff_write(_pad1(src), _pad1(ln), src.size, n, str(path).encode()) == 0
+
+
+def ref_huff_read(path, cap, tau=512):
+    """The reference's huff_factor_iterator (misc/huffman.hpp:385-436). Returns (src, len, n)."""
+    src = np.zeros(max(1, cap), dtype=np.uint64); ln = np.zeros(max(1, cap), dtype=np.uint64)
+    n = C.c_uint64(0)
+    z = ref(tau).refdrv_huff_read(str(path).encode(), src, ln, cap, C.byref(n))
+    assert 0 <= z <= cap, z
+    return src[:z].copy(), ln[:z].copy(), int(n.value)
+
+
+def ref_vbyte_write(vals, bits, path, tau=512):
+    vals = np.ascontiguousarray(vals, dtype=np.uint64)
+    assert ref(tau).refdrv_vbyte_write(_pad1(vals), vals.size, bits, str(path).encode()) == 0
+
+
+NAIVE, WITH_SAMPLES, WITHOUT_SAMPLES = 0, 1, 2      # lz77_sss.hpp:60-64
+
+
+def ref_factorize_exact(text, tau=512, p=1, transf_mode=WITH_SAMPLES):
+    """The reference's own factorize_exact<greedy, lpf_opt, transf_mode> (tau 64 or 512). Returns (src, len, seconds)."""
+    t = _text(text)
+    cap = t.size + 1
+    src = np.zeros(cap, dtype=np.uint64); ln = np.zeros(cap, dtype=np.uint64)
+    sec = C.c_double(0)
+    z = ref(tau).refdrv_factorize_exact(t, t.size, transf_mode, p, src, ln, cap, C.byref(sec))
+    assert 0 <= z <= cap, z
+    return src[:z].copy(), ln[:z].copy(), sec.value
+
+
+def lz77_exact(text):
+    """Independent exact LZ77 (suffix array + nearest earlier suffixes in suffix order, KKP-style): (src, len)."""
+    t = _text(text)
+    cap = t.size + 1
+    src = np.zeros(cap, dtype=np.uint64); ln = np.zeros(cap, dtype=np.uint64)
+    L = core()
+    L.oracle_lz77_exact.restype = C.c_int64
+    L.oracle_lz77_exact.argtypes = [_u8p, C.c_uint64, _u64p, _u64p, C.c_uint64]
+    z = L.oracle_lz77_exact(_pad1(t), t.size, src, ln, cap)
+    assert 0 <= z <= cap
+    return src[:z].copy(), ln[:z].copy()

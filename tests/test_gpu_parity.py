@@ -510,3 +510,48 @@ def test_cpp_header_example_runs(capi, tmp_path):
     env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(ROOT, "lz77_sss_b200"))
     r = subprocess.run([str(exe)], capture_output=True, text=True, env=env)
     assert r.returncode == 0 and "decode ok" in r.stdout and "rabin_karp_substring ok" in r.stdout, r.stdout + r.stderr
+
+
+def _build_tool(name, tmp_path):
+    exe = tmp_path / name
+    cmd = ["/usr/bin/g++", "-std=c++20", "-O1", "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "lz77_sss_b200", "include"),
+           os.path.join(ROOT, "tools", "cpp", name + ".cpp"), "-L" + os.path.join(ROOT, "lz77_sss_b200"), "-llz77sss_b200", "-o", str(exe)]
+    subprocess.run(cmd, check=True)
+    return str(exe)
+
+
+def test_file_level_tools_round_trip(capi, oracle, tmp_path):
+    """tools/cpp: the file-level drop-ins for lz77-sss-3-aprx / lz77-sss-decode (Huffman factor files, misc/huffman.hpp),
+    the tau-sweep harness with the reference's RESULT lines (bench/lz77_sss_bench_tau.cpp) and ssszip's gapped container
+    (skip_phrases + vbyte, cli/ssszip.cpp:120-180)."""
+    env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(ROOT, "lz77_sss_b200"))
+    text = synth.dna_collection(300_000, seed=61, chrom_len=40_000)
+    src_file = tmp_path / "text.bin"
+    text.tofile(src_file)
+    aprx, dec = _build_tool("lz77_sss_3_aprx", tmp_path), _build_tool("lz77_sss_decode", tmp_path)
+    r = subprocess.run([aprx, str(src_file), str(tmp_path / "text.lz77"), "1"], capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    r = subprocess.run([dec, str(tmp_path / "text.lz77"), str(tmp_path / "text.out")], capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert (np.fromfile(tmp_path / "text.out", dtype=np.uint8) == text).all()
+    if oracle.ref_available(512):          # the reference's own reader and decoder accept the file
+        fs, fl, n = oracle.ref_huff_read(tmp_path / "text.lz77", text.size + 1)
+        assert n == text.size and (oracle.ref_decode(fs, fl, n) == text).all()
+    elif oracle.ref_require():
+        pytest.fail("oracle/_ref missing and LZ77SSS_REQUIRE_REF=1")
+    bench = _build_tool("lz77_sss_bench_tau", tmp_path)
+    r = subprocess.run([bench, str(src_file), str(tmp_path / "results.txt"), "16", "512"], capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    lines = open(tmp_path / "results.txt").read().strip().splitlines()
+    assert len(lines) == 6                                       # tau = 16, 32, 64, 128, 256, 512
+    for line, tau in zip(lines, (16, 32, 64, 128, 256, 512)):
+        kv = dict(tok.split("=", 1) for tok in line.split()[1:])
+        assert line.startswith("RESULT ") and kv["tau"] == str(tau) and kv["n"] == str(text.size) and kv["num_threads"] == "1"
+        for key in ("lce_t", "nsv_psv", "lpf", "phrase_info", "init_gap_idx", "factorize", "num_factors", "comp_ratio", "time", "throughput"):
+            assert key in kv
+    zipper = _build_tool("ssszip_gapped", tmp_path)
+    for cmd, a, b in (("encode", src_file, tmp_path / "text.gap"), ("decode", tmp_path / "text.gap", tmp_path / "text.gap.out")):
+        r = subprocess.run([zipper, cmd, str(a), str(b)], capture_output=True, text=True, env=env)
+        assert r.returncode == 0, r.stdout + r.stderr
+    assert (np.fromfile(tmp_path / "text.gap.out", dtype=np.uint8) == text).all()
+    assert os.path.getsize(tmp_path / "text.gap") < text.size // 2
