@@ -395,6 +395,16 @@ def main():
     prof_rows = F.kernel_profile_rows()
     st_prof = F.stats()
 
+    # decode (lz77_sss<>::decode, algorithms/common.cpp:33-54) of the factors just produced: device-resident kernel time
+    # (CUDA events on the library's stream, output compared with the text in HBM) and the public call with host buffers
+    zz = int(sink.count)
+    dec_ms, dec_rounds, dec_launches, dec_ok = F.time_decode(src[:zz], ln[:zz], n, iters=5, d_expect=d_text)
+    t0 = time.perf_counter()
+    dec_host = F.decode(src[:zz], ln[:zz], n)
+    dec_e2e_ms = 1e3 * (time.perf_counter() - t0)
+    dec_ok = bool(dec_ok) and bool((dec_host == text).all())
+    del dec_host
+
     # the dominant streaming kernel (K1+K2), CUDA events on the library's own stream
     k_ms, s_size = F.time_sss_kernel(d_text, n, iters=10)
     # the other streaming kernel of the path: the prefix-fingerprint table of rabin_karp_substring<31> (row a19)
@@ -437,6 +447,13 @@ def main():
             out["other_kernels"] = [{"kernel": "rks_build_kernel (rabin_karp_substring<31> prefix fingerprints)", "bound": "hbm",
                                      "achieved": rks_gbs, "peak": peak, "unit": "GB/s", "frac": rks_gbs / peak,
                                      "algorithmic_bytes": int(rks_bytes), "kernel_ms": rks_ms}]
+        dec_bytes = 2 * n + 16 * zz
+        out["decode"] = {"metric": "output MiB/s decoded", "value": (n / MIB) / (dec_ms / 1e3), "unit": "MiB/s", "ms": dec_ms,
+                         "rounds": dec_rounds, "gpu_launches": dec_launches, "round_trip_ok": dec_ok,
+                         "e2e": {"value": (n / MIB) / (dec_e2e_ms / 1e3), "unit": "MiB/s", "ms": dec_e2e_ms,
+                                 "h2d_bytes": 16 * zz, "d2h_bytes": int(n)},
+                         "roofline": {"bound": "hbm", "algorithmic_bytes": int(dec_bytes), "achieved": dec_bytes / (dec_ms / 1e3) / 1e9,
+                                      "peak": peak, "unit": "GB/s", "frac": dec_bytes / (dec_ms / 1e3) / 1e9 / peak}}
         out.setdefault("other_kernels", [])
         for r in prof_rows:         # live CUDA-event times of one profiled step; frac only where the kernel has a byte count
             row = {"kernel": r["kernel"], "launches_per_step": r["launches"], "ms_per_step": r["ms"],

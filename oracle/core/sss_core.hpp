@@ -36,7 +36,9 @@
 #include <cstdint>
 #include <cstring>
 #include <deque>
+#include <memory>
 #include <numeric>
+#include <utility>
 #include <vector>
 #ifdef _OPENMP
 #include <omp.h>
@@ -44,6 +46,16 @@
 #endif
 
 namespace oracle {
+
+// vectors of n ids / flags are written completely by parallel loops: skip the serial zero fill of resize()
+template <typename T>
+struct no_init_alloc : std::allocator<T> {
+    template <typename U> struct rebind { using other = no_init_alloc<U>; };
+    template <typename U> void construct(U* p) noexcept { ::new (static_cast<void*>(p)) U; }
+    template <typename U, typename... A> void construct(U* p, A&&... a) { ::new (static_cast<void*>(p)) U(std::forward<A>(a)...); }
+};
+using id_vec = std::vector<uint32_t, no_init_alloc<uint32_t>>;
+using flag_vec = std::vector<uint8_t, no_init_alloc<uint8_t>>;
 
 static constexpr uint32_t ID_INF = 0xFFFFFFFFu;
 static constexpr uint32_t DEFAULT_SSS_BASE = 0x9E3779B1u;  // odd
@@ -95,10 +107,12 @@ inline uint64_t naive_lce(const uint8_t* T, uint64_t n, uint64_t i, uint64_t j) 
 // iff that segment has smallest period p <= P and the maximal p-periodic stretch around the
 // segment covers the window.  tests/test_oracle_core.py checks this against the plain definition.
 inline uint64_t mark_q(const uint8_t* T, uint64_t n, uint64_t tau, uint32_t qmax,
-                       std::vector<uint8_t>& q) {
+                       flag_vec& q) {
     uint64_t nw = n >= tau ? n - tau + 1 : 0;  // windows 0..nw-1
-    q.assign(nw, 0);
+    q.resize(nw);
     if (nw == 0) return 0;
+#pragma omp parallel for schedule(static)
+    for (int64_t j = 0; j < (int64_t)nw; j++) q[j] = 0;
     const uint32_t P = q_period_bound(tau, qmax);
     const uint64_t A = q_anchor_spacing(tau, P);
     uint64_t marked = 0;
@@ -137,13 +151,13 @@ inline uint64_t mark_q(const uint8_t* T, uint64_t n, uint64_t tau, uint32_t qmax
 
 // id(j) for j in [0, n-tau+1] (last one is the virtual terminator window).
 inline void window_ids(const uint8_t* T, uint64_t n, uint64_t tau, uint32_t base, uint32_t qmax,
-                       std::vector<uint32_t>& id, uint64_t& num_q) {
+                       id_vec& id, uint64_t& num_q) {
     id.clear();
     num_q = 0;
     if (n + 1 < tau) return;
     uint64_t nw = n - tau + 1;  // real windows (may be 0 when n == tau-1)
     id.resize(nw + 1);
-    std::vector<uint8_t> q;
+    flag_vec q;
     num_q = mark_q(T, n, tau, qmax, q);
     const uint32_t btau = pow_u32(base, tau);
     if (nw) {
@@ -177,24 +191,45 @@ inline sss_result build_sss(const uint8_t* T, uint64_t n, uint64_t tau,
                             uint32_t base = DEFAULT_SSS_BASE, uint32_t qmax = DEFAULT_QMAX) {
     sss_result r;
     if (n + 1 < 2 * tau) return r;
-    std::vector<uint32_t> id;
+    id_vec id;
     window_ids(T, n, tau, base, qmax, id, r.num_q);
     r.has_runs = r.num_q > 0;
     uint64_t cnt = n - 2 * tau + 2;  // candidate positions 0..n-2tau+1
-    // sliding minimum over [i, i+tau] with a monotone deque
-    std::deque<uint64_t> dq;
-    for (uint64_t j = 0; j < tau; j++) {
-        while (!dq.empty() && id[dq.back()] >= id[j]) dq.pop_back();
-        dq.push_back(j);
+    // sliding minimum over [i, i+tau] with a monotone queue (a ring of tau + 2 window indices); the candidates are cut into
+    // one chunk per thread, each chunk warms its queue up on the tau ids in front of its first window end
+    int nthr = 1;
+#ifdef _OPENMP
+    nthr = omp_get_max_threads();
+#endif
+    if (cnt < (uint64_t)nthr * 4 * tau) nthr = 1;
+    std::vector<std::vector<uint64_t>> part(nthr);
+    const uint64_t chunk = (cnt + nthr - 1) / nthr;
+#pragma omp parallel for schedule(static, 1) num_threads(nthr)
+    for (int t = 0; t < nthr; t++) {
+        const uint64_t cb = (uint64_t)t * chunk, ce = std::min(cnt, cb + chunk);
+        if (cb >= ce) continue;
+        const uint64_t cap = tau + 2;
+        std::vector<uint64_t> ring(cap);
+        uint64_t head = 0, tail = 0;          // queue = ring[head % cap .. tail % cap)
+        auto push = [&](uint64_t j) {
+            while (tail > head && id[ring[(tail - 1) % cap]] >= id[j]) tail--;
+            ring[tail % cap] = j;
+            tail++;
+        };
+        for (uint64_t j = cb; j < cb + tau; j++) push(j);
+        auto& out = part[t];
+        out.reserve(2 * (ce - cb) / tau + 16);
+        for (uint64_t i = cb; i < ce; i++) {
+            push(i + tau);
+            while (ring[head % cap] < i) head++;
+            const uint32_t m = id[ring[head % cap]];
+            if (m != ID_INF && (id[i] == m || id[i + tau] == m)) out.push_back(i);
+        }
     }
-    for (uint64_t i = 0; i < cnt; i++) {
-        uint64_t j = i + tau;
-        while (!dq.empty() && id[dq.back()] >= id[j]) dq.pop_back();
-        dq.push_back(j);
-        while (dq.front() < i) dq.pop_front();
-        uint32_t m = id[dq.front()];
-        if (m != ID_INF && (id[i] == m || id[i + tau] == m)) r.S.push_back(i);
-    }
+    size_t total = 0;
+    for (auto& v : part) total += v.size();
+    r.S.reserve(total);
+    for (auto& v : part) r.S.insert(r.S.end(), v.begin(), v.end());
     return r;
 }
 

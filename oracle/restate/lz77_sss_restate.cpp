@@ -464,14 +464,14 @@ void oracle_q_bruteforce(const uint8_t* T, uint64_t n, uint64_t tau, uint32_t qm
 
 void oracle_q_anchored(const uint8_t* text, uint64_t n, uint64_t tau, uint32_t qmax, uint8_t* q_out) {
     auto buf = padded(text, n);
-    std::vector<uint8_t> q;
+    oracle::flag_vec q;
     oracle::mark_q(buf.data(), n, tau, qmax, q);
     std::copy(q.begin(), q.end(), q_out);
 }
 
 void oracle_window_ids(const uint8_t* text, uint64_t n, uint64_t tau, uint32_t base, uint32_t qmax, uint32_t* id_out) {
     auto buf = padded(text, n);
-    std::vector<uint32_t> id;
+    oracle::id_vec id;
     uint64_t nq;
     oracle::window_ids(buf.data(), n, tau, base, qmax, id, nq);
     std::copy(id.begin(), id.end(), id_out);
