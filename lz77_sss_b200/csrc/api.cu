@@ -11,6 +11,10 @@
 // The host never computes a fingerprint, never sorts and never builds an index: it consumes device results.
 #include <algorithm>
 #include <array>
+#include <atomic>
+#include <exception>
+#include <mutex>
+#include <thread>
 #include <chrono>
 #include <cmath>
 #include <cstring>
@@ -25,7 +29,7 @@
 #include "stages.cuh"
 
 namespace lz77sss {
-unsigned long long g_kernel_launches = 0;
+thread_local unsigned long long g_kernel_launches = 0;
 bool g_sync_every_kernel = getenv("LZ77SSS_SYNC_KERNELS") != nullptr;
 bool g_prof_on = false;
 namespace {
@@ -59,6 +63,17 @@ namespace {
 
 thread_local std::string g_last_error;
 
+// cfg.pos_bits == 0 means "choose per input" (cli/lz77_sss_3_aprx.cpp:73); the choice must not outlive the call, also
+// when the call throws
+struct pos_bits_guard {
+    lz77sss_config& cfg;
+    const uint32_t saved;
+    pos_bits_guard(lz77sss_config& c, uint64_t n) : cfg(c), saved(c.pos_bits) {
+        if (cfg.pos_bits == 0) cfg.pos_bits = n <= 0xFFFFFFFFull ? 32 : 64;
+    }
+    ~pos_bits_guard() { cfg.pos_bits = saved; }
+};
+
 struct lpf_t { uint64_t beg, end, src; };
 
 using clk = std::chrono::steady_clock;
@@ -76,6 +91,7 @@ struct hbuf {
         if (n <= cap) return;
         if (p) cudaFreeHost(p);
         p = nullptr;
+        cap = 0;                    // (a failed allocation below must not leave a capacity without a buffer)
         size_t want = n + n / 8 + 64;
         CUDA_CHECK(cudaMallocHost(&p, want * sizeof(T)));
         cap = want;
@@ -131,8 +147,8 @@ struct lz77sss_handle {
     // sharded run (lz77sss_shard_*): what lz77sss_shard_prepare leaves for the range parses
     bool prepare_only = false, prepared = false;
     const uint8_t* host_text = nullptr;
-    std::vector<lpf_t> ML;
-    std::vector<uint64_t> ml_planes;
+    hbuf<uint64_t> ml_buf;            // merged phrase list incl. the sentinel: three planes (beg, end, src) of ml_count entries
+    size_t ml_count = 0;
     uint64_t table_entries = 0;
 };
 
@@ -179,6 +195,32 @@ pipeline<pos_t>& pipe(lz77sss_handle* h);
 template <> pipeline<uint32_t>& pipe<uint32_t>(lz77sss_handle* h) { return h->p32; }
 template <> pipeline<uint64_t>& pipe<uint64_t>(lz77sss_handle* h) { return h->p64; }
 
+// runs f(0) .. f(p-1) on up to hardware_concurrency host threads; the first exception is rethrown
+template <typename F>
+void run_blocks(uint32_t p, F f) {
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned nt = std::min<unsigned>(p, hw);
+    if (nt <= 1) {
+        for (uint32_t i = 0; i < p; i++) f(i);
+        return;
+    }
+    std::atomic<uint32_t> next{0};
+    std::exception_ptr err;
+    std::mutex mu;
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nt; t++)
+        th.emplace_back([&]() {
+            try {
+                for (uint32_t i = next++; i < p; i = next++) f(i);
+            } catch (...) {
+                std::lock_guard<std::mutex> g(mu);
+                if (!err) err = std::current_exception();
+            }
+        });
+    for (auto& t : th) t.join();
+    if (err) std::rethrow_exception(err);
+}
+
 // ---- host side of build_LPF_opt: the coverage chain (lpf_opt.cpp:46-145) over the device-computed candidates ----
 template <typename pos_t>
 void lpf_chain(lz77sss_handle* h, pipeline<pos_t>& P) {
@@ -188,7 +230,9 @@ void lpf_chain(lz77sss_handle* h, pipeline<pos_t>& P) {
     h->LPF.resize(p);
     for (auto& v : h->LPF) v.clear();          // keeps the capacity of the last run
     const pos_t* S = P.hS.p;
-    for (uint32_t i_p = 0; i_p < p; i_p++) {
+    // the logical blocks are independent (that is how the reference's threads run them, lpf_opt.cpp:46-56): one host
+    // thread per block, at most the hardware's
+    auto run_block = [&](uint32_t i_p) {
         const uint64_t b = (uint64_t)i_p * (n / p);
         const uint64_t e = i_p == p - 1 ? n : (uint64_t)(i_p + 1) * (n / p);
         const uint64_t i_min = std::lower_bound(S, S + s, (pos_t)b) - S;
@@ -235,7 +279,8 @@ void lpf_chain(lz77sss_handle* h, pipeline<pos_t>& P) {
                 if (phr.end - phr.beg > 1) out.push_back(phr);     // pushed only inside the NSV branch (lpf_opt.cpp:141-143)
             }
         }
-    }
+    };
+    run_blocks(p, run_block);
 }
 
 // host side of build_LPF_naive (lpf_naive.cpp:33-122): the longer of the two candidates without left extension,
@@ -596,47 +641,68 @@ inline uint64_t host_lce(const uint8_t* T, uint64_t n, uint64_t src, uint64_t po
     return k;
 }
 
+// The merged phrase list as three planes (the layout the device kernels read); element access for the host loops.
+struct phrase_list {
+    const uint64_t* p = nullptr;
+    size_t m = 0;
+    size_t size() const { return m; }
+    lpf_t operator[](size_t k) const { return lpf_t{p[k], p[m + k], p[2 * m + k]}; }
+};
+
 // next_lpf (approximate/factorize/common.cpp:74-104) takes no argument, so the sequence of phrases it returns is
-// fixed before the emission starts: the per-block lists concatenated, where the first survivor of a block is
-// trimmed against the last phrase of the previous one, and the sentinel {n, n+1, 0} (lz77_sss.hpp:418,423) at the end.
-std::vector<lpf_t> merged_phrase_list(lz77sss_handle* h) {
+// fixed before the emission starts: the per-block lists concatenated, where a block continues behind the last phrase of
+// the one before it (phrases that end at or before it are dropped, the first survivor is trimmed to start there), and
+// the sentinel {n, n+1, 0} (lz77_sss.hpp:418,423) at the end.  Written as planes into the handle's pinned buffer (reused
+// between calls: a fresh 100 MB allocation per call costs more in page faults than the whole device pipeline).
+phrase_list merged_phrase_list(lz77sss_handle* h) {
     const uint64_t n = h->n;
     const uint32_t p = h->cfg.num_threads;
-    std::vector<std::vector<lpf_t>> LPF = h->LPF;    // trimmed copies; the introspection view stays as built
-    LPF[p - 1].push_back(lpf_t{n, n + 1, 0});
-    std::vector<lpf_t> ML;
-    uint32_t i_p = 0;
-    size_t li = 0;
-    while (LPF[i_p].empty()) i_p++;
-    while (true) {
-        lpf_t phr = LPF[i_p][li++];
-        ML.push_back(phr);
-        if (phr.beg == n) break;
-        if (li == LPF[i_p].size()) {
-            if (i_p < p - 1 && p > 1) {
-                do {
-                    i_p++;
-                    li = 0;
-                    auto& V = LPF[i_p];
-                    while (li < V.size() && V[li].end <= phr.end) li++;
-                    if (li < V.size() && V[li].beg < phr.end) {
-                        const uint64_t offs = phr.end - V[li].beg;
-                        V[li].beg += offs;
-                        V[li].src += offs;
-                    }
-                } while (li == LPF[i_p].size() && i_p < p - 1);
-            } else {
-                li--;
-            }
+    const auto& LPF = h->LPF;
+    struct part { size_t first, out; uint64_t cut; };      // first phrase taken, its slot in the output, where it must start
+    std::vector<part> parts(p);
+    size_t m = 0;
+    uint64_t last_end = 0;
+    bool any = false;
+    for (uint32_t i_p = 0; i_p < p; i_p++) {
+        const auto& V = LPF[i_p];
+        size_t li = 0;
+        if (any) while (li < V.size() && V[li].end <= last_end) li++;
+        parts[i_p] = part{li, m, any ? last_end : 0};
+        if (li < V.size()) {
+            m += V.size() - li;
+            last_end = V.back().end;                        // ends ascend inside a block's list
+            any = true;
         }
     }
-    return ML;
+    m += 1;                                                 // the sentinel
+    h->ml_buf.reserve(3 * m);
+    uint64_t* B = h->ml_buf.p;
+    run_blocks(p, [&](uint32_t i_p) {
+        const auto& V = LPF[i_p];
+        size_t o = parts[i_p].out;
+        for (size_t li = parts[i_p].first; li < V.size(); li++, o++) {
+            lpf_t ph = V[li];
+            if (li == parts[i_p].first && ph.beg < parts[i_p].cut) {
+                const uint64_t offs = parts[i_p].cut - ph.beg;
+                ph.beg += offs;
+                ph.src += offs;
+            }
+            B[o] = ph.beg;
+            B[m + o] = ph.end;
+            B[2 * m + o] = ph.src;
+        }
+    });
+    B[m - 1] = n;
+    B[2 * m - 1] = n + 1;
+    B[3 * m - 1] = 0;
+    h->ml_count = m;
+    return phrase_list{B, m};
 }
 
 // factorize (approximate/factorize/common.cpp:66-111) + factorize_greedy (greedy.cpp:34-140) from the state
 // (i, idx.cur_pos, k): ML[k] is the first phrase that ends behind i.
 template <typename table_t>
-uint64_t greedy_emit_from(const uint8_t* T, uint64_t n, const std::vector<lpf_t>& ML, const gap_params& g,
+uint64_t greedy_emit_from(const uint8_t* T, uint64_t n, const phrase_list& ML, const gap_params& g,
                           gap_index<table_t>& idx, uint64_t i, size_t k, lz77sss_emit_fn emit, void* ctx) {
     uint64_t num_fact = 0;
     const size_t last = ML.size() - 1;
@@ -709,7 +775,7 @@ uint64_t greedy_emit_from(const uint8_t* T, uint64_t n, const std::vector<lpf_t>
 // factorize_greedy_naive (greedy_naive.cpp:34-113) from the state (i, idx.cur_pos, k): ML[k] is the next phrase
 // (ML[k].beg >= i).  Every position is inserted before the table is probed behind it.
 template <typename table_t>
-uint64_t greedy_naive_emit_from(const uint8_t* T, uint64_t n, const std::vector<lpf_t>& ML, gap_index<table_t>& idx,
+uint64_t greedy_naive_emit_from(const uint8_t* T, uint64_t n, const phrase_list& ML, gap_index<table_t>& idx,
                                 uint64_t i, size_t k, lz77sss_emit_fn emit, void* ctx) {
     uint64_t num_fact = 0;
     const size_t last = ML.size() - 1;
@@ -763,7 +829,7 @@ uint64_t greedy_naive_emit_from(const uint8_t* T, uint64_t n, const std::vector<
 }
 
 // factorize_skip_gaps (skip_gaps.cpp:34-61): the phrases and the lengths of the gaps between them
-uint64_t skip_gaps_emit(uint64_t n, const std::vector<lpf_t>& ML, lz77sss_emit_fn emit, void* ctx) {
+uint64_t skip_gaps_emit(uint64_t n, const phrase_list& ML, lz77sss_emit_fn emit, void* ctx) {
     uint64_t num = 0;
     size_t k = 0;
     const size_t last = ML.size() - 1;
@@ -786,7 +852,7 @@ uint64_t skip_gaps_emit(uint64_t n, const std::vector<lpf_t>& ML, lz77sss_emit_f
 
 // The last 65 positions (end-of-text rules of the gap index, rolling_hash_index_107.hpp:93,112,123,145) on the host,
 // from the state the device parse handed over, with the table entries of every bucket they can touch.
-uint64_t emit_tail(lz77sss_handle* h, const uint8_t* host_text, uint64_t n, const std::vector<lpf_t>& ML, const gap_params& g,
+uint64_t emit_tail(lz77sss_handle* h, const uint8_t* host_text, uint64_t n, const phrase_list& ML, const gap_params& g,
                    bucket_provider& bp, const uint64_t ho[4], bool naive, lz77sss_emit_fn emit, void* ctx) {
     auto& st = h->stats;
     cudaStream_t s = h->st;
@@ -940,9 +1006,8 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     h->have_result = true;
     if (g.patt_lens[0] == 0) return fail(LZ77SSS_E_UNSUPPORTED, "degenerate phrase statistics (no LPF phrase or no gap): pattern lengths undefined in the reference (SURVEY.md A7)");
 
-    const std::vector<lpf_t> ML = merged_phrase_list(h);
+    const phrase_list ML = merged_phrase_list(h);
     if (h->prepare_only) {                     // lz77sss_shard_prepare: the ranges are parsed by lz77sss_shard_parse
-        h->ML = ML;
         h->table_entries = g.table_entries;
         h->host_text = host_text;
         h->prepared = true;
@@ -994,17 +1059,11 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     // greedy emission on the device up to n_cut; the last 65 positions (end-of-text rules of the gap index) on the host
     t0 = clk::now();
     const uint64_t n_cut = n > 65 ? n - 65 : 0;
-    std::vector<uint64_t> h_ml(3 * ML.size());
-    for (size_t q = 0; q < ML.size(); q++) {
-        h_ml[q] = ML[q].beg;
-        h_ml[ML.size() + q] = ML[q].end;
-        h_ml[2 * ML.size() + q] = ML[q].src;
-    }
     h->f_src.clear();
     h->f_len.clear();
     uint64_t ho[4];
     gap_hash_params gpar = bp.gp;
-    gap_parse_run<pos_t>(d_text, n, tau, P.S.get(), size_s, P.suf, P.lce, gpar, g.table_entries, h_ml.data(), ML.size(), n_cut,
+    gap_parse_run<pos_t>(d_text, n, tau, P.S.get(), size_s, P.suf, P.lce, gpar, g.table_entries, ML.p, ML.size(), n_cut,
                          h->slice_len, h->block_len, h->gp, s, h->f_src, h->f_len, ho, naive);
     st.h2d_bytes += 24 * ML.size();
     st.d2h_bytes += 16 * h->f_src.size();
@@ -1072,15 +1131,7 @@ int shard_parse_impl(lz77sss_handle* h, uint64_t beg, uint64_t end, const uint64
     gap_hash_params gpar;
     for (int x = 0; x < 5; x++) { gpar.patt_len[x] = g.patt_lens[x]; gpar.base[x] = h->cfg.gap_bases[x]; }
     gpar.mask = g.table_entries - 1;
-    const size_t m = h->ML.size();
-    if (h->ml_planes.size() != 3 * m) {
-        h->ml_planes.resize(3 * m);
-        for (size_t q = 0; q < m; q++) {
-            h->ml_planes[q] = h->ML[q].beg;
-            h->ml_planes[m + q] = h->ML[q].end;
-            h->ml_planes[2 * m + q] = h->ML[q].src;
-        }
-    }
+    const size_t m = h->ml_count;
     h->f_src.clear();
     h->f_len.clear();
     gap_parse_range R;
@@ -1093,7 +1144,7 @@ int shard_parse_impl(lz77sss_handle* h, uint64_t beg, uint64_t end, const uint64
     uint64_t ho[4];
     const uint64_t n_cut = n > 65 ? n - 65 : 0;
     auto t0 = clk::now();
-    gap_parse_run<pos_t>(h->d_text, n, h->cfg.tau, P.S.get(), P.s, P.suf, P.lce, gpar, g.table_entries, h->ml_planes.data(), m,
+    gap_parse_run<pos_t>(h->d_text, n, h->cfg.tau, P.S.get(), P.s, P.suf, P.lce, gpar, g.table_entries, h->ml_buf.p, m,
                          n_cut, h->slice_len, h->block_len, h->gp, h->st, h->f_src, h->f_len, ho,
                          h->cfg.fact_mode == LZ77SSS_FACT_GREEDY_NAIVE, &R);
     h->stats.t_gap_hash_ns += ns_since(t0);
@@ -1189,8 +1240,7 @@ int lz77sss_factorize_approximate(lz77sss_handle* h, const uint8_t* text, uint64
     if (n == 0) return fail(LZ77SSS_E_ARG, "empty input");
     return guarded([&]() {
         CUDA_CHECK(cudaSetDevice(h->cfg.device));
-        lz77sss_config saved = h->cfg;
-        if (h->cfg.pos_bits == 0) h->cfg.pos_bits = n <= 0xFFFFFFFFull ? 32 : 64;
+        pos_bits_guard guard(h->cfg, n);
         auto t0 = clk::now();
         uint8_t* d = alloc_text(h->text_buf, n, h->st);
         CUDA_CHECK(cudaMemcpyAsync(d, text, n, cudaMemcpyHostToDevice, h->st));
@@ -1200,7 +1250,6 @@ int lz77sss_factorize_approximate(lz77sss_handle* h, const uint8_t* text, uint64
         h->stats.t_h2d_ns = t_h2d;
         h->stats.h2d_bytes += n;
         h->stats.t_total_ns += t_h2d;
-        h->cfg.pos_bits = saved.pos_bits == 0 ? 0 : h->cfg.pos_bits;
         return rc;
     });
 }
@@ -1245,11 +1294,8 @@ int lz77sss_factorize_approximate_device(lz77sss_handle* h, const uint8_t* d_tex
     if (!h || !d_text) return fail(LZ77SSS_E_ARG, "null argument");
     return guarded([&]() {
         CUDA_CHECK(cudaSetDevice(h->cfg.device));
-        lz77sss_config saved = h->cfg;
-        if (h->cfg.pos_bits == 0) h->cfg.pos_bits = n <= 0xFFFFFFFFull ? 32 : 64;
-        int rc = factorize_dispatch(h, d_text, host_text, n, emit, ctx);
-        h->cfg.pos_bits = saved.pos_bits == 0 ? 0 : h->cfg.pos_bits;
-        return rc;
+        pos_bits_guard guard(h->cfg, n);
+        return factorize_dispatch(h, d_text, host_text, n, emit, ctx);
     });
 }
 
@@ -1262,16 +1308,13 @@ int lz77sss_shard_prepare(lz77sss_handle* h, const uint8_t* d_text, const uint8_
     if (h->cfg.fact_mode == LZ77SSS_FACT_SKIP_PHRASES) return fail(LZ77SSS_E_UNSUPPORTED, "skip_phrases has no gap index to shard");
     return guarded([&]() {
         CUDA_CHECK(cudaSetDevice(h->cfg.device));
-        lz77sss_config saved = h->cfg;
-        if (h->cfg.pos_bits == 0) h->cfg.pos_bits = n <= 0xFFFFFFFFull ? 32 : 64;
+        pos_bits_guard guard(h->cfg, n);
         h->prepared = false;
         h->prepare_only = true;
         for (auto& K : h->gp.keep) K->sorted = K->parsed = false;     // the buffers stay, their contents are stale
-        h->ml_planes.clear();
         auto nop = +[](void*, uint64_t, uint64_t) {};
         int rc = factorize_dispatch(h, d_text, host_text, n, nop, nullptr);
         h->prepare_only = false;
-        h->cfg.pos_bits = saved.pos_bits == 0 ? 0 : h->cfg.pos_bits;
         h->stats.t_gap_hash_ns = 0;
         return rc;
     });
@@ -1288,7 +1331,7 @@ int lz77sss_shard_entry_guess(lz77sss_handle* h, uint64_t pos, uint64_t state[4]
     NEED_PREPARED();
     if (!state || pos >= h->n) return fail(LZ77SSS_E_ARG, "bad argument");
     // the speculation the blocks of a slice start from (gap_parse.cu, spec_entry_kernel)
-    const auto& ML = h->ML;
+    const phrase_list ML{h->ml_buf.p, h->ml_count};
     size_t lo = 0, hi = ML.size() - 1;              // first phrase with end > pos (the sentinel ends at n + 1)
     while (lo < hi) {
         const size_t mid = (lo + hi) / 2;
@@ -1356,7 +1399,7 @@ int lz77sss_shard_finish(lz77sss_handle* h, const uint64_t state[4], lz77sss_emi
         bp.h = h;
         for (int x = 0; x < 5; x++) { bp.gp.patt_len[x] = g.patt_lens[x]; bp.gp.base[x] = h->cfg.gap_bases[x]; }
         bp.gp.mask = g.table_entries - 1;
-        h->stats.num_factors += emit_tail(h, h->host_text, h->n, h->ML, g, bp, state,
+        h->stats.num_factors += emit_tail(h, h->host_text, h->n, phrase_list{h->ml_buf.p, h->ml_count}, g, bp, state,
                                           h->cfg.fact_mode == LZ77SSS_FACT_GREEDY_NAIVE, emit, ctx);
         return LZ77SSS_OK;
     });

@@ -24,7 +24,7 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 }
 #define CUDA_CHECK(x) ::lz77sss::cuda_check((x), #x, __FILE__, __LINE__)
 // every kernel launch of the library goes through KERNEL_CHECK, which also counts it (bench.py's gpu_launches)
-extern unsigned long long g_kernel_launches;
+extern thread_local unsigned long long g_kernel_launches;   // per host thread: handles driven from different threads count separately
 extern bool g_sync_every_kernel;   // LZ77SSS_SYNC_KERNELS=1: device-synchronize after every launch, so a fault names its kernel
 #define KERNEL_CHECK()                                                                    \
     do {                                                                                  \

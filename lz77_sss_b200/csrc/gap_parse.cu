@@ -250,6 +250,8 @@ struct parse_ctx {
     const uint32_t* skip;      // sparse slice: bit = 1: the position has no entries (nullptr: every position has)
     const uint64_t* rk;        // sparse slice: entries added after the sort (repair list), (bucket << 32 | entry id) ascending
     uint32_t R;                // number of entries in the repair list
+    const uint64_t* rk2;       // second, small repair list: what later rounds add (re-sorted alone; merged when it grows)
+    uint32_t R2;
     uint32_t* req;             // sparse slice: req[0] = number of repair requests of this round, then (beg, end) pairs
     uint32_t req_cap;          //   (slice-relative positions that a parse needs entries for)
     uint8_t* ovr;              // per block: its parse needed entries that a sparse slice does not have (yet)
@@ -334,17 +336,20 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
             if (q == rel) { occ = i; found = true; break; }       // an earlier pattern of this position wrote the bucket
             if (!not_inserted(C.notins, q)) { occ = C.a0 + q; found = true; break; }
         }
-        if (C.R) {
+        for (int which = 0; which < 2; which++) {
+            const uint64_t* __restrict__ rk = which ? C.rk2 : C.rk;
+            const uint32_t R = which ? C.R2 : C.R;
+            if (!R) continue;
             const uint64_t key = ((uint64_t)b << 32) | e;
-            uint32_t rl = 0, rh = C.R;
+            uint32_t rl = 0, rh = R;
             while (rl < rh) {
                 const uint32_t mid = (rl + rh) >> 1;
-                if (C.rk[mid] < key) rl = mid + 1;
+                if (rk[mid] < key) rl = mid + 1;
                 else rh = mid;
             }
             while (rl > 0) {
                 rl--;
-                const uint64_t v = C.rk[rl];
+                const uint64_t v = rk[rl];
                 if ((uint32_t)(v >> 32) != b) break;
                 const uint32_t q = (uint32_t)v / 5u;
                 uint64_t o2 = NONE64;
@@ -613,19 +618,22 @@ __global__ void __launch_bounds__(256) dirty_from_bitmap_kernel(const parse_ctx 
                 if (oi && ni) break;
             }
         }
-        if (C.R) {                                   // the same walk over the repair list
+        for (int which = 0; which < 2; which++) {        // the same walk over the repair lists
+            const uint64_t* __restrict__ rk = which ? C.rk2 : C.rk;
+            const uint32_t R = which ? C.R2 : C.R;
+            if (!R) continue;
             for (uint32_t pat = 0; pat < 5; pat++) {
                 const uint32_t e = 5u * (uint32_t)rel + pat;
                 const uint32_t b = C.tkey[e];
                 const uint64_t key = ((uint64_t)b << 32) | e;
-                uint32_t rl = 0, rh = C.R;
+                uint32_t rl = 0, rh = R;
                 while (rl < rh) {
                     const uint32_t mid = (rl + rh) >> 1;
-                    if (C.rk[mid] <= key) rl = mid + 1;
+                    if (rk[mid] <= key) rl = mid + 1;
                     else rh = mid;
                 }
-                for (; rl < C.R; rl++) {
-                    const uint64_t v = C.rk[rl];
+                for (; rl < R; rl++) {
+                    const uint64_t v = rk[rl];
                     if ((uint32_t)(v >> 32) != b) break;
                     const uint32_t q = (uint32_t)v / 5u;
                     const bool oi = !not_inserted(old_bm, q), ni = !not_inserted(new_bm, q);
@@ -770,10 +778,11 @@ __global__ void dirty_from_block_kernel(uint8_t* __restrict__ dirty, uint32_t fb
 }
 
 // the repair list's share of the carried table
-__global__ void carry_repair_kernel(const parse_ctx C, uint32_t nbuckets, unsigned long long* __restrict__ Hc) {
+__global__ void carry_repair_kernel(const parse_ctx C, const uint64_t* __restrict__ rk, uint32_t R, uint32_t nbuckets,
+                                    unsigned long long* __restrict__ Hc) {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= C.R) return;
-    const uint64_t v = C.rk[k];
+    if (k >= R) return;
+    const uint64_t v = rk[k];
     const uint32_t b = (uint32_t)(v >> 32);
     if (b >= nbuckets) return;
     const uint32_t q = (uint32_t)v / 5u;
@@ -1077,17 +1086,19 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         C.Hc = reinterpret_cast<const uint64_t*>(sc.Hc.get());
         C.notins = sc.notins;
         C.skip = sparse ? sc.skip.get() : nullptr;
-        C.rk = nullptr; C.R = 0; C.req = nullptr; C.req_cap = 0;
-        uint32_t rcap = 0;
-        uint64_t *rk_cur = nullptr, *rk_alt = nullptr;
+        C.rk = nullptr; C.R = 0; C.rk2 = nullptr; C.R2 = 0; C.req = nullptr; C.req_cap = 0;
+        uint32_t rcap = 0, rcap2 = 0;
+        uint64_t *rk_cur = nullptr, *rk_alt = nullptr, *rk2_cur = nullptr, *rk2_alt = nullptr;
         uint32_t *rv_cur = nullptr, *rv_alt = nullptr;
         if (sparse) {
             C.req_cap = std::max<uint32_t>(1u << 16, 4 * nb);
             sc.req.reserve(2 + 2 * (uint64_t)C.req_cap);
             C.req = sc.req;
             rcap = (uint32_t)std::min<uint64_t>(1ull << 30, std::max<uint64_t>(1ull << 20, E / 2));
+            rcap2 = std::max<uint32_t>(1u << 20, rcap / 2);
             sc.rk0.reserve(rcap + 8); sc.rk1.reserve(rcap + 8); sc.rv0.reserve(rcap + 8); sc.rv1.reserve(rcap + 8);
-            rk_cur = sc.rk0; rk_alt = sc.rk1; rv_cur = sc.rv0; rv_alt = sc.rv1;
+            sc.rkb0.reserve(rcap2 + 8); sc.rkb1.reserve(rcap2 + 8);
+            rk_cur = sc.rk0; rk_alt = sc.rk1; rv_cur = sc.rv0; rv_alt = sc.rv1; rk2_cur = sc.rkb0; rk2_alt = sc.rkb1;
             CUDA_CHECK(cudaMemsetAsync(sc.req.get(), 0, 8, st));
         }
         bool give_up_sparse = false;
@@ -1111,22 +1122,46 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             CUDA_CHECK(cudaStreamSynchronize(st));
             if (!nreq) return false;
             if (nreq > C.req_cap) { give_up_sparse = true; return false; }
+            // the first batch of a slice (what round 0 found: most of it) becomes the big list; later batches go to the
+            // small list, which is sorted alone and folded into the big one when it outgrows its buffer
+            const bool to_big = C.R == 0;
+            const uint32_t before = to_big ? 0u : C.R2;
+            const uint32_t cap_here = to_big ? rcap : rcap2;
             CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 5, 0xFF, 4, st));
-            CUDA_CHECK(cudaMemcpyAsync(sc.changed.get() + 6, &C.R, 4, cudaMemcpyHostToDevice, st));
+            CUDA_CHECK(cudaMemcpyAsync(sc.changed.get() + 6, &before, 4, cudaMemcpyHostToDevice, st));
             repair_entries_kernel<<<ceil_div_u((uint64_t)nreq * 32, 128), 128, 0, st>>>(d_text, n, hp, a0, sc.req, nreq, sc.skip, sc.tkey,
-                                                                                      rk_cur, sc.changed.get() + 6, rcap, sc.changed.get() + 5);
+                                                                                      to_big ? rk_cur : rk2_cur, sc.changed.get() + 6,
+                                                                                      cap_here, sc.changed.get() + 5);
             KERNEL_CHECK();
             uint32_t r2[2];
             CUDA_CHECK(cudaMemcpyAsync(r2, sc.changed.get() + 5, 8, cudaMemcpyDeviceToHost, st));
             CUDA_CHECK(cudaMemsetAsync(sc.req.get(), 0, 4, st));
             CUDA_CHECK(cudaStreamSynchronize(st));
-            if (r2[1] > rcap) { give_up_sparse = true; return false; }
-            if (r2[1] == C.R) return false;
-            const uint32_t r_before = C.R;
-            C.R = r2[1];
-            radix_sort_pairs(rk_cur, rk_alt, rv_cur, rv_alt, C.R, 0, 32 + key_bits, sc.sort, st);
-            C.rk = rk_cur;
-            repair_total += C.R - r_before;
+            if (r2[1] == before) return false;
+            repair_total += r2[1] - before;
+            if (to_big) {
+                if (r2[1] > rcap) { give_up_sparse = true; return false; }
+                C.R = r2[1];
+                radix_sort_pairs(rk_cur, rk_alt, rv_cur, rv_alt, C.R, 0, 32 + key_bits, sc.sort, st);
+                C.rk = rk_cur;
+            } else if (r2[1] <= rcap2) {
+                C.R2 = r2[1];
+                radix_sort_pairs(rk2_cur, rk2_alt, rv_cur, rv_alt, C.R2, 0, 32 + key_bits, sc.sort, st);   // (payload unused)
+                C.rk2 = rk2_cur;
+            } else {
+                // the small list overflowed: some positions lost their skip bit without getting entries, so the slice is
+                // redone with every position
+                give_up_sparse = true;
+                return false;
+            }
+            if (C.R2 > rcap2 / 2 && (uint64_t)C.R + C.R2 <= rcap) {       // fold the small list into the big one
+                CUDA_CHECK(cudaMemcpyAsync(rk_cur + C.R, rk2_cur, (size_t)C.R2 * 8, cudaMemcpyDeviceToDevice, st));
+                C.R += C.R2;
+                C.R2 = 0;
+                C.rk2 = nullptr;
+                radix_sort_pairs(rk_cur, rk_alt, rv_cur, rv_alt, C.R, 0, 32 + key_bits, sc.sort, st);
+                C.rk = rk_cur;
+            }
             const uint32_t fb = r2[0] / BL;
             if (fb < pending_fb) pending_fb = fb;
             return true;
@@ -1220,6 +1255,11 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
                 KERNEL_CHECK();
                 PROF_END(st, "parse_kernel (block-speculative greedy parse, latency-bound)", 0);
+                if (g_prof_on && dbg_rounds) {       // per-round view: the same launch once more under its round number
+                    char nm[64];
+                    snprintf(nm, sizeof nm, "parse round %02llu%s", (unsigned long long)round, track ? " (tracking)" : "");
+                    prof_end(st, nm, 0);
+                }
                 sc.rounds++;
                 uint32_t chg = 0;
                 CUDA_CHECK(cudaMemcpyAsync(&chg, sc.changed.get(), 4, cudaMemcpyDeviceToHost, st));
@@ -1289,7 +1329,11 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             carry_big_kernel<<<1184, 128, 0, st>>>(C, sc.Hc.get(), sc.big, sc.changed.get() + 1);
             KERNEL_CHECK();
             if (C.R) {
-                carry_repair_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(C, (uint32_t)table_entries, sc.Hc.get());
+                carry_repair_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(C, C.rk, C.R, (uint32_t)table_entries, sc.Hc.get());
+                KERNEL_CHECK();
+            }
+            if (C.R2) {
+                carry_repair_kernel<<<ceil_div_u(C.R2, 256), 256, 0, st>>>(C, C.rk2, C.R2, (uint32_t)table_entries, sc.Hc.get());
                 KERNEL_CHECK();
             }
             first = ex;

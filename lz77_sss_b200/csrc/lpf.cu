@@ -194,6 +194,40 @@ __global__ void all_candidates_kernel(const uint8_t* __restrict__ T, const pos_t
     o_lcel[i] = lcel;
 }
 
+// Both sides in one thread: the variant that faulted (kept behind LZ77SSS_FUSED_CANDIDATES=1 so that the fault can be
+// reproduced under compute-sanitizer).
+template <typename pos_t>
+__global__ void all_candidates_fused_kernel(const uint8_t* __restrict__ T, const pos_t* __restrict__ S, uint64_t s,
+                                            const uint32_t* __restrict__ SAx, uint32_t flip, const uint32_t* __restrict__ ISA,
+                                            const pos_t* __restrict__ LCP, const uint32_t* __restrict__ tab,
+                                            const pos_t* __restrict__ lcp_tab, uint32_t nblk, uint64_t lcap,
+                                            uint32_t* __restrict__ p_idx, uint32_t* __restrict__ n_idx,
+                                            pos_t* __restrict__ p_lce, pos_t* __restrict__ n_lce,
+                                            pos_t* __restrict__ p_lcel, pos_t* __restrict__ n_lcel) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s) return;
+    const uint64_t r = ISA[i];
+    const uint64_t pos = S[i];
+    const uint32_t v = (uint32_t)i ^ flip;
+    const uint32_t pr = prev_smaller(SAx, tab, nblk, r, v);
+    const uint32_t nr = next_smaller(SAx, tab, nblk, s, r, v);
+    uint32_t pi = NONE32, ni = NONE32;
+    pos_t pl = 0, nl = 0, pll = 0, nll = 0;
+    if (pr != NONE32) {
+        pi = SAx[pr] ^ flip;
+        pl = range_min(LCP, lcp_tab, nblk, (uint64_t)pr + 1, r);
+        pll = (pos_t)capped_left(T, (uint64_t)S[pi], pos, lcap);
+    }
+    if (nr != NONE32) {
+        ni = SAx[nr] ^ flip;
+        nl = range_min(LCP, lcp_tab, nblk, r + 1, (uint64_t)nr);
+        nll = (pos_t)capped_left(T, (uint64_t)S[ni], pos, lcap);
+    }
+    p_idx[i] = pi; n_idx[i] = ni;
+    p_lce[i] = pl; n_lce[i] = nl;
+    p_lcel[i] = pll; n_lcel[i] = nll;
+}
+
 __global__ void flip_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t s) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < s) out[i] = ~in[i];
@@ -336,6 +370,14 @@ void all_candidates(const uint8_t* T, uint64_t n, const pos_t* S, uint64_t s, bo
         }
         SAx = ls.sa_flip;
         tab = ls.saf_blkmin;
+    }
+    static const bool fused = getenv("LZ77SSS_FUSED_CANDIDATES") && getenv("LZ77SSS_FUSED_CANDIDATES")[0] == '1';
+    if (fused) {
+        all_candidates_fused_kernel<pos_t><<<ceil_div_u(s, 128), 128, 0, st>>>(
+            T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.psv_idx,
+            ls.nsv_idx, ls.psv_lce, ls.nsv_lce, ls.psv_lcel, ls.nsv_lcel);
+        KERNEL_CHECK();
+        return;
     }
     all_candidates_kernel<pos_t, 0><<<ceil_div_u(s, 128), 128, 0, st>>>(
         T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.psv_idx, ls.psv_lce,

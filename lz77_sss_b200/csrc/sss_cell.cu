@@ -5,9 +5,11 @@
 //
 // One CTA (512 threads) = one tile of NP = 16384 window ids = B = NP - tau candidate positions.
 // A thread owns a CELL of 32 consecutive windows and keeps their ids in registers:
-//   pass 1  roll the fingerprint of its cell from zero (2 IMAD + 2 byte extracts per window, text read straight
-//           from global memory with coalesced 16-byte loads: every byte is fetched from HBM once, the second
-//           use, tau bytes later, is an L1/L2 hit);  the missing start value of every cell comes from one
+//   stage   one elected thread arms an mbarrier and issues ONE bulk-async copy (cp.async.bulk, SASS UBLKCP: the TMA unit) of
+//           the tile's NP + tau + 16 text bytes into shared memory (the region that later holds the ids); every byte is
+//           fetched from HBM once, and with 2 CTAs per SM the copy of one tile overlaps the arithmetic of the other,
+//   pass 1  roll the fingerprint of its cell from zero (2 IMAD + 2 byte extracts per window, the 32 outgoing and the 32
+//           incoming bytes as 16-byte shared-memory loads);  the missing start value of every cell comes from one
 //           block-wide scan of affine maps (fingerprint algebra: fp' = fp * b^32 + c),
 //   pass 2  ids = F * b^k + partial_k, cell minimum, ids to (swizzled) shared memory,
 //   cells   F[t] = min of the tau/32 - 1 cells that every window starting in cell t fully contains (doubling),
@@ -52,6 +54,8 @@ __device__ __forceinline__ uint32_t make_id(uint32_t fp, uint32_t m, uint32_t o)
     return r;
 }
 
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
 __device__ __forceinline__ int id_slot(int p) {   // word index of id p in the swizzled shared array
     const int t = p >> 5, m = (p >> 2) & 7, e = p & 3;
     return (t << 5) + ((m ^ (t & 7)) << 2) + e;
@@ -79,12 +83,17 @@ __global__ void __launch_bounds__(NT, 2) sss_cell_kernel(const uint8_t* __restri
     __shared__ uint32_t s_warp[NW + 1];
     __shared__ uint32_t s_cnt[NW];
     __shared__ uint32_t s_nqpass, s_anyq, s_q;
+    __shared__ __align__(8) uint64_t s_mbar;
+    constexpr uint32_t TXT = NP + TAU + 16;                            // text bytes of the tile; fits the id array (4 NP bytes)
+    const uint8_t* sT = reinterpret_cast<const uint8_t*>(sId);         // staged text, dead before the ids are written
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     if (tid == 0) {
         s_nqpass = 0;
         s_anyq = 0;
         s_q = 0;
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&s_mbar)), "r"(1));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     sBits[tid] = 0;
     if (tid < CMPAD) { sCM0[NT + tid] = INFI; sCM1[NT + tid] = INFI; }
@@ -93,6 +102,13 @@ __global__ void __launch_bounds__(NT, 2) sss_cell_kernel(const uint8_t* __restri
     const uint32_t tile = blockIdx.x;
     const uint64_t i0 = (uint64_t)tile * B;
     const uint8_t* __restrict__ gT = T + i0;
+    if (tid == 0) {
+        // i0 is a multiple of 32, the text buffer is 256-byte aligned and zero-padded 64 KiB behind n: the copy is 16-byte
+        // aligned at both ends and stays inside the allocation
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&s_mbar)), "r"(TXT) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(sId)), "l"(gT), "r"(TXT), "r"(smem_u32(&s_mbar)) : "memory");
+    }
     const uint64_t nw = n - TAU + 1;                                    // real windows 0..nw-1; id(nw) = 0
     const uint64_t cnt_pos = n - 2 * (uint64_t)TAU + 2;                 // candidates 0..cnt_pos-1
     const bool last_tile = tile == gridDim.x - 1;
@@ -106,8 +122,14 @@ __global__ void __launch_bounds__(NT, 2) sss_cell_kernel(const uint8_t* __restri
     uint32_t cell_c, cell_min;
     {
         uint32_t ow[8], iw[8];
-        const uint4* po = reinterpret_cast<const uint4*>(gT + (size_t)tid * CH);
-        const uint4* pi = reinterpret_cast<const uint4*>(gT + (size_t)tid * CH + TAU);
+        {   // the staged text has arrived
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                             : "=r"(done) : "r"(smem_u32(&s_mbar)), "r"(0) : "memory");
+        }
+        const uint4* po = reinterpret_cast<const uint4*>(sT + (size_t)tid * CH);
+        const uint4* pi = reinterpret_cast<const uint4*>(sT + (size_t)tid * CH + TAU);
         uint4 a0 = po[0], a1 = po[1], b0 = pi[0], b1 = pi[1];
         ow[0] = a0.x; ow[1] = a0.y; ow[2] = a0.z; ow[3] = a0.w; ow[4] = a1.x; ow[5] = a1.y; ow[6] = a1.z; ow[7] = a1.w;
         iw[0] = b0.x; iw[1] = b0.y; iw[2] = b0.z; iw[3] = b0.w; iw[4] = b1.x; iw[5] = b1.y; iw[6] = b1.z; iw[7] = b1.w;

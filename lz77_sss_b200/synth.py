@@ -92,3 +92,31 @@ def markov_text(n: int, seed: int = 4, reuse: float = 0.3) -> np.ndarray:
             out[pos:pos + ln] = (32 + np.minimum(rng.geometric(0.08, size=ln), 90)).astype(np.uint8)
         pos += ln
     return out
+
+
+def genome_collection(n: int, seed: int = 3, genome_len: int = 30_000, edits: int = 10) -> np.ndarray:
+    """sars2-like: one random genome over {A,C,G,T,N}, then copies with `edits` random substitutions,
+    insertions or deletions each (against the previous copy, so the collection drifts), separated by '\\n'."""
+    rng = np.random.default_rng(seed)
+    alpha = np.frombuffer(b"ACGTN", dtype=np.uint8)
+    cur = alpha[rng.choice(5, size=genome_len, p=[0.3, 0.2, 0.2, 0.29, 0.01])]
+    out = np.empty(n, dtype=np.uint8)
+    pos = 0
+    while pos < n:
+        ln = min(cur.size, n - pos)
+        out[pos:pos + ln] = cur[:ln]
+        pos += ln
+        if pos < n:
+            out[pos] = 10
+            pos += 1
+        # next copy: `edits` edit operations on the current genome
+        kinds = rng.integers(0, 3, size=edits)
+        at = np.sort(rng.integers(0, cur.size, size=edits))[::-1]
+        for kind, a in zip(kinds, at):
+            if kind == 0:
+                cur[a] = alpha[rng.integers(0, 4)]
+            elif kind == 1:
+                cur = np.insert(cur, a, alpha[rng.integers(0, 4)])
+            elif cur.size > genome_len // 2:
+                cur = np.delete(cur, a)
+    return out
