@@ -68,6 +68,7 @@ typedef struct lz77sss_stats {
     uint64_t parse_rounds, parse_slices;   /* device emission: block-parse rounds over all slices, slices */
     uint64_t sparse_slices, sparse_fallbacks;  /* slices parsed with gap-only index entries / redone with all positions */
     uint64_t repair_entries;               /* index entries added while parsing (positions under gap factors that ran over phrases) */
+    uint64_t t_exact_ns, exact_doubling_rounds, exact_parse_rounds;   /* lz77sss_factorize_exact: suffix array + parse */
 } lz77sss_stats;
 
 /* factor callback: lz77_sss<pos_t>::factor {src,len} by value, in text order, on the calling thread
@@ -95,6 +96,14 @@ void lz77sss_destroy(lz77sss_handle* h);
 /* lz77_sss<pos_t>::factorize_approximate<greedy, lpf_opt, tau> (lz77_sss.hpp:176-186).
  * text: HOST pointer to n bytes (no padding required); copied to the device inside the call. */
 int lz77sss_factorize_approximate(lz77sss_handle* h, const uint8_t* text, uint64_t n, lz77sss_emit_fn emit, void* ctx);
+
+/* lz77_sss<pos_t>::factorize_exact<fact_mode, phr_mode, transf_mode, range_ds_t, tau> (lz77_sss.hpp:188-200): the exact LZ77
+ * factorization; with num_threads > 1 exact per section (16 sections per thread, cut at phrase boundaries of the
+ * approximation, transform_to_exact/common.cpp:48-74).  The approximation runs first with the handle's phr_mode / fact_mode
+ * (fact_mode must not be skip_phrases, lz77_sss.hpp:319); then the exact parse is computed from the suffix array of the text
+ * (csrc/exact.cu).  Factor LENGTHS equal the reference's for every transform_mode and range structure; sources are valid
+ * earlier occurrences (the reference's own choice depends on its range structure's scan order).  n < 2^32 - 2^16. */
+int lz77sss_factorize_exact(lz77sss_handle* h, const uint8_t* text, uint64_t n, lz77sss_emit_fn emit, void* ctx);
 
 /* Same, with the text already resident in device memory: d_text is a DEVICE pointer to a buffer obtained from
  * lz77sss_device_text_alloc (which provides the zero padding the kernels rely on).  host_text must hold the

@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "csrc", "_obj")
 LIB = os.path.join(HERE, "liblz77sss_b200.so")
-SOURCES = ["util", "sss", "sss_cell", "sss_small", "suffix", "lpf", "gap_hash", "gap_parse", "decode", "rks", "api"]
+SOURCES = ["util", "sss", "sss_cell", "sss_small", "suffix", "lpf", "gap_hash", "gap_parse", "decode", "rks", "exact", "api"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 

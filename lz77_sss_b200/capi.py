@@ -21,7 +21,7 @@ DEFAULT_GAP_BASES = (65599, 131071, 262147, 524309, 1048573)
 
 EXPORTS = [
     "lz77sss_last_error", "lz77sss_version", "lz77sss_device_count", "lz77sss_create", "lz77sss_destroy",
-    "lz77sss_factorize_approximate", "lz77sss_device_text_alloc", "lz77sss_device_text_upload",
+    "lz77sss_factorize_approximate", "lz77sss_factorize_exact", "lz77sss_device_text_alloc", "lz77sss_device_text_upload",
     "lz77sss_device_text_free", "lz77sss_factorize_approximate_device", "lz77sss_decode", "lz77sss_build_sss",
     "lz77sss_time_sss_kernel", "lz77sss_get_stats", "lz77sss_get_sss", "lz77sss_get_sa_s", "lz77sss_get_lcp_s",
     "lz77sss_get_lpf", "lz77sss_lce_batch", "lz77sss_sink_emit",
@@ -44,7 +44,8 @@ class Stats(C.Structure):
                [(k, C.c_uint64) for k in ("roll_threshold", "table_entries", "ctx_levels", "doubling_rounds",
                                           "gap_positions_hashed", "t_h2d_ns", "t_sss_ns", "t_sort_ns", "t_lce_ns",
                                           "t_lpf_ns", "t_d2h_ns", "t_chain_ns", "t_gap_hash_ns", "t_emit_ns", "t_total_ns",
-                                          "kernel_launches", "h2d_bytes", "d2h_bytes", "parse_rounds", "parse_slices", "sparse_slices", "sparse_fallbacks", "repair_entries")]
+                                          "kernel_launches", "h2d_bytes", "d2h_bytes", "parse_rounds", "parse_slices", "sparse_slices", "sparse_fallbacks", "repair_entries",
+                                          "t_exact_ns", "exact_doubling_rounds", "exact_parse_rounds")]
 
     def as_dict(self):
         d = {}
@@ -80,6 +81,7 @@ def lib():
         L.lz77sss_destroy.argtypes = [C.c_void_p]
         L.lz77sss_destroy.restype = None
         L.lz77sss_factorize_approximate.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+        L.lz77sss_factorize_exact.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
         L.lz77sss_device_text_alloc.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]
         L.lz77sss_device_text_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
         L.lz77sss_device_text_free.argtypes = [C.c_void_p, C.c_void_p]
@@ -180,6 +182,18 @@ class Factorizer:
         src, ln, s = self._sink(cap)
         emit = C.cast(lib().lz77sss_sink_emit, C.c_void_p)
         _check(lib().lz77sss_factorize_approximate(self._h, _ptr(t), t.size, emit, C.byref(s)))
+        z = int(s.count)
+        if z > cap:
+            raise RuntimeError(f"factor sink too small: {z} > {cap}")
+        return src[:z], ln[:z]
+
+    def factorize_exact(self, text, cap=None):
+        """Exact LZ77 (per section when num_threads > 1): host text -> (src, len)."""
+        t = _u8(text)
+        cap = cap if cap is not None else t.size + 1
+        src, ln, s = self._sink(cap)
+        emit = C.cast(lib().lz77sss_sink_emit, C.c_void_p)
+        _check(lib().lz77sss_factorize_exact(self._h, _ptr(t), t.size, emit, C.byref(s)))
         z = int(s.count)
         if z > cap:
             raise RuntimeError(f"factor sink too small: {z} > {cap}")

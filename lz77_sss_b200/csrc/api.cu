@@ -138,9 +138,10 @@ struct lz77sss_handle {
     // device emission
     gap_parse_scratch gp;
     decode_scratch dec;
+    exact_scratch ex;
     dbuf<uint64_t> dec_src, dec_len;
     dbuf<uint8_t> dec_out;
-    std::vector<uint64_t> f_src, f_len;
+    pinned_vec<uint64_t> f_src, f_len;  // factors of the device emission (pinned: they arrive by D2H copies)
     uint64_t slice_len = 1ull << 28;
     uint32_t block_len = 2048;
     bool host_emit = false;
@@ -1251,6 +1252,66 @@ int lz77sss_factorize_approximate(lz77sss_handle* h, const uint8_t* text, uint64
         h->stats.h2d_bytes += n;
         h->stats.t_total_ns += t_h2d;
         return rc;
+    });
+}
+
+int lz77sss_factorize_exact(lz77sss_handle* h, const uint8_t* text, uint64_t n, lz77sss_emit_fn emit, void* ctx) {
+    if (!h || !text || !emit) return fail(LZ77SSS_E_ARG, "null argument");
+    if (n == 0) return fail(LZ77SSS_E_ARG, "empty input");
+    if (h->cfg.fact_mode == LZ77SSS_FACT_SKIP_PHRASES) return fail(LZ77SSS_E_ARG, "factorize_exact: fact_mode must not be skip_phrases (lz77_sss.hpp:319)");
+    if (n >= 0xFFFF0000ull) return fail(LZ77SSS_E_UNSUPPORTED, "factorize_exact: n must be below 2^32 - 2^16 (the suffix array of a longer text does not fit one GPU)");
+    return guarded([&]() {
+        CUDA_CHECK(cudaSetDevice(h->cfg.device));
+        pos_bits_guard guard(h->cfg, n);
+        auto t0 = clk::now();
+        uint8_t* d = alloc_text(h->text_buf, n, h->st);
+        CUDA_CHECK(cudaMemcpyAsync(d, text, n, cudaMemcpyHostToDevice, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        const uint64_t t_h2d = ns_since(t0);
+        // the approximation (lz77_sss.hpp:320-325): its phrase boundaries place the sections, its LCE structure answers
+        // the parse's longest-common-extension queries
+        std::vector<uint64_t> aprx_len;
+        auto collect = +[](void* c, uint64_t, uint64_t len) { static_cast<std::vector<uint64_t>*>(c)->push_back(len ? len : 1); };
+        int rc = factorize_dispatch(h, d, text, n, collect, &aprx_len);
+        if (rc) return rc;
+        const uint64_t z = aprx_len.size();
+        const uint32_t p = h->cfg.num_threads;
+        const uint64_t nsect = p == 1 ? 1 : (uint64_t)p * 16;               // num_par_sect_per_thr (lz77_sss.hpp:94)
+        std::vector<uint64_t> sect{0};
+        if (nsect > 1 && z / nsect > 0) {       // section k starts where phrase k * (z / nsect) of the approximation starts
+            const uint64_t step = z / nsect;
+            uint64_t pos = 0, next = step, k = 1;
+            for (uint64_t f = 0; f < z && k < nsect; f++) {
+                if (f == next) {
+                    sect.push_back(pos);
+                    k++;
+                    next = k * step;
+                }
+                pos += aprx_len[f];
+            }
+        }
+        sect.push_back(n);
+        t0 = clk::now();
+        h->f_src.clear();
+        h->f_len.clear();
+        if (h->pos_bytes == 4) {
+            auto& P = h->p32;
+            exact_run<uint32_t>(d, n, h->cfg.tau, P.S.get(), P.s, P.suf, P.lce, sect, h->ex, h->st, h->f_src, h->f_len);
+        } else {
+            auto& P = h->p64;
+            exact_run<uint64_t>(d, n, h->cfg.tau, P.S.get(), P.s, P.suf, P.lce, sect, h->ex, h->st, h->f_src, h->f_len);
+        }
+        h->stats.t_exact_ns = ns_since(t0);
+        h->stats.exact_doubling_rounds = h->ex.rounds;
+        h->stats.exact_parse_rounds = h->ex.parse_rounds;
+        const uint64_t ze = h->f_src.size();
+        for (uint64_t q = 0; q < ze; q++) emit(ctx, h->f_src[q], h->f_len[q]);
+        h->stats.num_factors = ze;
+        h->stats.t_h2d_ns = t_h2d;
+        h->stats.h2d_bytes += n;
+        h->stats.d2h_bytes += 16 * ze;
+        h->stats.t_total_ns += t_h2d + h->stats.t_exact_ns;
+        return LZ77SSS_OK;
     });
 }
 

@@ -6,6 +6,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 
@@ -72,6 +73,36 @@ struct dbuf {
     }
     T* get() const { return p; }
     operator T*() const { return p; }
+};
+
+// Pinned host array that grows and keeps its contents (factor output: device-to-host copies into pageable memory are
+// staged by the driver and run at a fraction of the link rate).
+template <typename T>
+struct pinned_vec {
+    T* p = nullptr;
+    size_t n = 0, cap = 0;
+    pinned_vec() = default;
+    pinned_vec(const pinned_vec&) = delete;
+    pinned_vec& operator=(const pinned_vec&) = delete;
+    ~pinned_vec() { if (p) cudaFreeHost(p); }
+    size_t size() const { return n; }
+    void clear() { n = 0; }
+    T* data() { return p; }
+    const T* data() const { return p; }
+    T& operator[](size_t i) { return p[i]; }
+    const T& operator[](size_t i) const { return p[i]; }
+    void resize(size_t m) {
+        if (m > cap) {
+            const size_t want = m + m / 2 + 4096;
+            T* q = nullptr;
+            CUDA_CHECK(cudaMallocHost(&q, want * sizeof(T)));
+            if (n) memcpy(q, p, n * sizeof(T));
+            if (p) cudaFreeHost(p);
+            p = q;
+            cap = want;
+        }
+        n = m;
+    }
 };
 
 static inline unsigned ceil_div_u(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }

@@ -888,7 +888,7 @@ template <typename pos_t>
 void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, suffix_state<pos_t>& ss,
                    lce_state<pos_t>& ls, const gap_hash_params& gp, uint64_t table_entries, const uint64_t* h_ml,
                    uint64_t m, uint64_t n_cut, uint64_t slice_len, uint32_t block_len, gap_parse_scratch& sc,
-                   cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4],
+                   cudaStream_t st, pinned_vec<uint64_t>& out_src, pinned_vec<uint64_t>& out_len, uint64_t handover[4],
                    bool naive, const gap_parse_range* range) {
     static_assert(sizeof(block_state) == 32, "block_state layout");
     if (slice_len > (1ull << 28)) slice_len = 1ull << 28;
@@ -1390,7 +1390,7 @@ void gap_parse_query(gap_parse_scratch& sc, const uint32_t* h_buckets, uint32_t 
     template void gap_parse_run<pos_t>(const uint8_t*, uint64_t, uint32_t, const pos_t*, uint64_t, suffix_state<pos_t>&, \
                                        lce_state<pos_t>&, const gap_hash_params&, uint64_t, const uint64_t*, uint64_t,  \
                                        uint64_t, uint64_t, uint32_t, gap_parse_scratch&, cudaStream_t,                  \
-                                       std::vector<uint64_t>&, std::vector<uint64_t>&, uint64_t[4], bool,                 \
+                                       pinned_vec<uint64_t>&, pinned_vec<uint64_t>&, uint64_t[4], bool,                   \
                                        const gap_parse_range*);
 INST(uint32_t)
 INST(uint64_t)

@@ -38,6 +38,63 @@ __device__ __forceinline__ val_t range_min(const val_t* __restrict__ v, const va
 }
 
 
+// ---- nearest smaller values over an array SA with a sparse table `tab` of its block minima (blocks of RMQ_BLK) -------------
+// largest r' < r with SA[r'] < v, or NONE32
+__device__ __forceinline__ uint32_t prev_smaller(const uint32_t* __restrict__ SA, const uint32_t* __restrict__ tab,
+                                                 uint32_t nblk, uint64_t r, uint32_t v) {
+    const uint64_t b = r / RMQ_BLK;
+    for (uint64_t j = r; j > b * RMQ_BLK;) {
+        j--;
+        if (SA[j] < v) return (uint32_t)j;
+    }
+    if (b == 0) return NONE32;
+    uint64_t e = b, w = 1, lo;
+    while (true) {
+        lo = e >= w ? e - w : 0;
+        if (blk_range_min(tab, nblk, lo, e - 1) < v) break;
+        if (lo == 0) return NONE32;
+        w *= 2;
+    }
+    uint64_t hi = e - 1;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi + 1) / 2;
+        if (blk_range_min(tab, nblk, mid, hi) < v) lo = mid;
+        else hi = mid - 1;
+    }
+    for (uint64_t j = (lo + 1) * RMQ_BLK; j > lo * RMQ_BLK;) {
+        j--;
+        if (SA[j] < v) return (uint32_t)j;
+    }
+    return NONE32;  // unreachable
+}
+
+// smallest r' > r with SA[r'] < v, or NONE32
+__device__ __forceinline__ uint32_t next_smaller(const uint32_t* __restrict__ SA, const uint32_t* __restrict__ tab,
+                                                 uint32_t nblk, uint64_t s, uint64_t r, uint32_t v) {
+    const uint64_t b = r / RMQ_BLK;
+    const uint64_t bend = min(s, (b + 1) * RMQ_BLK);
+    for (uint64_t j = r + 1; j < bend; j++)
+        if (SA[j] < v) return (uint32_t)j;
+    if (b + 1 >= nblk) return NONE32;
+    uint64_t e = b + 1, w = 1, hi;   // search blocks [e, ...]
+    while (true) {
+        hi = e + w - 1 < nblk ? e + w - 1 : nblk - 1;
+        if (blk_range_min(tab, nblk, e, hi) < v) break;
+        if (hi == nblk - 1) return NONE32;
+        w *= 2;
+    }
+    uint64_t lo = e;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi) / 2;
+        if (blk_range_min(tab, nblk, lo, mid) < v) hi = mid;
+        else lo = mid + 1;
+    }
+    const uint64_t be = min(s, (lo + 1) * RMQ_BLK);
+    for (uint64_t j = lo * RMQ_BLK; j < be; j++)
+        if (SA[j] < v) return (uint32_t)j;
+    return NONE32;  // unreachable
+}
+
 template <typename pos_t>
 struct lce_view {
     const uint8_t* T;

@@ -41,62 +41,6 @@ __global__ void sparse_level_kernel(val_t* __restrict__ tab, uint32_t nblk, int 
     tab[(uint64_t)l * nblk + b] = y < x ? y : x;
 }
 
-// largest r' < r with SA[r'] < v, or NONE32
-__device__ __forceinline__ uint32_t prev_smaller(const uint32_t* __restrict__ SA, const uint32_t* __restrict__ tab,
-                                                 uint32_t nblk, uint64_t r, uint32_t v) {
-    const uint64_t b = r / BLK;
-    for (uint64_t j = r; j > b * BLK;) {
-        j--;
-        if (SA[j] < v) return (uint32_t)j;
-    }
-    if (b == 0) return NONE32;
-    uint64_t e = b, w = 1, lo;
-    while (true) {
-        lo = e >= w ? e - w : 0;
-        if (blk_range_min(tab, nblk, lo, e - 1) < v) break;
-        if (lo == 0) return NONE32;
-        w *= 2;
-    }
-    uint64_t hi = e - 1;
-    while (lo < hi) {
-        uint64_t mid = (lo + hi + 1) / 2;
-        if (blk_range_min(tab, nblk, mid, hi) < v) lo = mid;
-        else hi = mid - 1;
-    }
-    for (uint64_t j = (lo + 1) * BLK; j > lo * BLK;) {
-        j--;
-        if (SA[j] < v) return (uint32_t)j;
-    }
-    return NONE32;  // unreachable
-}
-
-// smallest r' > r with SA[r'] < v, or NONE32
-__device__ __forceinline__ uint32_t next_smaller(const uint32_t* __restrict__ SA, const uint32_t* __restrict__ tab,
-                                                 uint32_t nblk, uint64_t s, uint64_t r, uint32_t v) {
-    const uint64_t b = r / BLK;
-    const uint64_t bend = min(s, (b + 1) * BLK);
-    for (uint64_t j = r + 1; j < bend; j++)
-        if (SA[j] < v) return (uint32_t)j;
-    if (b + 1 >= nblk) return NONE32;
-    uint64_t e = b + 1, w = 1, hi;   // search blocks [e, ...]
-    while (true) {
-        hi = e + w - 1 < nblk ? e + w - 1 : nblk - 1;
-        if (blk_range_min(tab, nblk, e, hi) < v) break;
-        if (hi == nblk - 1) return NONE32;
-        w *= 2;
-    }
-    uint64_t lo = e;
-    while (lo < hi) {
-        uint64_t mid = (lo + hi) / 2;
-        if (blk_range_min(tab, nblk, lo, mid) < v) hi = mid;
-        else lo = mid + 1;
-    }
-    const uint64_t be = min(s, (lo + 1) * BLK);
-    for (uint64_t j = lo * BLK; j < be; j++)
-        if (SA[j] < v) return (uint32_t)j;
-    return NONE32;  // unreachable
-}
-
 // number of equal characters going left from T[i] and T[j] (i < j), at most cap (cap <= i + 1)
 __device__ __forceinline__ uint64_t thread_lce_left(const uint8_t* __restrict__ T, uint64_t i, uint64_t j, uint64_t cap) {
     uint64_t k = 0;

@@ -151,10 +151,26 @@ template <typename pos_t>
 void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, suffix_state<pos_t>& ss,
                    lce_state<pos_t>& ls, const gap_hash_params& gp, uint64_t table_entries, const uint64_t* h_ml,
                    uint64_t m, uint64_t n_cut, uint64_t slice_len, uint32_t block_len, gap_parse_scratch& sc,
-                   cudaStream_t st, std::vector<uint64_t>& out_src, std::vector<uint64_t>& out_len, uint64_t handover[4],
+                   cudaStream_t st, pinned_vec<uint64_t>& out_src, pinned_vec<uint64_t>& out_len, uint64_t handover[4],
                    bool naive = false, const gap_parse_range* range = nullptr);
 // table entries (last inserted position + 1, 0 = none) of the given buckets after gap_parse_run
 void gap_parse_query(gap_parse_scratch& sc, const uint32_t* h_buckets, uint32_t cnt, uint64_t* h_out, cudaStream_t st);
+
+// ---- exact.cu: exact LZ77 (factorize_exact) from the full suffix array -------------------------------------------------------
+struct exact_scratch {
+    dbuf<uint64_t> k0, k1, fsrc, flen, sect;
+    dbuf<uint32_t> v0, v1, rank, flag, acc, counter, tab, tr_cnt, cnt, J;
+    dbuf<uint8_t> blk, marked, dirty;
+    sort_scratch sort;
+    scan_scratch scan;
+    int rounds = 0, parse_rounds = 0;      // prefix-doubling rounds, parse rounds of the last run
+};
+// sect: section starts, ascending, sect.front() == 0, sect.back() == n (factors are cut at section ends).
+// Needs the LCE structures of a preceding approximation on the same text (S, ss, ls).
+template <typename pos_t>
+void exact_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t* d_S, uint64_t s, suffix_state<pos_t>& ss,
+               lce_state<pos_t>& ls, const std::vector<uint64_t>& sect, exact_scratch& sc, cudaStream_t st,
+               pinned_vec<uint64_t>& out_src, pinned_vec<uint64_t>& out_len);
 
 // ---- rks.cu: rabin_karp_substring<31> (prefix fingerprints modulo 2^31 - 1, one per 16 bytes) ---------------------------
 struct rks_state {

@@ -11,8 +11,9 @@
 //    (rolling_hash.hpp:30-39,127-130).  lz77_sss_b200::options().gap_bases does the same when left at 0 and can be
 //    pinned for reproducible factor streams (the parity tests do).
 //  * the input needs no zero padding; it is only read in [0, n).
-//  * implemented: factorize_approximate for all three factorize modes x four phrase modes, and decode (any n).
-//    factorize_exact has the reference's template list but throws: the exact path is not built (scope: DESIGN.md).
+//  * implemented: factorize_approximate for all three factorize modes x four phrase modes, decode (any n), and
+//    factorize_exact for texts below 4 GiB (same factor lengths as the reference for every transform_mode / range_ds_t;
+//    sources are valid earlier occurrences but not necessarily the reference's, whose choice depends on its range structure).
 //  * LZ77_SSS_BENCH: like the reference (lz77_sss.hpp:298-311,357-365), a translation unit that defines LZ77_SSS_BENCH
 //    and the globals text_name / result_file_path / result_file before including this header gets one
 //    `RESULT key=value ...` line per logged factorization, with the reference's keys; the phase keys carry the
@@ -140,9 +141,16 @@ public:
               transform_mode transf_mode = default_transf_mode,
               template <typename> typename range_ds_t = default_range_ds_t, uint64_t tau = default_tau, typename char_t,
               typename output_fnc_t>
-    static void factorize_exact(char_t*, pos_t, output_fnc_t, parameters = {}) {       // lz77_sss.hpp:188-200
+    static void factorize_exact(char_t* input, pos_t input_size, output_fnc_t output, parameters params = {}) {   // lz77_sss.hpp:188-200
+        static_assert(sizeof(char_t) == 1);
         static_assert(fact_mode != skip_phrases);                         // lz77_sss.hpp:319
-        throw std::runtime_error("lz77sss_b200: factorize_exact is not built (DESIGN.md scope table)");
+        // transf_mode and range_ds_t choose HOW the reference searches; the factor lengths do not depend on them, and the
+        // device computes them from the suffix array of the text (csrc/exact.cu)
+        handle h(tau, params, (uint32_t)phr_mode, (uint32_t)fact_mode);
+        auto tramp = [](void* ctx, uint64_t src, uint64_t len) {
+            (*static_cast<output_fnc_t*>(ctx))(factor{(pos_t)src, (pos_t)len});
+        };
+        lz77_sss_b200::check(lz77sss_factorize_exact(h.h, reinterpret_cast<const uint8_t*>(input), input_size, +tramp, &output));
     }
 
     template <std::input_iterator fact_it_t, typename out_it_t>

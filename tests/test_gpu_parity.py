@@ -555,3 +555,50 @@ def test_file_level_tools_round_trip(capi, oracle, tmp_path):
         assert r.returncode == 0, r.stdout + r.stderr
     assert (np.fromfile(tmp_path / "text.gap.out", dtype=np.uint8) == text).all()
     assert os.path.getsize(tmp_path / "text.gap") < text.size // 2
+
+
+def _valid_copies(text, src, ln):
+    lens = np.maximum(ln, 1).astype(np.int64)
+    pos = np.concatenate([[0], np.cumsum(lens)])[:-1]
+    for k in np.nonzero(ln > 0)[0]:
+        s_, l_, p_ = int(src[k]), int(ln[k]), int(pos[k])
+        if not (s_ < p_ and (text[s_:s_ + l_] == text[p_:p_ + l_]).all()):
+            return False
+    lit = ln == 0
+    return bool((text[pos[lit]] == src[lit].astype(np.uint8)).all())
+
+
+def test_factorize_exact_equals_exact_lz77(capi, oracle):
+    """factorize_exact (lz77_sss.hpp:188-200) at num_threads = 1: the factor lengths are those of the greedy longest-previous-
+    factor parse (independent suffix-array checker in the oracle; the reference's three transform modes give the same
+    lengths, tests/test_oracle.py), every source is a real earlier occurrence, and decode reproduces the text."""
+    for name, text in _texts().items():
+        if name in ("zeros", "period3"):
+            continue
+        for tau in (16, 512):
+            es, el = oracle.lz77_exact(text)
+            with capi.Factorizer(tau=tau, num_threads=1) as F:
+                src, ln = F.factorize_exact(text)
+                assert _eq(ln, el), (name, tau, src.size, es.size)
+                assert _valid_copies(text, src, ln), (name, tau)
+                assert (F.decode(src, ln, text.size) == text).all()
+                st = F.stats()
+                assert st["exact_parse_rounds"] >= 1 and st["t_exact_ns"] > 0
+
+
+def test_factorize_exact_sections_against_reference_build(capi, oracle):
+    """num_threads > 1: exact per section (16 sections per thread, cut at the approximation's phrase boundaries,
+    transform_to_exact/common.cpp:48-74): lengths equal the reference's own factorize_exact<greedy, lpf_opt, with_samples>."""
+    tau = 64
+    _need_ref(oracle, tau)
+    for name in ("rep", "dna", "markov", "xx"):
+        text = _texts()[name]
+        for p, tm in ((1, oracle.WITH_SAMPLES), (2, oracle.WITH_SAMPLES), (3, oracle.WITHOUT_SAMPLES)):
+            # the reference draws its gap-index bases while it runs; peek them first so that both approximations agree
+            bases = np.zeros(5, dtype=np.uint64)
+            oracle.ref(tau).refdrv_peek_next_bases(bases)
+            rs, rl, _ = oracle.ref_factorize_exact(text, tau, p=p, transf_mode=tm)
+            with capi.Factorizer(tau=tau, num_threads=p, gap_bases=bases) as F:
+                src, ln = F.factorize_exact(text)
+                assert _eq(ln, rl), (name, p, tm, src.size, rs.size)
+                assert _valid_copies(text, src, ln), (name, p)
