@@ -891,6 +891,22 @@ uint64_t emit_tail(lz77sss_handle* h, const uint8_t* host_text, uint64_t n, cons
     return z;
 }
 
+// hands z factors to the callback in order; the library's own array sink (lz77sss_sink_emit) is filled with two block
+// copies instead of z indirect calls
+void emit_all(const uint64_t* src, const uint64_t* len, uint64_t z, lz77sss_emit_fn emit, void* ctx) {
+    if (emit == &lz77sss_sink_emit) {
+        auto* s = static_cast<lz77sss_factor_sink*>(ctx);
+        const uint64_t room = s->count < s->cap ? s->cap - s->count : 0, m = std::min(z, room);
+        if (m) {
+            std::memcpy(s->src + s->count, src, m * 8);
+            std::memcpy(s->len + s->count, len, m * 8);
+        }
+        s->count += z;
+        return;
+    }
+    for (uint64_t q = 0; q < z; q++) emit(ctx, src[q], len[q]);
+}
+
 template <typename pos_t>
 int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n,
                    lz77sss_emit_fn emit, void* ctx) {
@@ -1078,7 +1094,7 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
 
     t0 = clk::now();
     uint64_t z = h->f_src.size();
-    for (uint64_t q = 0; q < z; q++) emit(ctx, h->f_src[q], h->f_len[q]);
+    emit_all(h->f_src.data(), h->f_len.data(), z, emit, ctx);
     if (ho[0] < n) z += emit_tail(h, host_text, n, ML, g, bp, ho, naive, emit, ctx);
     st.num_factors = z;
     st.t_emit_ns = ns_since(t0);
@@ -1305,7 +1321,7 @@ int lz77sss_factorize_exact(lz77sss_handle* h, const uint8_t* text, uint64_t n, 
         h->stats.exact_doubling_rounds = h->ex.rounds;
         h->stats.exact_parse_rounds = h->ex.parse_rounds;
         const uint64_t ze = h->f_src.size();
-        for (uint64_t q = 0; q < ze; q++) emit(ctx, h->f_src[q], h->f_len[q]);
+        emit_all(h->f_src.data(), h->f_len.data(), ze, emit, ctx);
         h->stats.num_factors = ze;
         h->stats.t_h2d_ns = t_h2d;
         h->stats.h2d_bytes += n;

@@ -177,6 +177,103 @@ __global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restr
     }
 }
 
+// Sparse slice, few positions need entries (a few percent on repetitive texts): the dense kernel above rolls every window of
+// every tile.  Here one CTA takes SP_TILE = 16384 positions, lists the 64-position segments that hold a needed position, and
+// a lane rolls one listed segment (warp x <-> pattern x as above) from its first to its last needed position only.  Output
+// as above: keys / vals compacted in time order at 5 * (needed positions in front), tkey at the dense index.
+constexpr int SP_TILE = 16384, SP_SEGS = SP_TILE / GE_SEG, SP_WORDS = SP_TILE / 32;
+__global__ void __launch_bounds__(160) gap_entries_sparse_kernel(const uint8_t* __restrict__ T, uint64_t n, const ghp5 hp,
+                                                                 uint64_t a0, uint64_t cnt, uint32_t* __restrict__ keys,
+                                                                 uint32_t* __restrict__ tkeys, uint32_t* __restrict__ vals,
+                                                                 const uint32_t* __restrict__ skip,
+                                                                 const uint32_t* __restrict__ tile_off) {
+    __shared__ uint32_t sNeed[SP_WORDS], sRank[SP_WORDS + 1];
+    __shared__ uint16_t sAct[SP_SEGS];
+    __shared__ uint32_t s_nact;
+    const int tid = threadIdx.x, lane = tid & 31, x = tid >> 5;
+    const uint64_t t0 = (uint64_t)blockIdx.x * SP_TILE;                   // tile start, slice-relative
+    const uint32_t in_tile = cnt - t0 < (uint64_t)SP_TILE ? (uint32_t)(cnt - t0) : (uint32_t)SP_TILE;
+    constexpr int SUB = SP_TILE / GE_TILE;                                // tile_off counts per GE_TILE positions
+    const uint32_t first = tile_off[(uint64_t)blockIdx.x * SUB];
+    const uint64_t lastsub = min((uint64_t)(blockIdx.x + 1) * SUB, (cnt + GE_TILE - 1) / GE_TILE);
+    if (tile_off[lastsub] == first) return;                               // nothing needed in this tile
+    if (tid == 0) s_nact = 0;
+    for (int k = tid; k < SP_WORDS; k += 160) {
+        const uint64_t p0 = (uint64_t)k * 32;
+        uint32_t need = p0 < in_tile ? ~skip[t0 / 32 + k] : 0u;
+        if (p0 < in_tile && p0 + 32 > in_tile) need &= (1u << (in_tile & 31)) - 1u;
+        sNeed[k] = need;
+    }
+    __syncthreads();
+    if (x == 0) {                                                         // exclusive prefix of the popcounts, one warp
+        uint32_t run = 0;
+        for (int c = 0; c < SP_WORDS; c += 32) {
+            const uint32_t v = __popc(sNeed[c + lane]);
+            uint32_t inc = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += y;
+            }
+            sRank[c + lane] = run + inc - v;
+            run += __shfl_sync(0xffffffffu, inc, 31);
+        }
+    } else if (x == 1) {                                                  // list of the segments with a needed position
+        for (int sg = lane; sg < SP_SEGS; sg += 32)
+            if (sNeed[2 * sg] | sNeed[2 * sg + 1]) sAct[atomicAdd(&s_nact, 1u)] = (uint16_t)sg;
+    }
+    __syncthreads();
+    const uint32_t nact = s_nact;
+    const uint64_t L = hp.L[x], base = hp.base[x];
+    const m107* __restrict__ nbt = hp.nbtab + x * 256;
+    const uint64_t c0 = 5ull * first, e0 = 5 * t0;
+    for (uint32_t ai = lane; ai < nact; ai += 32) {
+        const int sg = sAct[ai];
+        const uint64_t need = (uint64_t)sNeed[2 * sg] | ((uint64_t)sNeed[2 * sg + 1] << 32);
+        const int lo = __ffsll((long long)need) - 1, hi = 63 - __clzll((long long)need);
+        const uint8_t* __restrict__ tp = T + a0 + t0 + (uint64_t)sg * GE_SEG;          // the device text is zero-padded behind n
+        const uint64_t pos0 = a0 + t0 + (uint64_t)sg * GE_SEG;
+        m107 fp;
+        fp.lo = fp.hi = 0;
+        bool live = false;                                                // fp holds the window at the current position
+        uint32_t rank = sRank[2 * sg];
+        for (int j = lo; j <= hi; j++) {
+            const uint64_t pos = pos0 + j;
+            const bool fits = pos + L < n;
+            if (fits && !live) {
+                fp.lo = fp.hi = 0;
+                for (uint64_t q = 0; q < L; q++) {
+                    m107 c;
+                    c.lo = tp[j + q]; c.hi = 0;
+                    fp = muladd107(fp, base, c);
+                }
+                live = true;
+            }
+            if ((need >> j) & 1ull) {
+                const uint32_t key = fits ? (uint32_t)(fp.lo & hp.mask) : hp.invalid_key;
+                const uint64_t o = 5ull * (uint64_t)(sg * GE_SEG + j) + (4 - x);
+                keys[c0 + 5ull * rank + (4 - x)] = key;
+                vals[c0 + 5ull * rank + (4 - x)] = (uint32_t)(e0 + o);
+                tkeys[e0 + o] = key;
+                rank++;
+            }
+            if (fits && j < hi) {
+                if (!((need >> (j + 1)) & 1ull) && __popcll(need >> (j + 1)) && __ffsll((long long)(need >> (j + 1))) - 1 > (int)L) {
+                    live = false;                                         // a long stretch without needed positions: start over
+                    j += __ffsll((long long)(need >> (j + 1))) - 1;       // (the loop's j++ lands on the next needed one)
+                    continue;
+                }
+                m107 infl = nbt[tp[j]];                                   // -(base^L) * T[pos]
+                const uint64_t in = tp[j + L];
+                infl.lo += in;
+                infl.hi += infl.lo < in;
+                infl = fold107(infl.lo, infl.hi);
+                fp = muladd107(fp, base, infl);
+            }
+        }
+    }
+}
+
 // positions of the slice that need no entry when no gap factor runs over a whole phrase: the inside (beg, end) of
 // every phrase (the phrase start is probed, greedy.cpp:111-117).  One warp per phrase k0 + w.
 __global__ void __launch_bounds__(128) skip_bits_kernel(const uint64_t* __restrict__ ml_beg, const uint64_t* __restrict__ ml_end,
@@ -457,7 +554,7 @@ __global__ void __launch_bounds__(128, 16) parse_kernel(const parse_ctx C, const
         C.exit_[b] = ex;
         C.tr_cnt[b] = t;
         C.ovr[b] = bad ? 1 : 0;
-        C.dirty[b] = 0;
+        C.dirty[b] = bad ? 1 : 0;          // a block that lacked entries is parsed again once they exist
         if (chg) {
             atomicOr(C.changed, 1u);
             atomicAdd(C.changed + 3, 1u);
@@ -777,6 +874,49 @@ __global__ void dirty_from_block_kernel(uint8_t* __restrict__ dirty, uint32_t fb
     if (b < nb) dirty[b] = 1;
 }
 
+// Which blocks can see NEW entries of the repair lists (change tracking): like a position whose bit flipped to "inserted",
+// a new entry can become the answer of the probes behind it in its bucket, up to and including the first entry that is
+// inserted (a probe inserts its position, so an entry that is not inserted is not a probe).  newent: the entries as the
+// repair kernel wrote them, (bucket << 32 | entry id); the lists are sorted again by now.
+__global__ void __launch_bounds__(256) dirty_from_new_entries_kernel(const parse_ctx C, const uint64_t* __restrict__ newent,
+                                                                    uint32_t cnt, uint32_t nbuckets) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= cnt) return;
+    const uint64_t key = newent[k];
+    const uint32_t b = (uint32_t)(key >> 32), e = (uint32_t)key;
+    if (b >= nbuckets) return;
+    {
+        uint32_t l = C.bstart[b], h = C.bstart[b + 1];
+        const uint32_t hi = h;
+        while (l < h) {                              // first entry of the sorted index behind e
+            const uint32_t mid = (l + h) >> 1;
+            if (C.sval[mid] <= e) l = mid + 1;
+            else h = mid;
+        }
+        for (uint32_t kk = l; kk < hi; kk++) {
+            const uint32_t q = C.sval[kk] / 5u;
+            if (!not_inserted(C.notins, q)) { C.dirty[q / C.BL] = 1; break; }
+        }
+    }
+    for (int which = 0; which < 2; which++) {
+        const uint64_t* __restrict__ rk = which ? C.rk2 : C.rk;
+        const uint32_t R = which ? C.R2 : C.R;
+        if (!R) continue;
+        uint32_t rl = 0, rh = R;
+        while (rl < rh) {
+            const uint32_t mid = (rl + rh) >> 1;
+            if (rk[mid] <= key) rl = mid + 1;
+            else rh = mid;
+        }
+        for (; rl < R; rl++) {
+            const uint64_t v = rk[rl];
+            if ((uint32_t)(v >> 32) != b) break;
+            const uint32_t q = (uint32_t)v / 5u;
+            if (!not_inserted(C.notins, q)) { C.dirty[q / C.BL] = 1; break; }
+        }
+    }
+}
+
 // the repair list's share of the carried table
 __global__ void carry_repair_kernel(const parse_ctx C, const uint64_t* __restrict__ rk, uint32_t R, uint32_t nbuckets,
                                     unsigned long long* __restrict__ Hc) {
@@ -1027,8 +1167,13 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             // a dense slice has vals[e] = e (the sort generates them in its first pass) and keys = tkey (its first
             // pass reads tkey)
             PROF_BEGIN(st);
-            gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, sparse ? keys : nullptr, sc.tkey, sparse ? vals : nullptr,
-                                                       sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
+            // sparse slice with few needed positions: only the 64-position segments that hold one are rolled
+            if (sparse && E * 8 < 5 * cnt)
+                gap_entries_sparse_kernel<<<ceil_div_u(cnt, SP_TILE), 160, 0, st>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, vals,
+                                                                                  sc.skip.get(), sc.tile_off.get());
+            else
+                gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, sparse ? keys : nullptr, sc.tkey, sparse ? vals : nullptr,
+                                                           sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
             KERNEL_CHECK();
             // algorithmic bytes: the slice's text once, the bucket ids of its indexed positions in time order, and on a
             // sparse slice the compacted (bucket, entry id) pairs for the sort
@@ -1101,7 +1246,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             rk_cur = sc.rk0; rk_alt = sc.rk1; rv_cur = sc.rv0; rv_alt = sc.rv1; rk2_cur = sc.rkb0; rk2_alt = sc.rkb1;
             CUDA_CHECK(cudaMemsetAsync(sc.req.get(), 0, 8, st));
         }
-        bool give_up_sparse = false;
+        bool give_up_sparse = false, track_now = false;
         uint64_t repair_total = 0;
         uint32_t pending_fb = 0xFFFFFFFFu;          // blocks from here on see new repair entries in the next round
         C.ovr = sc.ovr;
@@ -1139,6 +1284,12 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             CUDA_CHECK(cudaStreamSynchronize(st));
             if (r2[1] == before) return false;
             repair_total += r2[1] - before;
+            // the new entries, kept aside for the change tracking below (the sorts permute the lists)
+            const uint32_t nnew = std::min(r2[1], cap_here) - before;
+            if (track_now) {
+                sc.newent.reserve(nnew + 8);
+                CUDA_CHECK(cudaMemcpyAsync(sc.newent.get(), (to_big ? rk_cur : rk2_cur) + before, (size_t)nnew * 8, cudaMemcpyDeviceToDevice, st));
+            }
             if (to_big) {
                 if (r2[1] > rcap) { give_up_sparse = true; return false; }
                 C.R = r2[1];
@@ -1162,8 +1313,15 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 radix_sort_pairs(rk_cur, rk_alt, rv_cur, rv_alt, C.R, 0, 32 + key_bits, sc.sort, st);
                 C.rk = rk_cur;
             }
-            const uint32_t fb = r2[0] / BL;
-            if (fb < pending_fb) pending_fb = fb;
+            if (track_now) {
+                // following single changes: only the blocks whose probes can see one of the new entries (the block that
+                // asked for them kept its dirty flag)
+                dirty_from_new_entries_kernel<<<ceil_div_u(nnew, 256), 256, 0, st>>>(C, sc.newent.get(), nnew, (uint32_t)table_entries);
+                KERNEL_CHECK();
+            } else {
+                const uint32_t fb = r2[0] / BL;     // every block from the first request on is parsed again
+                if (fb < pending_fb) pending_fb = fb;
+            }
             return true;
         };
         const uint64_t stop = a1 < n_cut ? a1 : n_cut;
@@ -1271,6 +1429,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                             (unsigned long long)round, d[0], nb, d[1]);
                 }
                 CUDA_CHECK(cudaMemcpyAsync(sc.notins_prev.get(), sc.notins.get(), nwords * 4, cudaMemcpyDeviceToDevice, st));
+                track_now = track;
                 const bool repaired = sparse && repair();
                 if (give_up_sparse) break;
                 if (!chg && !repaired) { converged = true; break; }

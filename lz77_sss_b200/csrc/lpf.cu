@@ -172,6 +172,132 @@ __global__ void all_candidates_fused_kernel(const uint8_t* __restrict__ T, const
     p_lcel[i] = pll; n_lcel[i] = nll;
 }
 
+// The same computation with every global load bounds-checked by hand (compute-sanitizer is not available on the pool): the
+// first load outside its array is recorded as {array code, index, limit, thread} instead of being executed.
+// LZ77SSS_FUSED_CANDIDATES=2 runs it in front of the normal kernels and prints the record.
+struct chk_rec { unsigned long long code, index, limit, thread; };
+__device__ __forceinline__ bool chk_fail(chk_rec* rec, unsigned long long code, unsigned long long idx, unsigned long long lim,
+                                         unsigned long long thread) {
+    if (idx < lim) return false;
+    if (atomicCAS(&rec->code, 0ull, code) == 0ull) { rec->index = idx; rec->limit = lim; rec->thread = thread; }
+    return true;
+}
+template <typename pos_t>
+__global__ void all_candidates_checked_kernel(const pos_t* __restrict__ S, uint64_t s, const uint32_t* __restrict__ SAx,
+                                              uint32_t flip, const uint32_t* __restrict__ ISA, const pos_t* __restrict__ LCP,
+                                              const uint32_t* __restrict__ tab, const pos_t* __restrict__ lcp_tab, uint32_t nblk,
+                                              int levels, chk_rec* __restrict__ rec) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s) return;
+    const uint64_t tabn = (uint64_t)levels * nblk;
+#define LD(arr, idx, lim, code, dflt) (chk_fail(rec, code, (idx), (lim), i) ? (dflt) : arr[(idx)])
+    auto brm_u32 = [&](uint64_t lo, uint64_t hi) -> uint32_t {        // blk_range_min over tab
+        if (hi < lo) { chk_fail(rec, 90, lo, hi, i); return 0xFFFFFFFFu; }
+        const int l = 63 - __clzll((long long)(hi - lo + 1));
+        const uint32_t x = LD(tab, (uint64_t)l * nblk + lo, tabn, 1, 0xFFFFFFFFu);
+        const uint32_t y = LD(tab, (uint64_t)l * nblk + hi + 1 - (1ull << l), tabn, 2, 0xFFFFFFFFu);
+        return y < x ? y : x;
+    };
+    auto brm_pos = [&](uint64_t lo, uint64_t hi) -> pos_t {           // blk_range_min over lcp_tab
+        if (hi < lo) { chk_fail(rec, 91, lo, hi, i); return (pos_t)0; }
+        const int l = 63 - __clzll((long long)(hi - lo + 1));
+        const pos_t x = LD(lcp_tab, (uint64_t)l * nblk + lo, tabn, 3, (pos_t)0);
+        const pos_t y = LD(lcp_tab, (uint64_t)l * nblk + hi + 1 - (1ull << l), tabn, 4, (pos_t)0);
+        return y < x ? y : x;
+    };
+    auto rmin = [&](uint64_t lo, uint64_t hi) -> pos_t {              // range_min over LCP
+        if (hi < lo) { chk_fail(rec, 92, lo, hi, i); return (pos_t)0; }
+        const uint64_t bl = lo / RMQ_BLK, bh = hi / RMQ_BLK;
+        pos_t m = LD(LCP, lo, s, 5, (pos_t)0);
+        if (bl == bh) {
+            for (uint64_t k = lo + 1; k <= hi; k++) { const pos_t x = LD(LCP, k, s, 6, (pos_t)0); m = x < m ? x : m; }
+            return m;
+        }
+        for (uint64_t k = lo + 1; k < (bl + 1) * RMQ_BLK; k++) { const pos_t x = LD(LCP, k, s, 7, (pos_t)0); m = x < m ? x : m; }
+        for (uint64_t k = bh * RMQ_BLK; k <= hi; k++) { const pos_t x = LD(LCP, k, s, 8, (pos_t)0); m = x < m ? x : m; }
+        if (bl + 1 < bh) { const pos_t x = brm_pos(bl + 1, bh - 1); m = x < m ? x : m; }
+        return m;
+    };
+    const uint64_t r = LD(ISA, i, s, 10, 0u);
+    if (chk_fail(rec, 11, r, s, i)) return;
+    const uint32_t v = (uint32_t)i ^ flip;
+    // prev_smaller
+    uint32_t pr = NONE32;
+    {
+        const uint64_t b = r / RMQ_BLK;
+        bool found = false;
+        for (uint64_t j = r; j > b * RMQ_BLK && !found;) {
+            j--;
+            if (LD(SAx, j, s, 12, 0xFFFFFFFFu) < v) { pr = (uint32_t)j; found = true; }
+        }
+        if (!found && b > 0) {
+            uint64_t e = b, w = 1, lo = 0;
+            bool none = false;
+            while (true) {
+                lo = e >= w ? e - w : 0;
+                if (brm_u32(lo, e - 1) < v) break;
+                if (lo == 0) { none = true; break; }
+                w *= 2;
+            }
+            if (!none) {
+                uint64_t hi = e - 1;
+                while (lo < hi) {
+                    const uint64_t mid = (lo + hi + 1) / 2;
+                    if (brm_u32(mid, hi) < v) lo = mid;
+                    else hi = mid - 1;
+                }
+                for (uint64_t j = (lo + 1) * RMQ_BLK; j > lo * RMQ_BLK && !found;) {
+                    j--;
+                    if (LD(SAx, j, s, 13, 0xFFFFFFFFu) < v) { pr = (uint32_t)j; found = true; }
+                }
+                if (!found) chk_fail(rec, 93, lo, 0, i);          // "unreachable"
+            }
+        }
+    }
+    // next_smaller
+    uint32_t nr = NONE32;
+    {
+        const uint64_t b = r / RMQ_BLK;
+        const uint64_t bend = min(s, (b + 1) * RMQ_BLK);
+        bool found = false;
+        for (uint64_t j = r + 1; j < bend && !found; j++)
+            if (LD(SAx, j, s, 14, 0xFFFFFFFFu) < v) { nr = (uint32_t)j; found = true; }
+        if (!found && b + 1 < nblk) {
+            uint64_t e = b + 1, w = 1, hi = 0;
+            bool none = false;
+            while (true) {
+                hi = e + w - 1 < nblk ? e + w - 1 : nblk - 1;
+                if (brm_u32(e, hi) < v) break;
+                if (hi == (uint64_t)nblk - 1) { none = true; break; }
+                w *= 2;
+            }
+            if (!none) {
+                uint64_t lo = e;
+                while (lo < hi) {
+                    const uint64_t mid = (lo + hi) / 2;
+                    if (brm_u32(lo, mid) < v) hi = mid;
+                    else lo = mid + 1;
+                }
+                const uint64_t be = min(s, (lo + 1) * RMQ_BLK);
+                for (uint64_t j = lo * RMQ_BLK; j < be && !found; j++)
+                    if (LD(SAx, j, s, 15, 0xFFFFFFFFu) < v) { nr = (uint32_t)j; found = true; }
+                if (!found) chk_fail(rec, 94, lo, 0, i);
+            }
+        }
+    }
+    if (pr != NONE32) {
+        const uint32_t pi = LD(SAx, (uint64_t)pr, s, 16, 0u) ^ flip;
+        (void)rmin((uint64_t)pr + 1, r);
+        (void)LD(S, (uint64_t)pi, s, 17, (pos_t)0);
+    }
+    if (nr != NONE32) {
+        const uint32_t ni = LD(SAx, (uint64_t)nr, s, 18, 0u) ^ flip;
+        (void)rmin(r + 1, (uint64_t)nr);
+        (void)LD(S, (uint64_t)ni, s, 19, (pos_t)0);
+    }
+#undef LD
+}
+
 __global__ void flip_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t s) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < s) out[i] = ~in[i];
@@ -314,6 +440,21 @@ void all_candidates(const uint8_t* T, uint64_t n, const pos_t* S, uint64_t s, bo
         }
         SAx = ls.sa_flip;
         tab = ls.saf_blkmin;
+    }
+    static const bool checked = getenv("LZ77SSS_FUSED_CANDIDATES") && getenv("LZ77SSS_FUSED_CANDIDATES")[0] == '2';
+    if (checked) {
+        dbuf<chk_rec> rec;
+        rec.reserve(1);
+        CUDA_CHECK(cudaMemsetAsync(rec.get(), 0, sizeof(chk_rec), st));
+        all_candidates_checked_kernel<pos_t><<<ceil_div_u(s, 128), 128, 0, st>>>(S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP,
+                                                                               tab, ls.lcp_blkmin, ls.nblk, ls.sp_levels, rec);
+        KERNEL_CHECK();
+        chk_rec h_rec;
+        CUDA_CHECK(cudaMemcpyAsync(&h_rec, rec.get(), sizeof h_rec, cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        fprintf(stderr, "all_candidates check (|S| = %llu, nblk = %u, levels = %d, greater = %d): %s code %llu index %llu limit %llu thread %llu\n",
+                (unsigned long long)s, ls.nblk, ls.sp_levels, (int)greater, h_rec.code ? "FIRST BAD LOAD" : "all loads in range",
+                h_rec.code, h_rec.index, h_rec.limit, h_rec.thread);
     }
     static const bool fused = getenv("LZ77SSS_FUSED_CANDIDATES") && getenv("LZ77SSS_FUSED_CANDIDATES")[0] == '1';
     if (fused) {
