@@ -1429,15 +1429,19 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                             (unsigned long long)round, d[0], nb, d[1]);
                 }
                 CUDA_CHECK(cudaMemcpyAsync(sc.notins_prev.get(), sc.notins.get(), nwords * 4, cudaMemcpyDeviceToDevice, st));
-                track_now = track;
+                uint32_t d[2] = {0, 0};                 // blocks whose trace or exit changed, the first of them
+                if (!track) CUDA_CHECK(cudaMemcpy(d, sc.changed.get() + 3, 8, cudaMemcpyDeviceToHost));
+                // the next round follows single changes if this one did, or if few blocks changed (decided before the
+                // repair step, which marks the blocks that see its new entries only for a round that follows changes)
+                track_now = track || (uint64_t)d[0] * track_div <= nb;
+                if (!track && track_now && C.bmin > 0)      // the blocks in front of the last round's first change were not
+                    CUDA_CHECK(cudaMemsetAsync(sc.dirty.get(), 0, C.bmin, st));   // parsed and need not be: drop their flags
                 const bool repaired = sparse && repair();
                 if (give_up_sparse) break;
                 if (!chg && !repaired) { converged = true; break; }
                 if (!track) {
-                    uint32_t d[2];                      // blocks whose trace or exit changed, the first of them
-                    CUDA_CHECK(cudaMemcpy(d, sc.changed.get() + 3, 8, cudaMemcpyDeviceToHost));
-                    if ((uint64_t)d[0] * track_div <= nb) {    // few changes left: follow them (blocks in front of the old
-                        track = true;                   // bmin are still flagged and are parsed once more)
+                    if ((uint64_t)d[0] * track_div <= nb) {    // few changes left: follow them
+                        track = true;
                         C.bmin = 0;
                     } else {
                         C.bmin = d[1];

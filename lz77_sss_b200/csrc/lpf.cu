@@ -140,7 +140,7 @@ __global__ void all_candidates_kernel(const uint8_t* __restrict__ T, const pos_t
 
 // Both sides in one thread: the variant that faulted (kept behind LZ77SSS_FUSED_CANDIDATES=1 so that the fault can be
 // reproduced under compute-sanitizer).
-template <typename pos_t>
+template <typename pos_t, bool CLAMP>
 __global__ void all_candidates_fused_kernel(const uint8_t* __restrict__ T, const pos_t* __restrict__ S, uint64_t s,
                                             const uint32_t* __restrict__ SAx, uint32_t flip, const uint32_t* __restrict__ ISA,
                                             const pos_t* __restrict__ LCP, const uint32_t* __restrict__ tab,
@@ -157,15 +157,17 @@ __global__ void all_candidates_fused_kernel(const uint8_t* __restrict__ T, const
     const uint32_t nr = next_smaller(SAx, tab, nblk, s, r, v);
     uint32_t pi = NONE32, ni = NONE32;
     pos_t pl = 0, nl = 0, pll = 0, nll = 0;
+    // CLAMP: the guarded loads get an index that is valid even when the guard is false, so that a load the compiler
+    // moved in front of its guard cannot fault (experiment for DESIGN.md §9)
     if (pr != NONE32) {
-        pi = SAx[pr] ^ flip;
+        pi = SAx[CLAMP ? min((uint64_t)pr, s - 1) : (uint64_t)pr] ^ flip;
         pl = range_min(LCP, lcp_tab, nblk, (uint64_t)pr + 1, r);
-        pll = (pos_t)capped_left(T, (uint64_t)S[pi], pos, lcap);
+        pll = (pos_t)capped_left(T, (uint64_t)S[CLAMP ? min((uint64_t)pi, s - 1) : (uint64_t)pi], pos, lcap);
     }
     if (nr != NONE32) {
-        ni = SAx[nr] ^ flip;
+        ni = SAx[CLAMP ? min((uint64_t)nr, s - 1) : (uint64_t)nr] ^ flip;
         nl = range_min(LCP, lcp_tab, nblk, r + 1, (uint64_t)nr);
-        nll = (pos_t)capped_left(T, (uint64_t)S[ni], pos, lcap);
+        nll = (pos_t)capped_left(T, (uint64_t)S[CLAMP ? min((uint64_t)ni, s - 1) : (uint64_t)ni], pos, lcap);
     }
     p_idx[i] = pi; n_idx[i] = ni;
     p_lce[i] = pl; n_lce[i] = nl;
@@ -456,9 +458,10 @@ void all_candidates(const uint8_t* T, uint64_t n, const pos_t* S, uint64_t s, bo
                 (unsigned long long)s, ls.nblk, ls.sp_levels, (int)greater, h_rec.code ? "FIRST BAD LOAD" : "all loads in range",
                 h_rec.code, h_rec.index, h_rec.limit, h_rec.thread);
     }
-    static const bool fused = getenv("LZ77SSS_FUSED_CANDIDATES") && getenv("LZ77SSS_FUSED_CANDIDATES")[0] == '1';
-    if (fused) {
-        all_candidates_fused_kernel<pos_t><<<ceil_div_u(s, 128), 128, 0, st>>>(
+    static const char fused = getenv("LZ77SSS_FUSED_CANDIDATES") ? getenv("LZ77SSS_FUSED_CANDIDATES")[0] : '0';
+    if (fused == '1' || fused == '3') {
+        auto kern = fused == '1' ? all_candidates_fused_kernel<pos_t, false> : all_candidates_fused_kernel<pos_t, true>;
+        kern<<<ceil_div_u(s, 128), 128, 0, st>>>(
             T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.psv_idx,
             ls.nsv_idx, ls.psv_lce, ls.nsv_lce, ls.psv_lcel, ls.nsv_lcel);
         KERNEL_CHECK();
