@@ -328,7 +328,10 @@ void all_chain(lz77sss_handle* h, pipeline<pos_t>& P, const uint8_t* d_text, boo
     std::vector<pending> pend;
     std::vector<uint64_t> q;          // qi plane, then qj plane
     std::vector<size_t> first_new(p);
-    for (uint32_t i_p = 0; i_p < p; i_p++) {
+    // the logical blocks are independent: one host thread each; their pending left-extension queries are collected per block
+    std::vector<std::vector<pending>> pend_b(p);
+    std::vector<std::vector<uint64_t>> q_b(p);
+    run_blocks(p, [&](uint32_t i_p) {
         uint64_t b, e;
         if (lnf) {
             b = i_p == p - 1 ? 0 : n - (uint64_t)(i_p + 1) * (n / p);
@@ -340,6 +343,8 @@ void all_chain(lz77sss_handle* h, pipeline<pos_t>& P, const uint8_t* d_text, boo
         const uint64_t i_min = std::lower_bound(S, S + s, (pos_t)b) - S;
         const uint64_t i_max = e > (uint64_t)std::numeric_limits<pos_t>::max() ? s : std::lower_bound(S, S + s, (pos_t)e) - S;
         auto& out = h->LPF[i_p];
+        auto& pend = pend_b[i_p];
+        auto& q = q_b[i_p];
         first_new[i_p] = out.size();
         uint64_t lst_end[2] = {n, n}, lst_off[2] = {0, 0};
         for (uint64_t i = i_min; i < i_max; i++) {
@@ -369,6 +374,10 @@ void all_chain(lz77sss_handle* h, pipeline<pos_t>& P, const uint8_t* d_text, boo
                 }
             }
         }
+    });
+    for (uint32_t i_p = 0; i_p < p; i_p++) {
+        pend.insert(pend.end(), pend_b[i_p].begin(), pend_b[i_p].end());
+        q.insert(q.end(), q_b[i_p].begin(), q_b[i_p].end());
     }
     if (!pend.empty()) {
         const uint64_t nq = pend.size();
@@ -995,7 +1004,7 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
         build_and_fetch(d_text, 1);
         t0 = clk::now();
         all_chain<pos_t>(h, P, d_text, false, opt_mode);
-        for (auto& V : h->LPF) select_phrases(V);
+        run_blocks(h->cfg.num_threads, [&](uint32_t i_p) { select_phrases(h->LPF[i_p]); });
         st.t_chain_ns += ns_since(t0);
     } else {
         build_and_fetch(d_text, 0);

@@ -327,6 +327,18 @@ __global__ void __launch_bounds__(256) bucket_start_kernel(const uint32_t* __res
     }
 }
 
+// rstart[b] = first index of the (sorted) big repair list whose bucket is >= b, for b in [0, nkeys]
+__global__ void __launch_bounds__(256) repair_start_kernel(const uint64_t* __restrict__ rk, uint32_t R, uint32_t nkeys,
+                                                           uint32_t* __restrict__ rstart) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= R) return;
+    const uint32_t cur = (uint32_t)(rk[k] >> 32);
+    const int64_t prev = k ? (int64_t)(uint32_t)(rk[k - 1] >> 32) : -1;
+    for (int64_t b = prev + 1; b <= (int64_t)cur && b <= (int64_t)nkeys; b++) rstart[b] = k;
+    if (k == R - 1)
+        for (uint64_t b = (uint64_t)cur + 1; b <= nkeys; b++) rstart[b] = R;
+}
+
 struct block_state {
     uint64_t i, cur, k;
     uint32_t gap;      // last step before i was a gap step (positions up to i are inserted)
@@ -347,6 +359,7 @@ struct parse_ctx {
     const uint32_t* skip;      // sparse slice: bit = 1: the position has no entries (nullptr: every position has)
     const uint64_t* rk;        // sparse slice: entries added after the sort (repair list), (bucket << 32 | entry id) ascending
     uint32_t R;                // number of entries in the repair list
+    const uint32_t* rstart;    // bucket b of the big repair list = rk[rstart[b] .. rstart[b+1])
     const uint64_t* rk2;       // second, small repair list: what later rounds add (re-sorted alone; merged when it grows)
     uint32_t R2;
     uint32_t* req;             // sparse slice: req[0] = number of repair requests of this round, then (beg, end) pairs
@@ -439,12 +452,14 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
             if (!R) continue;
             const uint64_t key = ((uint64_t)b << 32) | e;
             uint32_t rl = 0, rh = R;
+            if (!which) { rl = C.rstart[b]; rh = C.rstart[b + 1]; }      // the big list has its bucket starts
+            const uint32_t rlo = rl;
             while (rl < rh) {
                 const uint32_t mid = (rl + rh) >> 1;
                 if (rk[mid] < key) rl = mid + 1;
                 else rh = mid;
             }
-            while (rl > 0) {
+            while (rl > rlo) {
                 rl--;
                 const uint64_t v = rk[rl];
                 if ((uint32_t)(v >> 32) != b) break;
@@ -724,6 +739,7 @@ __global__ void __launch_bounds__(256) dirty_from_bitmap_kernel(const parse_ctx 
                 const uint32_t b = C.tkey[e];
                 const uint64_t key = ((uint64_t)b << 32) | e;
                 uint32_t rl = 0, rh = R;
+                if (!which) { rl = C.rstart[b]; rh = C.rstart[b + 1]; }
                 while (rl < rh) {
                     const uint32_t mid = (rl + rh) >> 1;
                     if (rk[mid] <= key) rl = mid + 1;
@@ -903,6 +919,7 @@ __global__ void __launch_bounds__(256) dirty_from_new_entries_kernel(const parse
         const uint32_t R = which ? C.R2 : C.R;
         if (!R) continue;
         uint32_t rl = 0, rh = R;
+        if (!which) { rl = C.rstart[b]; rh = C.rstart[b + 1]; }
         while (rl < rh) {
             const uint32_t mid = (rl + rh) >> 1;
             if (rk[mid] <= key) rl = mid + 1;
@@ -1231,7 +1248,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         C.Hc = reinterpret_cast<const uint64_t*>(sc.Hc.get());
         C.notins = sc.notins;
         C.skip = sparse ? sc.skip.get() : nullptr;
-        C.rk = nullptr; C.R = 0; C.rk2 = nullptr; C.R2 = 0; C.req = nullptr; C.req_cap = 0;
+        C.rk = nullptr; C.R = 0; C.rk2 = nullptr; C.R2 = 0; C.req = nullptr; C.req_cap = 0; C.rstart = nullptr;
         uint32_t rcap = 0, rcap2 = 0;
         uint64_t *rk_cur = nullptr, *rk_alt = nullptr, *rk2_cur = nullptr, *rk2_alt = nullptr;
         uint32_t *rv_cur = nullptr, *rv_alt = nullptr;
@@ -1243,6 +1260,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             rcap2 = std::max<uint32_t>(1u << 20, rcap / 2);
             sc.rk0.reserve(rcap + 8); sc.rk1.reserve(rcap + 8); sc.rv0.reserve(rcap + 8); sc.rv1.reserve(rcap + 8);
             sc.rkb0.reserve(rcap2 + 8); sc.rkb1.reserve(rcap2 + 8);
+            sc.rstart.reserve(table_entries + 4);
+            C.rstart = sc.rstart;
             rk_cur = sc.rk0; rk_alt = sc.rk1; rv_cur = sc.rv0; rv_alt = sc.rv1; rk2_cur = sc.rkb0; rk2_alt = sc.rkb1;
             CUDA_CHECK(cudaMemsetAsync(sc.req.get(), 0, 8, st));
         }
@@ -1295,6 +1314,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 C.R = r2[1];
                 radix_sort_pairs(rk_cur, rk_alt, rv_cur, rv_alt, C.R, 0, 32 + key_bits, sc.sort, st);
                 C.rk = rk_cur;
+                repair_start_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(rk_cur, C.R, (uint32_t)table_entries + 1, sc.rstart);
+                KERNEL_CHECK();
             } else if (r2[1] <= rcap2) {
                 C.R2 = r2[1];
                 radix_sort_pairs(rk2_cur, rk2_alt, rv_cur, rv_alt, C.R2, 0, 32 + key_bits, sc.sort, st);   // (payload unused)
@@ -1312,6 +1333,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 C.rk2 = nullptr;
                 radix_sort_pairs(rk_cur, rk_alt, rv_cur, rv_alt, C.R, 0, 32 + key_bits, sc.sort, st);
                 C.rk = rk_cur;
+                repair_start_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(rk_cur, C.R, (uint32_t)table_entries + 1, sc.rstart);
+                KERNEL_CHECK();
             }
             if (track_now) {
                 // following single changes: only the blocks whose probes can see one of the new entries (the block that
