@@ -1316,6 +1316,9 @@ int lz77sss_factorize_exact(lz77sss_handle* h, const uint8_t* text, uint64_t n, 
             }
         }
         sect.push_back(n);
+        // the emission buffers of the approximation (a slice's index, traces) are not needed any more; the suffix array
+        // and its sort buffers (28 bytes per text byte) take their place
+        h->gp = gap_parse_scratch();
         t0 = clk::now();
         h->f_src.clear();
         h->f_len.clear();

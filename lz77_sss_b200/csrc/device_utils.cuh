@@ -41,6 +41,37 @@ __device__ __forceinline__ uint64_t warp_lce(const uint8_t* __restrict__ T, uint
     return lim;
 }
 
+// The same for a GROUP of G consecutive lanes of a warp (G = 8, 16 or 32; several groups of one warp work on different
+// queries at the same time).  gmask = the group's lanes, glane = lane index inside the group.  256 bytes per iteration per
+// string whatever G is: a lane compares 256 / G consecutive bytes.
+template <int G>
+__device__ __forceinline__ uint64_t group_lce(const uint8_t* __restrict__ T, uint64_t x, uint64_t y, uint64_t off, uint64_t lim,
+                                              unsigned gmask, unsigned glane) {
+    constexpr int PER = 256 / G;                        // bytes per lane and iteration
+    const unsigned gbase = __ffs(gmask) - 1;
+    while (off < lim) {
+        const uint64_t o0 = off + (uint64_t)PER * glane;
+        uint32_t first = PER;                           // first differing byte of the lane's chunk, PER = none
+#pragma unroll
+        for (int k = PER / 8 - 1; k >= 0; k--) {
+            const uint64_t o = o0 + 8 * k;
+            if (o < lim) {
+                const uint64_t diff = load_u64_unaligned(T + x + o) ^ load_u64_unaligned(T + y + o);
+                if (diff) first = 8 * k + (__ffsll((long long)diff) - 1) / 8;
+            }
+        }
+        const unsigned m = __ballot_sync(gmask, first < (uint32_t)PER);
+        if (m) {
+            const int fl = __ffs(m) - 1;                // warp lane of the first group lane with a difference
+            const uint32_t f = __shfl_sync(gmask, first, fl);
+            const uint64_t r = off + (uint64_t)PER * (fl - gbase) + f;
+            return r < lim ? r : lim;
+        }
+        off += 256;
+    }
+    return lim;
+}
+
 // single-thread LCE (8 bytes per step)
 __device__ __forceinline__ uint64_t thread_lce(const uint8_t* __restrict__ T, uint64_t x, uint64_t y, uint64_t lim) {
     uint64_t k = 0;

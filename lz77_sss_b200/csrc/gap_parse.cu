@@ -395,30 +395,29 @@ __device__ __forceinline__ void file_request(const parse_ctx& C, uint64_t s, uin
         C.req[3 + 2 * k] = (uint32_t)(e - C.a0);
     }
 }
-// does any position of [s, e) (text positions inside the slice) lack entries?  All 32 lanes.
-__device__ __forceinline__ bool warp_any_skip(const parse_ctx& C, uint64_t s, uint64_t e) {
+// does any position of [s, e) (text positions inside the slice) lack entries?  All lanes of the group.
+template <int G>
+__device__ __forceinline__ bool group_any_skip(const parse_ctx& C, uint64_t s, uint64_t e, unsigned gmask, unsigned glane) {
     if (e > C.a1) e = C.a1;
     if (s >= e) return false;
-    const unsigned lane = threadIdx.x & 31;
     const uint64_t rs = s - C.a0, re = e - C.a0;
     const uint64_t w0 = rs >> 5, w1 = (re - 1) >> 5;
     bool any = false;
-    for (uint64_t w = w0 + lane; w <= w1 && !any; w += 32) {
+    for (uint64_t w = w0 + glane; w <= w1 && !any; w += G) {
         uint32_t m = 0xFFFFFFFFu;
         if (w == w0) m &= 0xFFFFFFFFu << (rs & 31);
         if (w == w1) m &= 0xFFFFFFFFu >> (31 - ((re - 1) & 31));
         any = (C.skip[w] & m) != 0;
     }
-    return __any_sync(0xffffffffu, any);
+    return __ballot_sync(gmask, any) != 0;
 }
 
-// longest_prev_occ (factorize/common.cpp:33-61) at position i, all 32 lanes; lanes 0..4 own patterns 4..0.
+// longest_prev_occ (factorize/common.cpp:33-61) at position i, all lanes of the group; its lanes 0..4 own patterns 4..0.
 // "H[b] when i is probed" = the largest inserted position among the entries of bucket b in front of the probe's own
 // entry: the bucket's list of the sorted index and, on a sparse slice, of the repair list, else the carried table.
-template <typename pos_t>
+template <typename pos_t, int G>
 __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>& V, uint64_t i, uint64_t& f_src,
-                                      uint64_t& f_len, bool& bad) {
-    const unsigned lane = threadIdx.x & 31;
+                                      uint64_t& f_len, bool& bad, unsigned gmask, unsigned lane) {
     const uint32_t rel = (uint32_t)(i - C.a0);
     if (C.skip && ((C.skip[rel >> 5] >> (rel & 31)) & 1u)) {       // a wrong speculation, or the position a gap factor that
         bad = true;                                                 // ran over whole phrases lands on: ask for its entries
@@ -478,21 +477,24 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
     }
     const uint8_t ci = V.T[i];
     const bool valid = lane < 5 && occ != NONE64 && occ < i && V.T[occ] == ci;
-    const unsigned m = __ballot_sync(0xffffffffu, valid);
+    const unsigned m = __ballot_sync(gmask, valid);
     if (!m) {
         f_src = ci;
         f_len = 0;
         return;
     }
-    const int win = __ffs(m) - 1;
-    f_src = __shfl_sync(0xffffffffu, occ, win);
-    f_len = warp_lce_r(V, f_src, i);
+    const int win = __ffs(m) - 1;                       // (a warp lane: the group's lowest lane with a match)
+    f_src = __shfl_sync(gmask, occ, win);
+    f_len = group_lce_r<pos_t, G>(V, f_src, i, gmask, lane);
 }
 
-template <typename pos_t>
-__global__ void __launch_bounds__(128, 16) parse_kernel(const parse_ctx C, const lce_view<pos_t> V) {
-    const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    const unsigned lane = threadIdx.x & 31;
+// G lanes of a warp parse one block (G = 32: a warp per block; G = 8: four blocks per warp).  The parse is bound by the
+// latency of its dependent loads, so the number of blocks in flight per SM is what sets its throughput.
+template <typename pos_t, int G>
+__global__ void __launch_bounds__(128, G == 32 ? 16 : 12) parse_kernel(const parse_ctx C, const lce_view<pos_t> V) {
+    const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / G);
+    const unsigned lane = threadIdx.x & (G - 1);                       // lane inside the group
+    const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (threadIdx.x & 31 & ~(G - 1)));
     if (b >= C.nb || b < C.bmin || !C.marked[b] || !C.dirty[b]) return;
     const block_state st = C.entry[b];
     uint64_t i = st.i, cur = st.cur, k = st.k;
@@ -510,7 +512,7 @@ __global__ void __launch_bounds__(128, 16) parse_kernel(const parse_ctx C, const
         uint32_t kind;
         const uint64_t at = i;
         if (i < pb) {   // gap step (greedy.cpp:60-97, greedy_naive.cpp:56-67)
-            probe<pos_t>(C, V, i, o_src, o_len, bad);
+            probe<pos_t, G>(C, V, i, o_src, o_len, bad, gmask, lane);
             if (C.naive && o_len > pb - i) o_len = pb - i;
             uint64_t i2 = i + (o_len ? o_len : 1);
             if (i2 > pb) {
@@ -520,7 +522,7 @@ __global__ void __launch_bounds__(128, 16) parse_kernel(const parse_ctx C, const
                 } else {
                     // the positions of the phrases the factor ran over get inserted, and the position it lands on is probed
                     // if it lies inside a phrase (greedy.cpp:68-77,111-117): a sparse slice may lack their entries
-                    if (C.skip && warp_any_skip(C, pb, i2 + 1)) {
+                    if (C.skip && group_any_skip<G>(C, pb, i2 + 1, gmask, lane)) {
                         bad = true;
                         if (lane == 0) file_request(C, pb, i2 + 1);
                     }
@@ -538,7 +540,7 @@ __global__ void __launch_bounds__(128, 16) parse_kernel(const parse_ctx C, const
             kind = KIND_PHR;
             if (cur == i) {
                 uint64_t fs, fl;
-                probe<pos_t>(C, V, i, fs, fl, bad);
+                probe<pos_t, G>(C, V, i, fs, fl, bad, gmask, lane);
                 cur = i + 1;
                 kind |= KIND_PROBED;
                 if (C.naive && k + 1 < C.m) {            // greedy_naive.cpp:82-85: clipped to the next phrase start
@@ -777,6 +779,30 @@ __global__ void dirty_from_table_kernel(const parse_ctx C, const unsigned long l
         const bool oi = !not_inserted(old_bm, q), ni = !not_inserted(C.notins, q);
         if (oi || ni) C.dirty[q / C.BL] = 1;
         if (oi && ni) break;
+    }
+    for (int which = 0; which < 2; which++) {            // the bucket's entries in the repair lists, from their start
+        const uint64_t* __restrict__ rk = which ? C.rk2 : C.rk;
+        const uint32_t R = which ? C.R2 : C.R;
+        if (!R) continue;
+        uint32_t rl = 0, rh = R;
+        if (!which) {
+            rl = C.rstart[b];
+        } else {
+            const uint64_t key = (uint64_t)b << 32;
+            while (rl < rh) {
+                const uint32_t mid = (rl + rh) >> 1;
+                if (rk[mid] < key) rl = mid + 1;
+                else rh = mid;
+            }
+        }
+        for (; rl < R; rl++) {
+            const uint64_t v = rk[rl];
+            if ((uint32_t)(v >> 32) != b) break;
+            const uint32_t q = (uint32_t)v / 5u;
+            const bool oi = !not_inserted(old_bm, q), ni = !not_inserted(C.notins, q);
+            if (oi || ni) C.dirty[q / C.BL] = 1;
+            if (oi && ni) break;
+        }
     }
 }
 
@@ -1101,6 +1127,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         CUDA_CHECK(cudaMemsetAsync(sc.Hc.get(), 0, table_entries * 8, st));
     sc.changed.reserve(8);
     const bool dbg_rounds = getenv("LZ77SSS_DEBUG_ROUNDS") != nullptr;
+    // lanes per parsed block (LZ77SSS_PARSE_GROUP = 8, 16 or 32)
+    const int parse_group = getenv("LZ77SSS_PARSE_GROUP") ? atoi(getenv("LZ77SSS_PARSE_GROUP")) : 8;
     const uint64_t track_div = getenv("LZ77SSS_TRACK_DIV") ? strtoull(getenv("LZ77SSS_TRACK_DIV"), nullptr, 10) : 64;
     sc.slice_exit.reserve(sizeof(block_state));
 
@@ -1117,6 +1145,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         std::swap(K.entry, sc.entry); std::swap(K.exit_, sc.exit_); std::swap(K.marked, sc.marked); std::swap(K.ovr, sc.ovr);
         std::swap(K.dirty, sc.dirty); std::swap(K.notins_prev, sc.notins_prev); std::swap(K.Hc_prev, sc.Hc_prev);
         std::swap(K.tr_cnt, sc.tr_cnt); std::swap(K.tr_pos, sc.tr_pos); std::swap(K.tr_src, sc.tr_src); std::swap(K.tr_len, sc.tr_len);
+        std::swap(K.skip, sc.skip); std::swap(K.rstart, sc.rstart);
+        std::swap(K.rk0, sc.rk0); std::swap(K.rk1, sc.rk1); std::swap(K.rkb0, sc.rkb0); std::swap(K.rkb1, sc.rkb1);
     };
 
     size_t slice_no = 0;
@@ -1131,8 +1161,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             swap_keep(*K);
         }
         struct swap_back { slice_keep* K; decltype(swap_keep)& f; ~swap_back() { if (K) f(*K); } } guard{K, swap_keep};
-        const bool have_sorted = K && K->sorted;
-        const bool have_parse = K && K->parsed;
+        bool have_sorted = K && K->sorted;
+        bool have_parse = K && K->parsed;
         const uint64_t cnt = a1 - a0;
         const uint32_t BL = block_len;
         const uint32_t nb = (uint32_t)((cnt + BL - 1) / BL);
@@ -1147,10 +1177,12 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         // phrases that overlap the slice (the sentinel is not one of them)
         const uint64_t k0 = std::upper_bound(h_ml + m, h_ml + m + (m - 1), a0) - (h_ml + m);
         const uint64_t k1 = std::lower_bound(h_ml, h_ml + (m - 1), a1) - h_ml;
-      for (int attempt = (naive || !sparse_ok || retain) ? 1 : 0; attempt < 2; attempt++) {
+      for (int attempt = have_sorted ? (K->sparse ? 0 : 1) : (naive || !sparse_ok) ? 1 : 0; attempt < 2; attempt++) {
         bool sparse = attempt == 0;
         uint64_t E = 5 * cnt;
-        if (sparse) {
+        if (sparse && have_sorted) {
+            E = K->E;                                 // a retained sparse slice: its skip bitmap, index and repair lists stand
+        } else if (sparse) {
             sc.skip.reserve(nwords);
             sc.tile_off.reserve(ntiles + 2);
             CUDA_CHECK(cudaMemsetAsync(sc.skip.get(), 0, nwords * 4, st));
@@ -1203,7 +1235,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         bucket_start_kernel<<<ceil_div_u(E, 1024), 256, 0, st>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
         KERNEL_CHECK();
         }
-        if (K) { K->sorted = true; K->vals_in_v0 = vals == sc.v0.get(); }
+        if (K) { K->sorted = true; K->vals_in_v0 = vals == sc.v0.get(); K->sparse = sparse; K->E = E; K->R = K->R2 = 0; }
         }
         if (index_only) {
             // speculative table of this range: last position per bucket among the positions that the phrase list
@@ -1263,6 +1295,13 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             sc.rstart.reserve(table_entries + 4);
             C.rstart = sc.rstart;
             rk_cur = sc.rk0; rk_alt = sc.rk1; rv_cur = sc.rv0; rv_alt = sc.rv1; rk2_cur = sc.rkb0; rk2_alt = sc.rkb1;
+            if (have_sorted) {                        // the repair lists of the slice's last parse
+                if (!K->rk_in_0) std::swap(rk_cur, rk_alt);
+                if (!K->rk2_in_0) std::swap(rk2_cur, rk2_alt);
+                C.R = K->R; C.R2 = K->R2;
+                C.rk = C.R ? rk_cur : nullptr;
+                C.rk2 = C.R2 ? rk2_cur : nullptr;
+            }
             CUDA_CHECK(cudaMemsetAsync(sc.req.get(), 0, 8, st));
         }
         bool give_up_sparse = false, track_now = false;
@@ -1278,6 +1317,11 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         C.changed = sc.changed;
         block_state* d_exit = reinterpret_cast<block_state*>(sc.slice_exit.get());
         const unsigned gw = ceil_div_u((uint64_t)nb * 32, 128);
+        auto launch_parse = [&](const parse_ctx& CC) {
+            if (parse_group == 8) parse_kernel<pos_t, 8><<<ceil_div_u((uint64_t)nb * 8, 128), 128, 0, st>>>(CC, V);
+            else if (parse_group == 16) parse_kernel<pos_t, 16><<<ceil_div_u((uint64_t)nb * 16, 128), 128, 0, st>>>(CC, V);
+            else parse_kernel<pos_t, 32><<<gw, 128, 0, st>>>(CC, V);
+        };
 
         // sparse slice, after a parse round: hash the requested positions into the repair list and sort it
         auto repair = [&]() -> bool {               // true: entries were added
@@ -1369,7 +1413,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 KERNEL_CHECK();
             }
             PROF_BEGIN(st);
-            parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
+            launch_parse(C);
             KERNEL_CHECK();
             PROF_END(st, "parse_kernel (block-speculative greedy parse, latency-bound)", 0);
             sc.rounds++;
@@ -1377,6 +1421,14 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
           }
             if (K) K->parsed = true;
             bool track = have_parse;    // follow single changes (resumed slices from the start, fresh ones once few are left)
+            if (sparse && have_parse && first.gap && first.i > a0) {
+                // resumed sparse slice whose entry state says that a gap factor reaches into it: those positions are
+                // inserted and need entries (a fresh slice clears their skip bits before it hashes)
+                const uint32_t rq[4] = {1u, 0u, 0u, (uint32_t)((first.i < a1 ? first.i : a1) - a0)};
+                CUDA_CHECK(cudaMemcpyAsync(sc.req.get(), rq, sizeof rq, cudaMemcpyHostToDevice, st));
+                track_now = true;
+                repair();
+            }
             for (uint64_t round = 1; round <= (uint64_t)nb + 4; round++) {
                 if (track) CUDA_CHECK(cudaMemcpyAsync(sc.marked_prev.get(), sc.marked.get(), nb, cudaMemcpyDeviceToDevice, st));
                 {
@@ -1433,7 +1485,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 3, 0, 4, st));
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 4, 0xFF, 4, st));
                 PROF_BEGIN(st);
-                parse_kernel<pos_t><<<gw, 128, 0, st>>>(C, V);
+                launch_parse(C);
                 KERNEL_CHECK();
                 PROF_END(st, "parse_kernel (block-speculative greedy parse, latency-bound)", 0);
                 if (g_prof_on && dbg_rounds) {       // per-round view: the same launch once more under its round number
@@ -1473,6 +1525,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             }
             if (give_up_sparse) {                       // the repair list outgrew its bound: index every position
                 sc.sparse_fallbacks++;
+                if (K) K->sorted = K->parsed = false;
+                have_sorted = have_parse = false;
                 continue;
             }
             if (!converged) throw std::runtime_error("gap_parse: the block chain did not reach its fixed point");
@@ -1521,6 +1575,11 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             if (C.R2) {
                 carry_repair_kernel<<<ceil_div_u(C.R2, 256), 256, 0, st>>>(C, C.rk2, C.R2, (uint32_t)table_entries, sc.Hc.get());
                 KERNEL_CHECK();
+            }
+            if (K && sparse) {
+                K->R = C.R; K->R2 = C.R2;
+                K->rk_in_0 = rk_cur == sc.rk0.get();
+                K->rk2_in_0 = rk2_cur == sc.rkb0.get();
             }
             first = ex;
         } else {

@@ -144,4 +144,27 @@ __device__ __forceinline__ uint64_t warp_lce_r(const lce_view<pos_t>& V, uint64_
     return dl + (uint64_t)range_min(V.LCP, V.lcp_tab, V.nblk, a + 1, b);
 }
 
+// warp_lce_r for a group of G lanes (all lanes of the group call it with the same (i, j))
+template <typename pos_t, int G>
+__device__ __forceinline__ uint64_t group_lce_r(const lce_view<pos_t>& V, uint64_t i, uint64_t j, unsigned gmask, unsigned glane) {
+    if (i == j) return V.n - i;
+    const uint64_t l = min(i, j), r = max(i, j);
+    const uint64_t lce_max = V.n - r;
+    const uint64_t local_max = min((uint64_t)3 * V.tau, lce_max);
+    const uint64_t local = group_lce<G>(V.T, l, r, 0, local_max, gmask, glane);
+    if (local < local_max || local == lce_max) return local;
+    auto succ = [&](uint64_t x) -> uint64_t {
+        uint64_t b = x >> V.shift;
+        uint64_t idx = b < V.nb ? V.first[b] : V.s;
+        while (idx < V.s && (uint64_t)V.S[idx] < x) idx++;
+        return idx;
+    };
+    const uint64_t l_ = succ(l), r_ = succ(r);
+    const uint64_t dl = (uint64_t)V.S[l_] - l, dr = (uint64_t)V.S[r_] - r;
+    if (dl != dr) return min(dl, dr) + 2 * (uint64_t)V.tau - 1;
+    uint64_t a = V.ISA[l_], b = V.ISA[r_];
+    if (a > b) { uint64_t t = a; a = b; b = t; }
+    return dl + (uint64_t)range_min(V.LCP, V.lcp_tab, V.nblk, a + 1, b);
+}
+
 }  // namespace lz77sss

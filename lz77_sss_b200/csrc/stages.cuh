@@ -115,6 +115,11 @@ struct slice_keep {
     dbuf<uint8_t> entry, exit_, marked, ovr, dirty;
     dbuf<uint32_t> notins_prev;            // the bitmap the blocks were last parsed under
     dbuf<unsigned long long> Hc_prev;      // the table in front of the slice at its last parse
+    dbuf<uint32_t> skip, rstart;           // sparse slice: positions without entries, bucket starts of the big repair list
+    dbuf<uint64_t> rk0, rk1, rkb0, rkb1;   // sparse slice: the repair lists
+    uint32_t R = 0, R2 = 0;                // their sizes, and which buffer of each ping-pong pair holds them
+    bool rk_in_0 = true, rk2_in_0 = true, sparse = false;
+    uint64_t E = 0;                        // entries of the sorted index
     bool sorted = false, parsed = false, vals_in_v0 = true;
 };
 // sharded run: parse only [beg, end) from the entry state {i, table cursor, phrase index, gap flag} and the table

@@ -80,6 +80,7 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--ref", action="store_true", help="compare the factor stream with the reference build (CPU, minutes)")
     ap.add_argument("--no-decode", action="store_true")
+    ap.add_argument("--exact", action="store_true", help="factorize_exact instead of factorize_approximate (n < 4 GiB)")
     args = ap.parse_args()
     from lz77_sss_b200 import capi
     threads = args.threads or max(1, min(os.cpu_count() or 1, 64))
@@ -98,19 +99,20 @@ def main():
                "phases_ms": {k: v / 1e6 for k, v in phases.items() if k in keep}}
         del rs, rl
     out = {"workload": args.workload, "n_bytes": int(n), "tau": args.tau, "num_threads": threads, "phr_mode": args.phr,
-           "pos_bits": 64 if n > 0xFFFFFFFF else 32, "generate_s": gen_s}
+           "pos_bits": 64 if n > 0xFFFFFFFF else 32, "generate_s": gen_s, "mode": "factorize_exact" if args.exact else "factorize_approximate"}
     F = capi.Factorizer(tau=args.tau, num_threads=threads, gap_bases=bases, phr_mode=phr)
     times = []
     for _ in range(args.steps):
         t0 = time.perf_counter()
-        src, ln = F.factorize(text, cap=min(n // 4, 1 << 28) + 1024)
+        src, ln = (F.factorize_exact if args.exact else F.factorize)(text, cap=min(n // 4, 1 << 28) + 1024)
         times.append(time.perf_counter() - t0)
     st = F.stats()
     F.close()
     out.update(factors=int(src.size), size_sss=int(st["size_sss"]), seconds=min(times), mib_per_s=(n / MIB) / min(times),
                phases_ms={k[2:-3]: st[k] / 1e6 for k in st if k.startswith("t_")},
                index={k: int(st[k]) for k in ("parse_slices", "sparse_slices", "sparse_fallbacks", "repair_entries", "parse_rounds")},
-               kernel_launches=int(st["kernel_launches"]))
+               kernel_launches=int(st["kernel_launches"]),
+               exact={k: int(st[k]) for k in ("exact_doubling_rounds", "exact_parse_rounds")})
     out["factors_starting_beyond_4gib"] = check_factors(text, src, ln)
     out["factors_well_formed"] = True
     if ref:
