@@ -140,7 +140,7 @@ __global__ void all_candidates_kernel(const uint8_t* __restrict__ T, const pos_t
 
 // Both sides in one thread: the variant that faulted (kept behind LZ77SSS_FUSED_CANDIDATES=1 so that the fault can be
 // reproduced under compute-sanitizer).
-template <typename pos_t, bool CLAMP>
+template <typename pos_t, bool CLAMP, int PARTS = 7>
 __global__ void all_candidates_fused_kernel(const uint8_t* __restrict__ T, const pos_t* __restrict__ S, uint64_t s,
                                             const uint32_t* __restrict__ SAx, uint32_t flip, const uint32_t* __restrict__ ISA,
                                             const pos_t* __restrict__ LCP, const uint32_t* __restrict__ tab,
@@ -158,16 +158,17 @@ __global__ void all_candidates_fused_kernel(const uint8_t* __restrict__ T, const
     uint32_t pi = NONE32, ni = NONE32;
     pos_t pl = 0, nl = 0, pll = 0, nll = 0;
     // CLAMP: the guarded loads get an index that is valid even when the guard is false, so that a load the compiler
-    // moved in front of its guard cannot fault (experiment for DESIGN.md §9)
+    // moved in front of its guard cannot fault.  PARTS (bit 0: SAx[q] ^ flip, bit 1: range minimum over LCP, bit 2: S[idx]
+    // and the left extension) leaves parts of the body out.  Both are experiments for DESIGN.md §9.
     if (pr != NONE32) {
-        pi = SAx[CLAMP ? min((uint64_t)pr, s - 1) : (uint64_t)pr] ^ flip;
-        pl = range_min(LCP, lcp_tab, nblk, (uint64_t)pr + 1, r);
-        pll = (pos_t)capped_left(T, (uint64_t)S[CLAMP ? min((uint64_t)pi, s - 1) : (uint64_t)pi], pos, lcap);
+        if (PARTS & 1) pi = SAx[CLAMP ? min((uint64_t)pr, s - 1) : (uint64_t)pr] ^ flip;
+        if (PARTS & 2) pl = range_min(LCP, lcp_tab, nblk, (uint64_t)pr + 1, r);
+        if ((PARTS & 5) == 5) pll = (pos_t)capped_left(T, (uint64_t)S[CLAMP ? min((uint64_t)pi, s - 1) : (uint64_t)pi], pos, lcap);
     }
     if (nr != NONE32) {
-        ni = SAx[CLAMP ? min((uint64_t)nr, s - 1) : (uint64_t)nr] ^ flip;
-        nl = range_min(LCP, lcp_tab, nblk, r + 1, (uint64_t)nr);
-        nll = (pos_t)capped_left(T, (uint64_t)S[CLAMP ? min((uint64_t)ni, s - 1) : (uint64_t)ni], pos, lcap);
+        if (PARTS & 1) ni = SAx[CLAMP ? min((uint64_t)nr, s - 1) : (uint64_t)nr] ^ flip;
+        if (PARTS & 2) nl = range_min(LCP, lcp_tab, nblk, r + 1, (uint64_t)nr);
+        if ((PARTS & 5) == 5) nll = (pos_t)capped_left(T, (uint64_t)S[CLAMP ? min((uint64_t)ni, s - 1) : (uint64_t)ni], pos, lcap);
     }
     p_idx[i] = pi; n_idx[i] = ni;
     p_lce[i] = pl; n_lce[i] = nl;
@@ -459,13 +460,23 @@ void all_candidates(const uint8_t* T, uint64_t n, const pos_t* S, uint64_t s, bo
                 h_rec.code, h_rec.index, h_rec.limit, h_rec.thread);
     }
     static const char fused = getenv("LZ77SSS_FUSED_CANDIDATES") ? getenv("LZ77SSS_FUSED_CANDIDATES")[0] : '0';
-    if (fused == '1' || fused == '3') {
-        auto kern = fused == '1' ? all_candidates_fused_kernel<pos_t, false> : all_candidates_fused_kernel<pos_t, true>;
+    if (fused == '1' || (fused >= '3' && fused <= '7')) {
+        auto kern = fused == '1' ? all_candidates_fused_kernel<pos_t, false, 7>
+                  : fused == '3' ? all_candidates_fused_kernel<pos_t, true, 7>
+                  : fused == '4' ? all_candidates_fused_kernel<pos_t, false, 0>      // the two searches only
+                  : fused == '5' ? all_candidates_fused_kernel<pos_t, false, 1>      // + SAx[q]
+                  : fused == '6' ? all_candidates_fused_kernel<pos_t, false, 3>      // + range minimum over LCP
+                  : all_candidates_fused_kernel<pos_t, false, 5>;                    // searches + SAx[q] + S[idx] + left extension
         kern<<<ceil_div_u(s, 128), 128, 0, st>>>(
             T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.psv_idx,
             ls.nsv_idx, ls.psv_lce, ls.nsv_lce, ls.psv_lcel, ls.nsv_lcel);
         KERNEL_CHECK();
-        return;
+        if (fused >= '4') {        // partial bodies: synchronize (does it fault?), then compute the real candidates
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            fprintf(stderr, "fused variant %c: no fault (|S| = %llu, greater = %d)\n", fused, (unsigned long long)s, (int)greater);
+        } else {
+            return;
+        }
     }
     all_candidates_kernel<pos_t, 0><<<ceil_div_u(s, 128), 128, 0, st>>>(
         T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.psv_idx, ls.psv_lce,
