@@ -488,8 +488,8 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
     f_len = group_lce_r<pos_t, G>(V, f_src, i, gmask, lane);
 }
 
-// G lanes of a warp parse one block (G = 32: a warp per block; G = 8: four blocks per warp).  The parse is bound by the
-// latency of its dependent loads, so the number of blocks in flight per SM is what sets its throughput.
+// G lanes of a warp parse one block (G = 32: a warp per block, the default; G = 8: four blocks per warp, an experiment: more
+// blocks in flight per SM did not shorten the rounds).
 template <typename pos_t, int G>
 __global__ void __launch_bounds__(128, G == 32 ? 16 : 12) parse_kernel(const parse_ctx C, const lce_view<pos_t> V) {
     const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / G);
@@ -1127,8 +1127,9 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         CUDA_CHECK(cudaMemsetAsync(sc.Hc.get(), 0, table_entries * 8, st));
     sc.changed.reserve(8);
     const bool dbg_rounds = getenv("LZ77SSS_DEBUG_ROUNDS") != nullptr;
-    // lanes per parsed block (LZ77SSS_PARSE_GROUP = 8, 16 or 32)
-    const int parse_group = getenv("LZ77SSS_PARSE_GROUP") ? atoi(getenv("LZ77SSS_PARSE_GROUP")) : 8;
+    // lanes per parsed block (LZ77SSS_PARSE_GROUP = 8, 16 or 32).  Measured at 1 GiB: 65.9 / 74.5 / 80.2 ms of parse kernel
+    // for 32 / 16 / 8 lanes: four times the blocks in flight do not help, a round is as long as its heaviest block
+    const int parse_group = getenv("LZ77SSS_PARSE_GROUP") ? atoi(getenv("LZ77SSS_PARSE_GROUP")) : 32;
     const uint64_t track_div = getenv("LZ77SSS_TRACK_DIV") ? strtoull(getenv("LZ77SSS_TRACK_DIV"), nullptr, 10) : 64;
     sc.slice_exit.reserve(sizeof(block_state));
 

@@ -140,7 +140,7 @@ __global__ void all_candidates_kernel(const uint8_t* __restrict__ T, const pos_t
 
 // Both sides in one thread: the variant that faulted (kept behind LZ77SSS_FUSED_CANDIDATES=1 so that the fault can be
 // reproduced under compute-sanitizer).
-template <typename pos_t, bool CLAMP, int PARTS = 7>
+template <typename pos_t, bool CLAMP, int PARTS = 7, bool LAUNDER = false>
 __global__ void all_candidates_fused_kernel(const uint8_t* __restrict__ T, const pos_t* __restrict__ S, uint64_t s,
                                             const uint32_t* __restrict__ SAx, uint32_t flip, const uint32_t* __restrict__ ISA,
                                             const pos_t* __restrict__ LCP, const uint32_t* __restrict__ tab,
@@ -150,6 +150,15 @@ __global__ void all_candidates_fused_kernel(const uint8_t* __restrict__ T, const
                                             pos_t* __restrict__ p_lcel, pos_t* __restrict__ n_lcel) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= s) return;
+    if (LAUNDER) {          // the compiler forgets that these pointers are const __restrict__ (no ld.global.nc, no reordering
+        asm volatile("" : "+l"(T));        // across them): is the fault tied to how the loads are emitted?
+        asm volatile("" : "+l"(S));
+        asm volatile("" : "+l"(SAx));
+        asm volatile("" : "+l"(ISA));
+        asm volatile("" : "+l"(LCP));
+        asm volatile("" : "+l"(tab));
+        asm volatile("" : "+l"(lcp_tab));
+    }
     const uint64_t r = ISA[i];
     const uint64_t pos = S[i];
     const uint32_t v = (uint32_t)i ^ flip;
@@ -287,6 +296,12 @@ __global__ void all_candidates_checked_kernel(const pos_t* __restrict__ S, uint6
                 if (!found) chk_fail(rec, 94, lo, 0, i);
             }
         }
+    }
+    {   // the library's own search functions, both in this one kernel like in the fused kernel: same answers?
+        const uint32_t pr2 = prev_smaller(SAx, tab, nblk, r, v);
+        const uint32_t nr2 = next_smaller(SAx, tab, nblk, s, r, v);
+        if (pr2 != pr && atomicCAS(&rec->code, 0ull, 95ull) == 0ull) { rec->index = pr2; rec->limit = pr; rec->thread = i; }
+        if (nr2 != nr && atomicCAS(&rec->code, 0ull, 96ull) == 0ull) { rec->index = nr2; rec->limit = nr; rec->thread = i; }
     }
     if (pr != NONE32) {
         const uint32_t pi = LD(SAx, (uint64_t)pr, s, 16, 0u) ^ flip;
@@ -460,13 +475,14 @@ void all_candidates(const uint8_t* T, uint64_t n, const pos_t* S, uint64_t s, bo
                 h_rec.code, h_rec.index, h_rec.limit, h_rec.thread);
     }
     static const char fused = getenv("LZ77SSS_FUSED_CANDIDATES") ? getenv("LZ77SSS_FUSED_CANDIDATES")[0] : '0';
-    if (fused == '1' || (fused >= '3' && fused <= '7')) {
+    if (fused == '1' || (fused >= '3' && fused <= '8')) {
         auto kern = fused == '1' ? all_candidates_fused_kernel<pos_t, false, 7>
                   : fused == '3' ? all_candidates_fused_kernel<pos_t, true, 7>
                   : fused == '4' ? all_candidates_fused_kernel<pos_t, false, 0>      // the two searches only
                   : fused == '5' ? all_candidates_fused_kernel<pos_t, false, 1>      // + SAx[q]
                   : fused == '6' ? all_candidates_fused_kernel<pos_t, false, 3>      // + range minimum over LCP
-                  : all_candidates_fused_kernel<pos_t, false, 5>;                    // searches + SAx[q] + S[idx] + left extension
+                  : fused == '7' ? all_candidates_fused_kernel<pos_t, false, 5>      // searches + SAx[q] + S[idx] + left extension
+                  : all_candidates_fused_kernel<pos_t, false, 7, true>;              // everything, pointers laundered
         kern<<<ceil_div_u(s, 128), 128, 0, st>>>(
             T, S, s, SAx, greater ? 0xFFFFFFFFu : 0u, ss.ISA, ss.LCP, tab, ls.lcp_blkmin, ls.nblk, lcap, ls.psv_idx,
             ls.nsv_idx, ls.psv_lce, ls.nsv_lce, ls.psv_lcel, ls.nsv_lcel);
