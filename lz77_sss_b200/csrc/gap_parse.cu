@@ -960,7 +960,24 @@ __global__ void __launch_bounds__(256) dirty_from_new_entries_kernel(const parse
     }
 }
 
-// the repair list's share of the carried table
+// the big repair list's share of the carried table: one thread per bucket walks the bucket's entries backwards (the bucket
+// starts make this a coalesced sweep; an atomic per entry into a table of hundreds of megabytes was 14 ms per GiB)
+__global__ void carry_repair_buckets_kernel(const parse_ctx C, uint32_t nbuckets, unsigned long long* __restrict__ Hc) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nbuckets) return;
+    const uint32_t lo = C.rstart[b];
+    for (uint32_t kk = C.rstart[b + 1]; kk > lo;) {
+        kk--;
+        const uint32_t q = (uint32_t)C.rk[kk] / 5u;
+        if (!not_inserted(C.notins, q)) {
+            const unsigned long long cand = C.a0 + q + 1;
+            if (cand > Hc[b]) Hc[b] = cand;
+            return;
+        }
+    }
+}
+
+// a small repair list's share of the carried table
 __global__ void carry_repair_kernel(const parse_ctx C, const uint64_t* __restrict__ rk, uint32_t R, uint32_t nbuckets,
                                     unsigned long long* __restrict__ Hc) {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1570,7 +1587,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             carry_big_kernel<<<1184, 128, 0, st>>>(C, sc.Hc.get(), sc.big, sc.changed.get() + 1);
             KERNEL_CHECK();
             if (C.R) {
-                carry_repair_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(C, C.rk, C.R, (uint32_t)table_entries, sc.Hc.get());
+                carry_repair_buckets_kernel<<<ceil_div_u(table_entries, 256), 256, 0, st>>>(C, (uint32_t)table_entries, sc.Hc.get());
                 KERNEL_CHECK();
             }
             if (C.R2) {
