@@ -465,7 +465,7 @@ def main():
                 row.update(bound="latency (dependent loads)", achieved=None, frac=None)
             out["other_kernels"].append(row)
         out["index"] = {k: int(st_res[k]) for k in ("parse_slices", "sparse_slices", "sparse_fallbacks", "repair_entries",
-                                                    "parse_rounds", "gap_positions_hashed")}
+                                                    "parse_rounds", "gap_positions_hashed", "prefetched_slices")}
         if not args.no_cpu_baseline:
             # the reference on the same text, tau and num_threads: its time (cpu_baseline) and, outside every timed
             # region, its factor stream against the CUDA path's for the bases the reference drew (parity_checked)

@@ -69,6 +69,7 @@ typedef struct lz77sss_stats {
     uint64_t sparse_slices, sparse_fallbacks;  /* slices parsed with gap-only index entries / redone with all positions */
     uint64_t repair_entries;               /* index entries added while parsing (positions under gap factors that ran over phrases) */
     uint64_t t_exact_ns, exact_doubling_rounds, exact_parse_rounds;   /* lz77sss_factorize_exact: suffix array + parse */
+    uint64_t prefetched_slices;            /* slices whose index was built on the second stream while the slice before was parsed */
 } lz77sss_stats;
 
 /* factor callback: lz77_sss<pos_t>::factor {src,len} by value, in text order, on the calling thread

@@ -45,7 +45,7 @@ class Stats(C.Structure):
                                           "gap_positions_hashed", "t_h2d_ns", "t_sss_ns", "t_sort_ns", "t_lce_ns",
                                           "t_lpf_ns", "t_d2h_ns", "t_chain_ns", "t_gap_hash_ns", "t_emit_ns", "t_total_ns",
                                           "kernel_launches", "h2d_bytes", "d2h_bytes", "parse_rounds", "parse_slices", "sparse_slices", "sparse_fallbacks", "repair_entries",
-                                          "t_exact_ns", "exact_doubling_rounds", "exact_parse_rounds")]
+                                          "t_exact_ns", "exact_doubling_rounds", "exact_parse_rounds", "prefetched_slices")]
 
     def as_dict(self):
         d = {}

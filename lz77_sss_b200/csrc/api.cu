@@ -1099,6 +1099,7 @@ int factorize_impl(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host
     st.sparse_slices = h->gp.sparse_slices;
     st.sparse_fallbacks = h->gp.sparse_fallbacks;
     st.repair_entries = h->gp.repair_entries;
+    st.prefetched_slices = h->gp.prefetched_slices;
     st.t_gap_hash_ns = ns_since(t0);
 
     t0 = clk::now();
@@ -1247,7 +1248,11 @@ int lz77sss_create(const lz77sss_config* cfg, lz77sss_handle** out) {
         if (const char* e = getenv("LZ77SSS_HOST_EMIT")) h->host_emit = e[0] == '1';
         if (const char* e = getenv("LZ77SSS_SLICE_LEN")) h->slice_len = std::max<uint64_t>(64, strtoull(e, nullptr, 10));
         if (const char* e = getenv("LZ77SSS_BLOCK_LEN")) h->block_len = (uint32_t)std::max<uint64_t>(32, strtoull(e, nullptr, 10));
-        CUDA_CHECK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+        {   // the main stream outranks the side stream that builds the next slice's index during a parse (gap_parse.cu)
+            int least = 0, greatest = 0;
+            CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+            CUDA_CHECK(cudaStreamCreateWithPriority(&h->st, cudaStreamNonBlocking, greatest));
+        }
         *out = h.release();
         return LZ77SSS_OK;
     });

@@ -339,6 +339,61 @@ __global__ void __launch_bounds__(256) repair_start_kernel(const uint64_t* __res
         for (uint64_t b = (uint64_t)cur + 1; b <= nkeys; b++) rstart[b] = R;
 }
 
+constexpr uint32_t NOENT = 0xFFFFFFFFu;
+// Bucket chains: prev[e] = the entry in front of e in its bucket's list (time order = entry id order), NOENT for the first.
+// A probe walks the chain from its own entry instead of bisecting the bucket: the buckets of the short patterns (2 and 5
+// bytes) hold millions of entries, and every level of a bisection is a dependent load on the critical path of a block.
+__global__ void __launch_bounds__(256) link_prev_kernel(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ sval,
+                                                        uint64_t E, uint32_t* __restrict__ prev) {
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= E) return;
+    const uint32_t k = skey[j];
+    uint32_t p = NOENT;
+    if (j > 0 && skey[j - 1] == k) p = sval[j - 1];
+    prev[sval[j]] = p;
+}
+// Splices the sorted repair list L (bucket << 32 | entry id; all of it, the step is idempotent) into the chains.  The chains
+// hold the sorted index and, when L is the small list, the big list (big, rstart).  One thread per entry: its own link, and
+// the link of the entry behind it if no other entry of L lies in between.
+__global__ void __launch_bounds__(256) splice_repair_kernel(const uint32_t* __restrict__ sval, const uint32_t* __restrict__ bstart,
+                                                            const uint64_t* __restrict__ L, uint32_t cnt,
+                                                            const uint64_t* __restrict__ big, const uint32_t* __restrict__ rstart,
+                                                            uint32_t* __restrict__ prev) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= cnt) return;
+    const uint64_t x = L[k];
+    const uint32_t b = (uint32_t)(x >> 32), e = (uint32_t)x;
+    int64_t pred = -1;
+    uint32_t succ = NOENT;
+    {
+        const uint32_t lo = bstart[b], hi = bstart[b + 1];
+        uint32_t l = lo, h = hi;
+        while (l < h) {
+            const uint32_t mid = (l + h) >> 1;
+            if (sval[mid] < e) l = mid + 1;
+            else h = mid;
+        }
+        if (l > lo) pred = sval[l - 1];
+        if (l < hi) succ = sval[l];
+    }
+    if (big) {
+        const uint32_t lo = rstart[b], hi = rstart[b + 1];
+        uint32_t l = lo, h = hi;
+        while (l < h) {
+            const uint32_t mid = (l + h) >> 1;
+            if (big[mid] < x) l = mid + 1;
+            else h = mid;
+        }
+        if (l > lo) pred = max(pred, (int64_t)(uint32_t)big[l - 1]);
+        if (l < hi) succ = min(succ, (uint32_t)big[l]);
+    }
+    if (k > 0 && (uint32_t)(L[k - 1] >> 32) == b) pred = max(pred, (int64_t)(uint32_t)L[k - 1]);
+    uint32_t own_next = NOENT;
+    if (k + 1 < cnt && (uint32_t)(L[k + 1] >> 32) == b) own_next = (uint32_t)L[k + 1];
+    prev[e] = pred < 0 ? NOENT : (uint32_t)pred;
+    if (succ != NOENT && own_next > succ) prev[succ] = e;
+}
+
 struct block_state {
     uint64_t i, cur, k;
     uint32_t gap;      // last step before i was a gap step (positions up to i are inserted)
@@ -354,6 +409,7 @@ struct parse_ctx {
     const uint32_t* tkey;      // bucket of every entry, time order
     const uint32_t* sval;      // entries sorted by bucket, time order inside a bucket
     const uint32_t* bstart;    // bucket b = sval[bstart[b] .. bstart[b+1])
+    const uint32_t* prev;      // bucket chains: the entry in front of an entry in its bucket, over the index and the repair lists
     const uint64_t* Hc;        // last inserted position + 1 per bucket (0 = none), state before the slice
     const uint32_t* notins;    // bit = 1: position of the slice is NOT inserted
     const uint32_t* skip;      // sparse slice: bit = 1: the position has no entries (nullptr: every position has)
@@ -414,7 +470,7 @@ __device__ __forceinline__ bool group_any_skip(const parse_ctx& C, uint64_t s, u
 
 // longest_prev_occ (factorize/common.cpp:33-61) at position i, all lanes of the group; its lanes 0..4 own patterns 4..0.
 // "H[b] when i is probed" = the largest inserted position among the entries of bucket b in front of the probe's own
-// entry: the bucket's list of the sorted index and, on a sparse slice, of the repair list, else the carried table.
+// entry, found along the bucket's chain (sorted index and repair lists in one list, time order), else the carried table.
 template <typename pos_t, int G>
 __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>& V, uint64_t i, uint64_t& f_src,
                                       uint64_t& f_len, bool& bad, unsigned gmask, unsigned lane) {
@@ -429,49 +485,15 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
     uint64_t occ = NONE64;
     if (lane < 5) {
         const uint32_t e = 5u * rel + lane;
-        const uint32_t b = C.tkey[e];
-        const uint32_t lo = C.bstart[b];
-        uint32_t l = lo, h = C.bstart[b + 1];        // entries in front of the own one: [lo, l) after the search
-        while (l < h) {
-            const uint32_t mid = (l + h) >> 1;
-            if (C.sval[mid] < e) l = mid + 1;
-            else h = mid;
-        }
+        const uint32_t b = C.tkey[e];                 // (only the fallback needs it; loaded next to the first link)
+        uint32_t e1 = C.prev[e];
         bool found = false;
-        uint32_t kk = l;
-        while (kk > lo) {
-            kk--;
-            const uint32_t q = C.sval[kk] / 5u;
-            if (q == rel) { occ = i; found = true; break; }       // an earlier pattern of this position wrote the bucket
+        while (e1 != NOENT) {
+            const uint32_t q = e1 / 5u;
+            if (q == rel) { occ = i; found = true; break; }        // an earlier pattern of this position wrote the bucket
+            const uint32_t nxt = C.prev[e1];          // next link, in flight together with the bitmap word
             if (!not_inserted(C.notins, q)) { occ = C.a0 + q; found = true; break; }
-        }
-        for (int which = 0; which < 2; which++) {
-            const uint64_t* __restrict__ rk = which ? C.rk2 : C.rk;
-            const uint32_t R = which ? C.R2 : C.R;
-            if (!R) continue;
-            const uint64_t key = ((uint64_t)b << 32) | e;
-            uint32_t rl = 0, rh = R;
-            if (!which) { rl = C.rstart[b]; rh = C.rstart[b + 1]; }      // the big list has its bucket starts
-            const uint32_t rlo = rl;
-            while (rl < rh) {
-                const uint32_t mid = (rl + rh) >> 1;
-                if (rk[mid] < key) rl = mid + 1;
-                else rh = mid;
-            }
-            while (rl > rlo) {
-                rl--;
-                const uint64_t v = rk[rl];
-                if ((uint32_t)(v >> 32) != b) break;
-                const uint32_t q = (uint32_t)v / 5u;
-                uint64_t o2 = NONE64;
-                if (q == rel) o2 = i;
-                else if (!not_inserted(C.notins, q)) o2 = C.a0 + q;
-                if (o2 != NONE64) {
-                    if (!found || o2 > occ) occ = o2;
-                    found = true;
-                    break;
-                }
-            }
+            e1 = nxt;
         }
         if (!found) occ = C.Hc[b] - 1;
     }
@@ -1163,9 +1185,106 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         std::swap(K.entry, sc.entry); std::swap(K.exit_, sc.exit_); std::swap(K.marked, sc.marked); std::swap(K.ovr, sc.ovr);
         std::swap(K.dirty, sc.dirty); std::swap(K.notins_prev, sc.notins_prev); std::swap(K.Hc_prev, sc.Hc_prev);
         std::swap(K.tr_cnt, sc.tr_cnt); std::swap(K.tr_pos, sc.tr_pos); std::swap(K.tr_src, sc.tr_src); std::swap(K.tr_len, sc.tr_len);
-        std::swap(K.skip, sc.skip); std::swap(K.rstart, sc.rstart);
+        std::swap(K.skip, sc.skip); std::swap(K.rstart, sc.rstart); std::swap(K.prev, sc.prev);
         std::swap(K.rk0, sc.rk0); std::swap(K.rk1, sc.rk1); std::swap(K.rkb0, sc.rkb0); std::swap(K.rkb1, sc.rkb1);
     };
+
+    // 1. hash + 2. sort of the slice [a0, a1) into sc.{skip, tkey, v0 / v1, bstart}, on the stream bs.  Sparse (entries
+    // only for the positions that can be inserted or probed when no gap factor runs over a whole phrase, i.e. the gaps
+    // and the phrase starts) unless the gaps are most of the slice anyway.  head: that many leading positions were
+    // inserted by a gap factor that reaches into the slice (known only to a build in step with the parse).
+    struct built_index { uint64_t E = 0; bool sparse = false, vals_in_v0 = true; };
+    auto build_index = [&](uint64_t a0, uint64_t a1, bool sparse, uint64_t head, sort_scratch& srt, scan_scratch& scn,
+                           cudaStream_t bs) -> built_index {
+        const uint64_t cnt = a1 - a0;
+        const uint64_t nwords = (cnt + 31) / 32 + 1;
+        const uint32_t ntiles = ceil_div_u(cnt, GE_TILE);
+        uint64_t E = 5 * cnt;
+        if (sparse) {
+            // phrases that overlap the slice (the sentinel is not one of them)
+            const uint64_t k0 = std::upper_bound(h_ml + m, h_ml + m + (m - 1), a0) - (h_ml + m);
+            const uint64_t k1 = std::lower_bound(h_ml, h_ml + (m - 1), a1) - h_ml;
+            sc.skip.reserve(nwords);
+            sc.tile_off.reserve(ntiles + 2);
+            CUDA_CHECK(cudaMemsetAsync(sc.skip.get(), 0, nwords * 4, bs));
+            if (k1 > k0) {
+                skip_bits_kernel<<<ceil_div_u((k1 - k0) * 32, 128), 128, 0, bs>>>(sc.ml.get(), sc.ml.get() + m, k0, k1, a0, a1, sc.skip, 0);
+                KERNEL_CHECK();
+            }
+            if (head) {
+                clear_range_kernel<<<1, 32, 0, bs>>>(sc.skip, 0, head);
+                KERNEL_CHECK();
+            }
+            tile_need_kernel<<<ceil_div_u((uint64_t)ntiles * 32, 256), 256, 0, bs>>>(sc.skip, cnt, ntiles, sc.tile_off);
+            KERNEL_CHECK();
+            exclusive_scan_u32(sc.tile_off, ntiles, scn, bs, sc.tile_off.get() + ntiles);
+            uint32_t needed = 0;
+            CUDA_CHECK(cudaMemcpyAsync(&needed, sc.tile_off.get() + ntiles, 4, cudaMemcpyDeviceToHost, bs));
+            CUDA_CHECK(cudaStreamSynchronize(bs));
+            if ((uint64_t)needed * 2 > cnt) sparse = false;   // mostly gaps: the dense slice costs about the same and cannot fail
+            else E = 5ull * needed;
+        }
+        sc.k0.reserve(E + 8); sc.k1.reserve(E + 8); sc.v0.reserve(E + 8); sc.v1.reserve(E + 8); sc.tkey.reserve(5 * cnt);
+        sc.bstart.reserve(table_entries + 4);
+        sc.prev.reserve(5 * cnt);
+        uint32_t *keys = sc.k0, *kalt = sc.k1, *vals = sc.v0, *valt = sc.v1;
+        // a dense slice has vals[e] = e (the sort generates them in its first pass) and keys = tkey (its first pass
+        // reads tkey)
+        PROF_BEGIN(bs);
+        // sparse slice with few needed positions: only the 64-position segments that hold one are rolled
+        if (sparse && E * 8 < 5 * cnt)
+            gap_entries_sparse_kernel<<<ceil_div_u(cnt, SP_TILE), 160, 0, bs>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, vals,
+                                                                              sc.skip.get(), sc.tile_off.get());
+        else
+            gap_entries_kernel<<<ntiles, 160, 0, bs>>>(d_text, n, hp, a0, cnt, sparse ? keys : nullptr, sc.tkey, sparse ? vals : nullptr,
+                                                       sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
+        KERNEL_CHECK();
+        // algorithmic bytes: the slice's text once, the bucket ids of its indexed positions in time order, and on a
+        // sparse slice the compacted (bucket, entry id) pairs for the sort
+        PROF_END(bs, "gap_entries_kernel (5 rolling fingerprints mod 2^107-1)", cnt + (sparse ? E * 12 : 5 * cnt * 4));
+        if (E == 0) {                                  // no entry at all: every bucket list is empty
+            CUDA_CHECK(cudaMemsetAsync(sc.bstart.get(), 0, (table_entries + 2) * 4, bs));
+        } else {
+            radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, srt, bs, !sparse, sparse ? nullptr : sc.tkey.get());
+            bucket_start_kernel<<<ceil_div_u(E, 1024), 256, 0, bs>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
+            KERNEL_CHECK();
+            PROF_BEGIN(bs);
+            link_prev_kernel<<<ceil_div_u(E, 256), 256, 0, bs>>>(keys, vals, E, sc.prev);
+            KERNEL_CHECK();
+            PROF_END(bs, "link_prev_kernel (bucket chains of the sorted index)", E * 12);
+        }
+        built_index r;
+        r.E = E; r.sparse = sparse; r.vals_in_v0 = vals == sc.v0.get();
+        return r;
+    };
+    // second index set <-> the one the parse reads (host-side pointer swap; enqueued kernels keep their pointers)
+    auto swap_sets = [&]() {
+        std::swap(sc.next.v0, sc.v0); std::swap(sc.next.v1, sc.v1); std::swap(sc.next.tkey, sc.tkey);
+        std::swap(sc.next.bstart, sc.bstart); std::swap(sc.next.skip, sc.skip); std::swap(sc.next.prev, sc.prev);
+    };
+    // The next slice's index is built while this one is parsed unless the run keeps its slices (sharded passes), the
+    // kernels are being timed one by one, or the second set does not fit.
+    bool prefetch = !range && !g_prof_on && r_end - r_beg > slice_len &&
+                    !(getenv("LZ77SSS_PREFETCH_INDEX") && getenv("LZ77SSS_PREFETCH_INDEX")[0] == '0');
+    if (prefetch && !sc.next.tkey.cap) {
+        size_t free_b = 0, total_b = 0;
+        CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+        if ((double)free_b < 3.0 * 20.0 * (double)slice_len + 4e9) prefetch = false;
+    }
+    if (prefetch && !sc.side.st) {
+        int least = 0, greatest = 0;
+        CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        CUDA_CHECK(cudaStreamCreateWithPriority(&sc.side.st, cudaStreamNonBlocking, least));
+        CUDA_CHECK(cudaEventCreateWithFlags(&sc.side.ev_parse, cudaEventDisableTiming));
+        CUDA_CHECK(cudaEventCreateWithFlags(&sc.side.ev_build, cudaEventDisableTiming));
+    }
+    bool pf_valid = false;
+    uint64_t pf_a0 = 0;
+    int pf_attempt = 0;
+    built_index pf;
+    sc.prefetched_slices = 0;
+    // (a build that is still in flight when the parse ends or throws must not outlive the buffers' next use)
+    struct drain { cudaStream_t s; ~drain() { if (s) cudaStreamSynchronize(s); } } drain_guard{prefetch ? sc.side.st : nullptr};
 
     size_t slice_no = 0;
     for (uint64_t a0 = r_beg; a0 < r_end; a0 += slice_len, slice_no++) {
@@ -1195,66 +1314,55 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         // phrases that overlap the slice (the sentinel is not one of them)
         const uint64_t k0 = std::upper_bound(h_ml + m, h_ml + m + (m - 1), a0) - (h_ml + m);
         const uint64_t k1 = std::lower_bound(h_ml, h_ml + (m - 1), a1) - h_ml;
+        // a gap factor reaches into the slice: those positions are inserted and need entries
+        const uint64_t sparse_head = (first.gap && first.i > a0) ? (first.i < a1 ? first.i : a1) - a0 : 0;
+        uint64_t head_pending = 0;
       for (int attempt = have_sorted ? (K->sparse ? 0 : 1) : (naive || !sparse_ok) ? 1 : 0; attempt < 2; attempt++) {
         bool sparse = attempt == 0;
         uint64_t E = 5 * cnt;
-        if (sparse && have_sorted) {
-            E = K->E;                                 // a retained sparse slice: its skip bitmap, index and repair lists stand
-        } else if (sparse) {
-            sc.skip.reserve(nwords);
-            sc.tile_off.reserve(ntiles + 2);
-            CUDA_CHECK(cudaMemsetAsync(sc.skip.get(), 0, nwords * 4, st));
-            if (k1 > k0) {
-                skip_bits_kernel<<<ceil_div_u((k1 - k0) * 32, 128), 128, 0, st>>>(sc.ml.get(), sc.ml.get() + m, k0, k1, a0, a1, sc.skip, 0);
-                KERNEL_CHECK();
-            }
-            if (first.gap && first.i > a0) {          // a gap factor reaches into the slice: those positions are inserted
-                clear_range_kernel<<<1, 32, 0, st>>>(sc.skip, 0, (first.i < a1 ? first.i : a1) - a0);
-                KERNEL_CHECK();
-            }
-            tile_need_kernel<<<ceil_div_u((uint64_t)ntiles * 32, 256), 256, 0, st>>>(sc.skip, cnt, ntiles, sc.tile_off);
-            KERNEL_CHECK();
-            exclusive_scan_u32(sc.tile_off, ntiles, sc.scan, st, sc.tile_off.get() + ntiles);
-            uint32_t needed = 0;
-            CUDA_CHECK(cudaMemcpyAsync(&needed, sc.tile_off.get() + ntiles, 4, cudaMemcpyDeviceToHost, st));
-            CUDA_CHECK(cudaStreamSynchronize(st));
-            if ((uint64_t)needed * 2 > cnt) continue;   // mostly gaps: the dense slice costs about the same and cannot fail
-            E = 5ull * needed;
-        }
-        sc.entries_sorted += E;
-        // 1. hash + 2. sort
-        sc.k0.reserve(E + 8); sc.k1.reserve(E + 8); sc.v0.reserve(E + 8); sc.v1.reserve(E + 8); sc.tkey.reserve(5 * cnt);
-        sc.bstart.reserve(table_entries + 4);
-        sc.big.reserve(table_entries + 4);
-        uint32_t *keys = sc.k0, *kalt = sc.k1, *vals = sc.v0, *valt = sc.v1;
+        uint32_t* vals = nullptr;
         if (have_sorted) {
+            if (sparse) E = K->E;                     // a retained sparse slice: its skip bitmap, index and repair lists stand
             vals = K->vals_in_v0 ? sc.v0.get() : sc.v1.get();
         } else {
-        {
-            // a dense slice has vals[e] = e (the sort generates them in its first pass) and keys = tkey (its first
-            // pass reads tkey)
-            PROF_BEGIN(st);
-            // sparse slice with few needed positions: only the 64-position segments that hold one are rolled
-            if (sparse && E * 8 < 5 * cnt)
-                gap_entries_sparse_kernel<<<ceil_div_u(cnt, SP_TILE), 160, 0, st>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, vals,
-                                                                                  sc.skip.get(), sc.tile_off.get());
-            else
-                gap_entries_kernel<<<ntiles, 160, 0, st>>>(d_text, n, hp, a0, cnt, sparse ? keys : nullptr, sc.tkey, sparse ? vals : nullptr,
-                                                           sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
-            KERNEL_CHECK();
-            // algorithmic bytes: the slice's text once, the bucket ids of its indexed positions in time order, and on a
-            // sparse slice the compacted (bucket, entry id) pairs for the sort
-            PROF_END(st, "gap_entries_kernel (5 rolling fingerprints mod 2^107-1)", cnt + (sparse ? E * 12 : 5 * cnt * 4));
+            built_index bi;
+            if (pf_valid && pf_a0 == a0 && attempt == pf_attempt) {
+                // built on the second stream while the slice before was parsed
+                CUDA_CHECK(cudaStreamWaitEvent(st, sc.side.ev_build, 0));
+                swap_sets();
+                bi = pf;
+                pf_valid = false;
+                head_pending = sparse_head;           // (the build did not know the entry state)
+                sc.prefetched_slices++;
+            } else {
+                if (pf_valid) {                       // a build is in flight and shares the key buffers: after it
+                    CUDA_CHECK(cudaStreamWaitEvent(st, sc.side.ev_build, 0));
+                    if (pf_a0 <= a0) pf_valid = false;
+                }
+                bi = build_index(a0, a1, sparse, sparse_head, sc.sort, sc.scan, st);
+            }
+            E = bi.E;
+            if (sparse && !bi.sparse) { sparse = false; attempt = 1; }   // mostly gaps: every position is indexed
+            vals = bi.vals_in_v0 ? sc.v0.get() : sc.v1.get();
+            sc.entries_sorted += E;
+            if (K) { K->sorted = true; K->vals_in_v0 = bi.vals_in_v0; K->sparse = sparse; K->E = E; K->R = K->R2 = 0; }
         }
-        if (E == 0) {                                  // no entry at all: every bucket list is empty
-            CUDA_CHECK(cudaMemsetAsync(sc.bstart.get(), 0, (table_entries + 2) * 4, st));
-        } else {
-        radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, sc.sort, st, !sparse, sparse ? nullptr : sc.tkey.get());
-        bucket_start_kernel<<<ceil_div_u(E, 1024), 256, 0, st>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
-        KERNEL_CHECK();
+        // the index of the next slice, on the second stream, while this one is parsed
+        if (prefetch && !pf_valid && a0 + slice_len < r_end) {
+            const uint64_t b0 = a0 + slice_len, b1 = b0 + slice_len < r_end ? b0 + slice_len : r_end;
+            CUDA_CHECK(cudaEventRecord(sc.side.ev_parse, st));      // (the carry kernels of the slice before still read the other set)
+            CUDA_CHECK(cudaStreamWaitEvent(sc.side.st, sc.side.ev_parse, 0));
+            swap_sets();
+            try {
+                pf = build_index(b0, b1, !naive && sparse_ok, 0, sc.sort_b, sc.scan_b, sc.side.st);
+            } catch (...) { swap_sets(); throw; }
+            swap_sets();
+            CUDA_CHECK(cudaEventRecord(sc.side.ev_build, sc.side.st));
+            pf_valid = true;
+            pf_a0 = b0;
+            pf_attempt = (naive || !sparse_ok) ? 1 : 0;
         }
-        if (K) { K->sorted = true; K->vals_in_v0 = vals == sc.v0.get(); K->sparse = sparse; K->E = E; K->R = K->R2 = 0; }
-        }
+        sc.big.reserve(table_entries + 4);
         if (index_only) {
             // speculative table of this range: last position per bucket among the positions that the phrase list
             // alone says are inserted (everything but the inside of the phrases)
@@ -1294,7 +1402,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
 
         parse_ctx C;
         C.n = n; C.n_cut = n_cut; C.a0 = a0; C.a1 = a1; C.BL = BL; C.nb = nb; C.naive = naive ? 1u : 0u; C.bmin = 0;
-        C.tkey = sc.tkey; C.sval = vals; C.bstart = sc.bstart;
+        C.tkey = sc.tkey; C.sval = vals; C.bstart = sc.bstart; C.prev = sc.prev;
         C.Hc = reinterpret_cast<const uint64_t*>(sc.Hc.get());
         C.notins = sc.notins;
         C.skip = sparse ? sc.skip.get() : nullptr;
@@ -1323,6 +1431,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             CUDA_CHECK(cudaMemsetAsync(sc.req.get(), 0, 8, st));
         }
         bool give_up_sparse = false, track_now = false;
+        bool big_open = false;                      // the big list still takes batches (up to the one of round 0)
         uint64_t repair_total = 0;
         uint32_t pending_fb = 0xFFFFFFFFu;          // blocks from here on see new repair entries in the next round
         C.ovr = sc.ovr;
@@ -1350,8 +1459,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             if (nreq > C.req_cap) { give_up_sparse = true; return false; }
             // the first batch of a slice (what round 0 found: most of it) becomes the big list; later batches go to the
             // small list, which is sorted alone and folded into the big one when it outgrows its buffer
-            const bool to_big = C.R == 0;
-            const uint32_t before = to_big ? 0u : C.R2;
+            const bool to_big = C.R == 0 || big_open;
+            const uint32_t before = to_big ? C.R : C.R2;
             const uint32_t cap_here = to_big ? rcap : rcap2;
             CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 5, 0xFF, 4, st));
             CUDA_CHECK(cudaMemcpyAsync(sc.changed.get() + 6, &before, 4, cudaMemcpyHostToDevice, st));
@@ -1378,10 +1487,15 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 C.rk = rk_cur;
                 repair_start_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(rk_cur, C.R, (uint32_t)table_entries + 1, sc.rstart);
                 KERNEL_CHECK();
+                splice_repair_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(C.sval, C.bstart, rk_cur, C.R, nullptr, nullptr, sc.prev);
+                KERNEL_CHECK();
             } else if (r2[1] <= rcap2) {
                 C.R2 = r2[1];
                 radix_sort_pairs(rk2_cur, rk2_alt, rv_cur, rv_alt, C.R2, 0, 32 + key_bits, sc.sort, st);   // (payload unused)
                 C.rk2 = rk2_cur;
+                splice_repair_kernel<<<ceil_div_u(C.R2, 256), 256, 0, st>>>(C.sval, C.bstart, rk2_cur, C.R2, C.R ? C.rk : nullptr,
+                                                                            sc.rstart, sc.prev);
+                KERNEL_CHECK();
             } else {
                 // the small list overflowed: some positions lost their skip bit without getting entries, so the slice is
                 // redone with every position
@@ -1430,12 +1544,25 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
                 KERNEL_CHECK();
             }
+            if (sparse && head_pending) {
+                // the index was built ahead of the entry state: the positions a gap factor reaching into the slice has
+                // inserted get their entries now (first entries of the big repair list)
+                const uint32_t rq[4] = {1u, 0u, 0u, (uint32_t)head_pending};
+                CUDA_CHECK(cudaMemcpyAsync(sc.req.get(), rq, sizeof rq, cudaMemcpyHostToDevice, st));
+                CUDA_CHECK(cudaStreamSynchronize(st));      // (rq lives on this frame)
+                repair();
+                head_pending = 0;
+                pending_fb = 0xFFFFFFFFu;                   // (round 0 parses every block anyway)
+                if (give_up_sparse) { sc.sparse_fallbacks++; continue; }
+            }
+            big_open = true;
             PROF_BEGIN(st);
             launch_parse(C);
             KERNEL_CHECK();
             PROF_END(st, "parse_kernel (block-speculative greedy parse, latency-bound)", 0);
             sc.rounds++;
             if (sparse) repair();
+            big_open = false;
           }
             if (K) K->parsed = true;
             bool track = have_parse;    // follow single changes (resumed slices from the start, fresh ones once few are left)
@@ -1603,6 +1730,14 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         } else {
             // nothing to parse here, but positions up to first.i may have been inserted by a gap factor
             if (K) K->parsed = false;
+            if (sparse && head_pending) {               // (see round 0 above)
+                const uint32_t rq[4] = {1u, 0u, 0u, (uint32_t)head_pending};
+                CUDA_CHECK(cudaMemcpyAsync(sc.req.get(), rq, sizeof rq, cudaMemcpyHostToDevice, st));
+                CUDA_CHECK(cudaStreamSynchronize(st));
+                repair();
+                head_pending = 0;
+                if (give_up_sparse) { sc.sparse_fallbacks++; continue; }
+            }
             CUDA_CHECK(cudaMemsetAsync(sc.marked.get(), 0, nb + 1, st));
             CUDA_CHECK(cudaMemsetAsync(sc.tr_cnt.get(), 0, (size_t)nb * 4, st));
             CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
@@ -1622,6 +1757,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             KERNEL_CHECK();
             carry_big_kernel<<<1184, 128, 0, st>>>(C, sc.Hc.get(), sc.big, sc.changed.get() + 1);
             KERNEL_CHECK();
+            if (C.R) {
+                carry_repair_buckets_kernel<<<ceil_div_u(table_entries, 256), 256, 0, st>>>(C, (uint32_t)table_entries, sc.Hc.get());
+                KERNEL_CHECK();
+            }
         }
         if (sparse) { sc.sparse_slices++; sc.repair_entries += repair_total; }
         break;

@@ -116,6 +116,7 @@ struct slice_keep {
     dbuf<uint32_t> notins_prev;            // the bitmap the blocks were last parsed under
     dbuf<unsigned long long> Hc_prev;      // the table in front of the slice at its last parse
     dbuf<uint32_t> skip, rstart;           // sparse slice: positions without entries, bucket starts of the big repair list
+    dbuf<uint32_t> prev;                   // bucket chains
     dbuf<uint64_t> rk0, rk1, rkb0, rkb1;   // sparse slice: the repair lists
     uint32_t R = 0, R2 = 0;                // their sizes, and which buffer of each ping-pong pair holds them
     bool rk_in_0 = true, rk2_in_0 = true, sparse = false;
@@ -141,6 +142,7 @@ struct gap_parse_scratch {
     dbuf<uint32_t> notins_prev;
     dbuf<unsigned long long> Hc_prev;
     dbuf<uint32_t> skip, tile_off;         // sparse slices: positions without entries, compaction offsets per tile
+    dbuf<uint32_t> prev;                   // bucket chains: per entry id, the entry in front of it in its bucket
     dbuf<uint64_t> rk0, rk1;               // sparse slices: repair list (bucket << 32 | entry id), ping-pong for its sort
     dbuf<uint64_t> rkb0, rkb1;             // the small second repair list
     dbuf<uint32_t> rstart;                 // bucket starts of the big repair list
@@ -151,6 +153,27 @@ struct gap_parse_scratch {
     scan_scratch scan;
     uint64_t rounds = 0, slices = 0, entries_sorted = 0, sparse_slices = 0, sparse_fallbacks = 0;
     std::vector<std::unique_ptr<slice_keep>> keep;
+    // The index (hash + sort) of slice s+1 is built on a second stream while slice s is parsed: the parse rounds are
+    // bound by the latency of dependent loads and leave the memory system idle, the sort is bandwidth work.
+    struct index_set { dbuf<uint32_t> v0, v1, tkey, bstart, skip, prev; } next;
+    sort_scratch sort_b;                   // scratch of the builds on the second stream
+    scan_scratch scan_b;
+    struct side_stream {                   // (movable, so that the scratch can be reset by assignment)
+        cudaStream_t st = nullptr;
+        cudaEvent_t ev_parse = nullptr, ev_build = nullptr;
+        side_stream() = default;
+        side_stream(side_stream&& o) noexcept : st(o.st), ev_parse(o.ev_parse), ev_build(o.ev_build) { o.st = nullptr; o.ev_parse = o.ev_build = nullptr; }
+        side_stream& operator=(side_stream&& o) noexcept {
+            if (this != &o) { std::swap(st, o.st); std::swap(ev_parse, o.ev_parse); std::swap(ev_build, o.ev_build); }
+            return *this;
+        }
+        ~side_stream() {
+            if (st) cudaStreamDestroy(st);
+            if (ev_parse) cudaEventDestroy(ev_parse);
+            if (ev_build) cudaEventDestroy(ev_build);
+        }
+    } side;
+    uint64_t prefetched_slices = 0;
 };
 // h_ml: three planes (beg, end, src) of the merged phrase list incl. the sentinel {n, n+1, 0} (m entries).
 // Parses [0, n_cut); appends the factors to out_src/out_len; handover = {i, cur_pos, phrase index, gap flag}.

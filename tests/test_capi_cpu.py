@@ -27,7 +27,7 @@ def test_exports_match_header(capi):
 def test_struct_layout(capi):
     import ctypes as C
     assert C.sizeof(capi.Config) == 4 * 8 + 8 * 5 + 4 + 4
-    assert C.sizeof(capi.Stats) == 8 * 38
+    assert C.sizeof(capi.Stats) == 8 * 39
 
 
 def test_argument_validation(capi):
