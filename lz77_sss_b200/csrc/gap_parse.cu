@@ -81,12 +81,14 @@ __device__ __forceinline__ m107 muladd107(m107 fp, uint64_t base, m107 add) {
 // consecutive positions), the 5 x 2048 bucket ids are transposed through shared memory and leave coalesced.
 constexpr int GE_TILE = 2048, GE_SEG = 64, GE_HALO = 64;
 __device__ __forceinline__ int ge_txt(int p) { return p + ((p >> 6) << 2); }          // 68-byte pitch per 64-byte segment
+constexpr uint32_t NOENT = 0xFFFFFFFFu;       // bucket chains (below): no entry in front
+constexpr uint32_t NOLINK = 0xFFFFFFFEu;      // bucket chains: the link of this entry has not been looked up yet
 __device__ __forceinline__ int ge_out(int o) { return o + o / (5 * GE_SEG); }          // 321-word pitch per lane row
 __global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restrict__ T, uint64_t n, const ghp5 hp,
                                                           uint64_t a0, uint64_t cnt, uint32_t* __restrict__ keys,
                                                           uint32_t* __restrict__ tkeys, uint32_t* __restrict__ vals,
                                                           const uint32_t* __restrict__ skip,
-                                                          const uint32_t* __restrict__ tile_off) {
+                                                          const uint32_t* __restrict__ tile_off, uint32_t* __restrict__ prevs) {
     __shared__ __align__(16) uint8_t sT[(GE_TILE + GE_HALO) / 64 * 68 + 16];
     __shared__ uint32_t sOut[5 * GE_TILE + GE_TILE / GE_SEG + 8];
     __shared__ uint32_t sNeed[GE_TILE / 32], sRank[GE_TILE / 32];
@@ -146,6 +148,7 @@ __global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restr
             const uint32_t key = sOut[ge_out(o)];
             if (keys) keys[e0 + o] = key;
             tkeys[e0 + o] = key;
+            prevs[e0 + o] = NOLINK;
             if (vals) vals[e0 + o] = (uint32_t)(e0 + o);
         }
         return;
@@ -174,6 +177,7 @@ __global__ void __launch_bounds__(160) gap_entries_kernel(const uint8_t* __restr
         keys[c0 + 5ull * rank + j] = key;
         vals[c0 + 5ull * rank + j] = (uint32_t)(e0 + o);
         tkeys[e0 + o] = key;
+        prevs[e0 + o] = NOLINK;
     }
 }
 
@@ -186,7 +190,7 @@ __global__ void __launch_bounds__(160) gap_entries_sparse_kernel(const uint8_t* 
                                                                  uint64_t a0, uint64_t cnt, uint32_t* __restrict__ keys,
                                                                  uint32_t* __restrict__ tkeys, uint32_t* __restrict__ vals,
                                                                  const uint32_t* __restrict__ skip,
-                                                                 const uint32_t* __restrict__ tile_off) {
+                                                                 const uint32_t* __restrict__ tile_off, uint32_t* __restrict__ prevs) {
     __shared__ uint32_t sNeed[SP_WORDS], sRank[SP_WORDS + 1];
     __shared__ uint16_t sAct[SP_SEGS];
     __shared__ uint32_t s_nact;
@@ -255,6 +259,7 @@ __global__ void __launch_bounds__(160) gap_entries_sparse_kernel(const uint8_t* 
                 keys[c0 + 5ull * rank + (4 - x)] = key;
                 vals[c0 + 5ull * rank + (4 - x)] = (uint32_t)(e0 + o);
                 tkeys[e0 + o] = key;
+                prevs[e0 + o] = NOLINK;
                 rank++;
             }
             if (fits && j < hi) {
@@ -339,19 +344,13 @@ __global__ void __launch_bounds__(256) repair_start_kernel(const uint64_t* __res
         for (uint64_t b = (uint64_t)cur + 1; b <= nkeys; b++) rstart[b] = R;
 }
 
-constexpr uint32_t NOENT = 0xFFFFFFFFu;
-// Bucket chains: prev[e] = the entry in front of e in its bucket's list (time order = entry id order), NOENT for the first.
-// A probe walks the chain from its own entry instead of bisecting the bucket: the buckets of the short patterns (2 and 5
-// bytes) hold millions of entries, and every level of a bisection is a dependent load on the critical path of a block.
-__global__ void __launch_bounds__(256) link_prev_kernel(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ sval,
-                                                        uint64_t E, uint32_t* __restrict__ prev) {
-    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= E) return;
-    const uint32_t k = skey[j];
-    uint32_t p = NOENT;
-    if (j > 0 && skey[j - 1] == k) p = sval[j - 1];
-    prev[sval[j]] = p;
-}
+// Bucket chains: prev[e] = the entry in front of e in its bucket's list (time order = entry id order) over the sorted
+// index and both repair lists, NOENT for the first, NOLINK while nobody has asked.  A probe walks the chain from its own
+// entry; a missing link is looked up by bisecting the three lists (raw_pred below) and stored, so that the later rounds,
+// which probe nearly the same positions, find it with one load.  The buckets of the short patterns (2 and 5 bytes) hold
+// millions of entries, and every level of a bisection is a dependent load on the critical path of a block.
+// (Linking every entry up front, one scattered 4-byte store per sorted entry, was measured: 24.5 ms per GiB for 660 M
+// entries, as much as the probes gained; a round looks up some 20 M links.)
 // Splices the sorted repair list L (bucket << 32 | entry id; all of it, the step is idempotent) into the chains.  The chains
 // hold the sorted index and, when L is the small list, the big list (big, rstart).  One thread per entry: its own link, and
 // the link of the entry behind it if no other entry of L lies in between.
@@ -409,7 +408,8 @@ struct parse_ctx {
     const uint32_t* tkey;      // bucket of every entry, time order
     const uint32_t* sval;      // entries sorted by bucket, time order inside a bucket
     const uint32_t* bstart;    // bucket b = sval[bstart[b] .. bstart[b+1])
-    const uint32_t* prev;      // bucket chains: the entry in front of an entry in its bucket, over the index and the repair lists
+    uint32_t* prev;            // bucket chains: the entry in front of an entry in its bucket over the index and the repair lists
+                               // (NOLINK until a probe has looked it up)
     const uint64_t* Hc;        // last inserted position + 1 per bucket (0 = none), state before the slice
     const uint32_t* notins;    // bit = 1: position of the slice is NOT inserted
     const uint32_t* skip;      // sparse slice: bit = 1: the position has no entries (nullptr: every position has)
@@ -468,6 +468,36 @@ __device__ __forceinline__ bool group_any_skip(const parse_ctx& C, uint64_t s, u
     return __ballot_sync(gmask, any) != 0;
 }
 
+// the largest entry id below e in bucket b over the sorted index and both repair lists (NOENT: none).  The three
+// bisections advance in lockstep, so that their loads are in flight together.
+__device__ __forceinline__ uint32_t raw_pred(const parse_ctx& C, uint32_t e, uint32_t b) {
+    const uint32_t lo = C.bstart[b];
+    uint32_t l0 = lo, h0 = C.bstart[b + 1];
+    uint32_t rlo = 0, l1 = 0, h1 = 0, l2 = 0, h2 = C.rk2 ? C.R2 : 0u;
+    if (C.R) { rlo = l1 = C.rstart[b]; h1 = C.rstart[b + 1]; }
+    const uint64_t key = ((uint64_t)b << 32) | e;
+    while (l0 < h0 || l1 < h1 || l2 < h2) {
+        const uint32_t m0 = (l0 + h0) >> 1, m1 = (l1 + h1) >> 1, m2 = (l2 + h2) >> 1;
+        const bool a0 = l0 < h0, a1 = l1 < h1, a2 = l2 < h2;
+        uint32_t v0 = 0;
+        uint64_t v1 = 0, v2 = 0;
+        if (a0) v0 = C.sval[m0];
+        if (a1) v1 = C.rk[m1];
+        if (a2) v2 = C.rk2[m2];
+        if (a0) { if (v0 < e) l0 = m0 + 1; else h0 = m0; }
+        if (a1) { if (v1 < key) l1 = m1 + 1; else h1 = m1; }
+        if (a2) { if (v2 < key) l2 = m2 + 1; else h2 = m2; }
+    }
+    int64_t pred = -1;
+    if (l0 > lo) pred = C.sval[l0 - 1];
+    if (l1 > rlo) pred = max(pred, (int64_t)(uint32_t)C.rk[l1 - 1]);
+    if (l2 > 0) {
+        const uint64_t v = C.rk2[l2 - 1];
+        if ((uint32_t)(v >> 32) == b) pred = max(pred, (int64_t)(uint32_t)v);
+    }
+    return pred < 0 ? NOENT : (uint32_t)pred;
+}
+
 // longest_prev_occ (factorize/common.cpp:33-61) at position i, all lanes of the group; its lanes 0..4 own patterns 4..0.
 // "H[b] when i is probed" = the largest inserted position among the entries of bucket b in front of the probe's own
 // entry, found along the bucket's chain (sorted index and repair lists in one list, time order), else the carried table.
@@ -485,14 +515,22 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
     uint64_t occ = NONE64;
     if (lane < 5) {
         const uint32_t e = 5u * rel + lane;
-        const uint32_t b = C.tkey[e];                 // (only the fallback needs it; loaded next to the first link)
+        const uint32_t b = C.tkey[e];                 // (the lookup of a missing link and the fallback need it)
         uint32_t e1 = C.prev[e];
+        if (e1 == NOLINK) {
+            e1 = raw_pred(C, e, b);
+            C.prev[e] = e1;
+        }
         bool found = false;
         while (e1 != NOENT) {
             const uint32_t q = e1 / 5u;
             if (q == rel) { occ = i; found = true; break; }        // an earlier pattern of this position wrote the bucket
-            const uint32_t nxt = C.prev[e1];          // next link, in flight together with the bitmap word
+            uint32_t nxt = C.prev[e1];                // next link, in flight together with the bitmap word
             if (!not_inserted(C.notins, q)) { occ = C.a0 + q; found = true; break; }
+            if (nxt == NOLINK) {
+                nxt = raw_pred(C, e1, b);
+                C.prev[e1] = nxt;
+            }
             e1 = nxt;
         }
         if (!found) occ = C.Hc[b] - 1;
@@ -1193,6 +1231,16 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
     // only for the positions that can be inserted or probed when no gap factor runs over a whole phrase, i.e. the gaps
     // and the phrase starts) unless the gaps are most of the slice anyway.  head: that many leading positions were
     // inserted by a gap factor that reaches into the slice (known only to a build in step with the parse).
+    // LZ77SSS_DEBUG_ROUNDS: device timeline of the builds (either stream) and the parses
+    struct tl_mark { const char* what; uint64_t a0; cudaEvent_t ev; };
+    std::vector<tl_mark> tl;
+    auto mark = [&](const char* what, uint64_t a0, cudaStream_t s) {
+        if (!dbg_rounds) return;
+        cudaEvent_t e;
+        CUDA_CHECK(cudaEventCreate(&e));
+        CUDA_CHECK(cudaEventRecord(e, s));
+        tl.push_back({what, a0, e});
+    };
     struct built_index { uint64_t E = 0; bool sparse = false, vals_in_v0 = true; };
     auto build_index = [&](uint64_t a0, uint64_t a1, bool sparse, uint64_t head, sort_scratch& srt, scan_scratch& scn,
                            cudaStream_t bs) -> built_index {
@@ -1200,6 +1248,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         const uint64_t nwords = (cnt + 31) / 32 + 1;
         const uint32_t ntiles = ceil_div_u(cnt, GE_TILE);
         uint64_t E = 5 * cnt;
+        mark(bs == st ? "build begin (main stream)" : "build begin (side stream)", a0, bs);
         if (sparse) {
             // phrases that overlap the slice (the sentinel is not one of them)
             const uint64_t k0 = std::upper_bound(h_ml + m, h_ml + m + (m - 1), a0) - (h_ml + m);
@@ -1234,10 +1283,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         // sparse slice with few needed positions: only the 64-position segments that hold one are rolled
         if (sparse && E * 8 < 5 * cnt)
             gap_entries_sparse_kernel<<<ceil_div_u(cnt, SP_TILE), 160, 0, bs>>>(d_text, n, hp, a0, cnt, keys, sc.tkey, vals,
-                                                                              sc.skip.get(), sc.tile_off.get());
+                                                                              sc.skip.get(), sc.tile_off.get(), sc.prev.get());
         else
             gap_entries_kernel<<<ntiles, 160, 0, bs>>>(d_text, n, hp, a0, cnt, sparse ? keys : nullptr, sc.tkey, sparse ? vals : nullptr,
-                                                       sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr);
+                                                       sparse ? sc.skip.get() : nullptr, sparse ? sc.tile_off.get() : nullptr, sc.prev.get());
         KERNEL_CHECK();
         // algorithmic bytes: the slice's text once, the bucket ids of its indexed positions in time order, and on a
         // sparse slice the compacted (bucket, entry id) pairs for the sort
@@ -1248,11 +1297,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
             radix_sort_pairs32(keys, kalt, vals, valt, E, 0, key_bits, srt, bs, !sparse, sparse ? nullptr : sc.tkey.get());
             bucket_start_kernel<<<ceil_div_u(E, 1024), 256, 0, bs>>>(keys, E, (uint32_t)table_entries + 1, sc.bstart);
             KERNEL_CHECK();
-            PROF_BEGIN(bs);
-            link_prev_kernel<<<ceil_div_u(E, 256), 256, 0, bs>>>(keys, vals, E, sc.prev);
-            KERNEL_CHECK();
-            PROF_END(bs, "link_prev_kernel (bucket chains of the sorted index)", E * 12);
         }
+        mark("build end", a0, bs);
         built_index r;
         r.E = E; r.sparse = sparse; r.vals_in_v0 = vals == sc.v0.get();
         return r;
@@ -1400,6 +1446,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         sc.J.reserve((uint64_t)levels * (nb + 1));
         sc.cnt.reserve(nb + 2);
 
+        mark("parse begin", a0, st);
         parse_ctx C;
         C.n = n; C.n_cut = n_cut; C.a0 = a0; C.a1 = a1; C.BL = BL; C.nb = nb; C.naive = naive ? 1u : 0u; C.bmin = 0;
         C.tkey = sc.tkey; C.sval = vals; C.bstart = sc.bstart; C.prev = sc.prev;
@@ -1762,6 +1809,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 KERNEL_CHECK();
             }
         }
+        mark("parse end", a0, st);
         if (sparse) { sc.sparse_slices++; sc.repair_entries += repair_total; }
         break;
       }
@@ -1769,6 +1817,15 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
     if (range && range->d_table_out)
         CUDA_CHECK(cudaMemcpyAsync(range->d_table_out, sc.Hc.get(), table_entries * 8, cudaMemcpyDeviceToDevice, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
+    if (!tl.empty()) {
+        if (sc.side.st) CUDA_CHECK(cudaStreamSynchronize(sc.side.st));
+        for (auto& t : tl) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, tl[0].ev, t.ev);
+            fprintf(stderr, "timeline %9.3f ms  slice %llu  %s\n", ms, (unsigned long long)t.a0, t.what);
+        }
+        for (auto& t : tl) cudaEventDestroy(t.ev);
+    }
     handover[0] = first.i;
     handover[1] = first.cur;
     handover[2] = first.k;
