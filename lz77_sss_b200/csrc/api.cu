@@ -906,9 +906,17 @@ void emit_all(const uint64_t* src, const uint64_t* len, uint64_t z, lz77sss_emit
     if (emit == &lz77sss_sink_emit) {
         auto* s = static_cast<lz77sss_factor_sink*>(ctx);
         const uint64_t room = s->count < s->cap ? s->cap - s->count : 0, m = std::min(z, room);
-        if (m) {
+        if (m < (1u << 20)) {
             std::memcpy(s->src + s->count, src, m * 8);
             std::memcpy(s->len + s->count, len, m * 8);
+        } else {                  // tens of MB into (usually untouched) caller memory: page faults and copy on several threads
+            const uint32_t parts = 8;
+            const uint64_t at = s->count;
+            run_blocks(parts, [&](uint32_t t) {
+                const uint64_t b = m * t / parts, e = m * (t + 1) / parts;
+                std::memcpy(s->src + at + b, src + b, (e - b) * 8);
+                std::memcpy(s->len + at + b, len + b, (e - b) * 8);
+            });
         }
         s->count += z;
         return;

@@ -468,32 +468,57 @@ __device__ __forceinline__ bool group_any_skip(const parse_ctx& C, uint64_t s, u
     return __ballot_sync(gmask, any) != 0;
 }
 
-// the largest entry id below e in bucket b over the sorted index and both repair lists (NOENT: none).  The three
-// bisections advance in lockstep, so that their loads are in flight together.
-__device__ __forceinline__ uint32_t raw_pred(const parse_ctx& C, uint32_t e, uint32_t b) {
-    const uint32_t lo = C.bstart[b];
-    uint32_t l0 = lo, h0 = C.bstart[b + 1];
-    uint32_t rlo = 0, l1 = 0, h1 = 0, l2 = 0, h2 = C.rk2 ? C.R2 : 0u;
-    if (C.R) { rlo = l1 = C.rstart[b]; h1 = C.rstart[b + 1]; }
-    const uint64_t key = ((uint64_t)b << 32) | e;
-    while (l0 < h0 || l1 < h1 || l2 < h2) {
-        const uint32_t m0 = (l0 + h0) >> 1, m1 = (l1 + h1) >> 1, m2 = (l2 + h2) >> 1;
-        const bool a0 = l0 < h0, a1 = l1 < h1, a2 = l2 < h2;
-        uint32_t v0 = 0;
-        uint64_t v1 = 0, v2 = 0;
-        if (a0) v0 = C.sval[m0];
-        if (a1) v1 = C.rk[m1];
-        if (a2) v2 = C.rk2[m2];
-        if (a0) { if (v0 < e) l0 = m0 + 1; else h0 = m0; }
-        if (a1) { if (v1 < key) l1 = m1 + 1; else h1 = m1; }
-        if (a2) { if (v2 < key) l2 = m2 + 1; else h2 = m2; }
+// lower bound of key in the ascending arr[lo, hi), searched outwards from g, the result of this lane's last search in the
+// same list (any value is safe): consecutive probes of a block ask for neighbouring entries, so the doubling steps find
+// the bracket within a few dependent loads where a bisection of a 2-byte pattern's bucket takes 23.
+template <typename T>
+__device__ __forceinline__ uint32_t hinted_lower_bound(const T* __restrict__ arr, uint32_t lo, uint32_t hi, T key, uint32_t g) {
+    uint32_t l = lo, h = hi;
+    if (g >= lo && g <= hi && lo < hi) {
+        if (g < hi && arr[g] < key) {                 // the answer lies behind g
+            uint32_t step = 1;
+            l = g + 1;
+            while (l + step <= hi && arr[l + step - 1] < key) { l += step; step <<= 1; }
+            if (l + step <= hi) h = l + step - 1;
+        } else {                                      // arr[g] >= key (or g == hi): the answer is g or lies in front of it
+            uint32_t step = 1;
+            h = g;
+            while (h >= lo + step && arr[h - step] >= key) { h -= step; step <<= 1; }
+            if (h >= lo + step) l = h - step + 1;
+        }
     }
+    while (l < h) {
+        const uint32_t mid = (l + h) >> 1;
+        if (arr[mid] < key) l = mid + 1;
+        else h = mid;
+    }
+    return l;
+}
+
+// the largest entry id below e in bucket b over the sorted index and both repair lists (NOENT: none).
+// hint: this lane's last positions in the three lists (shared memory), or nullptr.
+__device__ __forceinline__ uint32_t raw_pred(const parse_ctx& C, uint32_t e, uint32_t b, uint32_t* hint) {
+    const uint64_t key = ((uint64_t)b << 32) | e;
     int64_t pred = -1;
-    if (l0 > lo) pred = C.sval[l0 - 1];
-    if (l1 > rlo) pred = max(pred, (int64_t)(uint32_t)C.rk[l1 - 1]);
-    if (l2 > 0) {
-        const uint64_t v = C.rk2[l2 - 1];
-        if ((uint32_t)(v >> 32) == b) pred = max(pred, (int64_t)(uint32_t)v);
+    {
+        const uint32_t lo = C.bstart[b], hi = C.bstart[b + 1];
+        const uint32_t l = hinted_lower_bound<uint32_t>(C.sval, lo, hi, e, hint ? hint[0] : NOENT);
+        if (hint) hint[0] = l;
+        if (l > lo) pred = C.sval[l - 1];
+    }
+    if (C.R) {
+        const uint32_t lo = C.rstart[b], hi = C.rstart[b + 1];
+        const uint32_t l = hinted_lower_bound<uint64_t>(C.rk, lo, hi, key, hint ? hint[1] : NOENT);
+        if (hint) hint[1] = l;
+        if (l > lo) pred = max(pred, (int64_t)(uint32_t)C.rk[l - 1]);
+    }
+    if (C.rk2 && C.R2) {
+        const uint32_t l = hinted_lower_bound<uint64_t>(C.rk2, 0, C.R2, key, hint ? hint[2] : NOENT);
+        if (hint) hint[2] = l;
+        if (l > 0) {
+            const uint64_t v = C.rk2[l - 1];
+            if ((uint32_t)(v >> 32) == b) pred = max(pred, (int64_t)(uint32_t)v);
+        }
     }
     return pred < 0 ? NOENT : (uint32_t)pred;
 }
@@ -503,7 +528,7 @@ __device__ __forceinline__ uint32_t raw_pred(const parse_ctx& C, uint32_t e, uin
 // entry, found along the bucket's chain (sorted index and repair lists in one list, time order), else the carried table.
 template <typename pos_t, int G>
 __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>& V, uint64_t i, uint64_t& f_src,
-                                      uint64_t& f_len, bool& bad, unsigned gmask, unsigned lane) {
+                                      uint64_t& f_len, bool& bad, unsigned gmask, unsigned lane, uint32_t* hint) {
     const uint32_t rel = (uint32_t)(i - C.a0);
     if (C.skip && ((C.skip[rel >> 5] >> (rel & 31)) & 1u)) {       // a wrong speculation, or the position a gap factor that
         bad = true;                                                 // ran over whole phrases lands on: ask for its entries
@@ -518,7 +543,7 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
         const uint32_t b = C.tkey[e];                 // (the lookup of a missing link and the fallback need it)
         uint32_t e1 = C.prev[e];
         if (e1 == NOLINK) {
-            e1 = raw_pred(C, e, b);
+            e1 = raw_pred(C, e, b, hint);
             C.prev[e] = e1;
         }
         bool found = false;
@@ -528,7 +553,7 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
             uint32_t nxt = C.prev[e1];                // next link, in flight together with the bitmap word
             if (!not_inserted(C.notins, q)) { occ = C.a0 + q; found = true; break; }
             if (nxt == NOLINK) {
-                nxt = raw_pred(C, e1, b);
+                nxt = raw_pred(C, e1, b, nullptr);
                 C.prev[e1] = nxt;
             }
             e1 = nxt;
@@ -555,6 +580,9 @@ __global__ void __launch_bounds__(128, G == 32 ? 16 : 12) parse_kernel(const par
     const uint32_t b = (uint32_t)(((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / G);
     const unsigned lane = threadIdx.x & (G - 1);                       // lane inside the group
     const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (threadIdx.x & 31 & ~(G - 1)));
+    __shared__ uint32_t s_hint[128 / G][5][3];      // per pattern lane: where its last lookups ended in the three lists
+    if (lane < 5) s_hint[(threadIdx.x & 127) / G][lane][0] = s_hint[(threadIdx.x & 127) / G][lane][1] = s_hint[(threadIdx.x & 127) / G][lane][2] = NOENT;
+    uint32_t* hint = s_hint[(threadIdx.x & 127) / G][lane < 5 ? lane : 0];
     if (b >= C.nb || b < C.bmin || !C.marked[b] || !C.dirty[b]) return;
     const block_state st = C.entry[b];
     uint64_t i = st.i, cur = st.cur, k = st.k;
@@ -572,7 +600,7 @@ __global__ void __launch_bounds__(128, G == 32 ? 16 : 12) parse_kernel(const par
         uint32_t kind;
         const uint64_t at = i;
         if (i < pb) {   // gap step (greedy.cpp:60-97, greedy_naive.cpp:56-67)
-            probe<pos_t, G>(C, V, i, o_src, o_len, bad, gmask, lane);
+            probe<pos_t, G>(C, V, i, o_src, o_len, bad, gmask, lane, hint);
             if (C.naive && o_len > pb - i) o_len = pb - i;
             uint64_t i2 = i + (o_len ? o_len : 1);
             if (i2 > pb) {
@@ -600,7 +628,7 @@ __global__ void __launch_bounds__(128, G == 32 ? 16 : 12) parse_kernel(const par
             kind = KIND_PHR;
             if (cur == i) {
                 uint64_t fs, fl;
-                probe<pos_t, G>(C, V, i, fs, fl, bad, gmask, lane);
+                probe<pos_t, G>(C, V, i, fs, fl, bad, gmask, lane, hint);
                 cur = i + 1;
                 kind |= KIND_PROBED;
                 if (C.naive && k + 1 < C.m) {            // greedy_naive.cpp:82-85: clipped to the next phrase start
@@ -940,32 +968,57 @@ __global__ void __launch_bounds__(128) repair_entries_kernel(const uint8_t* __re
     if (w >= nreq) return;
     const uint32_t s = req[2 + 2 * w], e = req[3 + 2 * w];
     if (lane == 0) atomicMin(first_pos, s);
-    for (uint32_t p = s + lane; p < e; p += 32) {
-        const uint32_t bit = 1u << (p & 31);
-        if (!(skip[p >> 5] & bit)) continue;
-        if (!(atomicAnd(&skip[p >> 5], ~bit) & bit)) continue;        // another request claimed it
-        const uint64_t pos = a0 + p;
-        uint32_t key[5];
-#pragma unroll
-        for (int x = 0; x < 5; x++) {
-            const uint64_t L = hp.L[x];
-            key[4 - x] = hp.invalid_key;
-            if (pos + L < n) {
-                m107 fp;
-                fp.lo = fp.hi = 0;
-                for (uint64_t j = 0; j < L; j++) {
-                    m107 c;
-                    c.lo = T[pos + j]; c.hi = 0;
-                    fp = muladd107(fp, hp.base[x], c);
-                }
-                key[4 - x] = (uint32_t)(fp.lo & hp.mask);
-            }
+    // a lane takes RCH consecutive positions: it claims those that still lack entries, then rolls every pattern from the
+    // first to the last claimed one (a fresh window per position would cost 79 multiply-adds instead of 5 roll steps)
+    constexpr uint32_t RCH = 8;
+    for (uint32_t c0 = s + lane * RCH; c0 < e; c0 += 32 * RCH) {
+        const uint32_t c1 = c0 + RCH < e ? c0 + RCH : e;
+        uint32_t mine = 0;
+        for (uint32_t p = c0; p < c1; p++) {
+            const uint32_t bit = 1u << (p & 31);
+            if (!(skip[p >> 5] & bit)) continue;
+            if (atomicAnd(&skip[p >> 5], ~bit) & bit) mine |= 1u << (p - c0);      // (else another request claimed it)
         }
-        const uint32_t slot = atomicAdd(rcount, 5u);
-#pragma unroll
-        for (int j = 0; j < 5; j++) {
-            tkey[5ull * p + j] = key[j];
-            if (slot + j < rcap) rk[slot + j] = ((uint64_t)key[j] << 32) | (5u * p + j);
+        if (!mine) continue;
+        const uint32_t slot = atomicAdd(rcount, 5u * (uint32_t)__popc(mine));
+        const int jlo = __ffs(mine) - 1, jhi = 31 - __clz(mine);
+#pragma unroll 1
+        for (int x = 0; x < 5; x++) {
+            const uint64_t L = hp.L[x], base = hp.base[x];
+            const m107* __restrict__ nbt = hp.nbtab + x * 256;
+            m107 fp;
+            fp.lo = fp.hi = 0;
+            bool live = false;
+            uint32_t rank = 0;
+            for (int j = jlo; j <= jhi; j++) {
+                const uint32_t p = c0 + j;
+                const uint64_t pos = a0 + p;
+                const bool fits = pos + L < n;
+                if (fits && !live) {
+                    for (uint64_t q = 0; q < L; q++) {
+                        m107 c;
+                        c.lo = T[pos + q]; c.hi = 0;
+                        fp = muladd107(fp, base, c);
+                    }
+                    live = true;
+                }
+                if ((mine >> j) & 1u) {
+                    const uint32_t key = fits ? (uint32_t)(fp.lo & hp.mask) : hp.invalid_key;
+                    const uint32_t en = 5u * p + (4 - x);
+                    tkey[en] = key;
+                    const uint32_t at = slot + 5u * rank + (4 - x);
+                    if (at < rcap) rk[at] = ((uint64_t)key << 32) | en;
+                    rank++;
+                }
+                if (fits && j < jhi) {
+                    m107 infl = nbt[T[pos]];                               // -(base^L) * T[pos]
+                    const uint64_t in = T[pos + L];
+                    infl.lo += in;
+                    infl.hi += infl.lo < in;
+                    infl = fold107(infl.lo, infl.hi);
+                    fp = muladd107(fp, base, infl);
+                }
+            }
         }
     }
 }
