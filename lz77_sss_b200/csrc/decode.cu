@@ -5,11 +5,13 @@
 //   1. output offsets = exclusive scan of max(1,len) over the factors (64-bit sums),
 //   2. every output byte gets a pointer to the byte it copies (or its literal value); a factor that overlaps its own
 //      source (period d = start - src < len) points every byte into the period in front of it, so a run costs one hop,
-//   3. pointer jumping: a byte whose source is resolved takes its value, otherwise it adopts the source's
-//      pointer; the chain length halves every round.  Tiles of 1024 bytes that are completely resolved are skipped.
-//      State per byte: n < 2^32 - 16: a 32-bit pointer and a 16-bit word (0x100 | value, 0 = unresolved), so that
-//      "resolved" and the value are read atomically; larger n: one 64-bit word, bit 63 = resolved, low 8 bits = value.
-// Algorithmic bytes: 2n + z*sizeof(factor); a round moves 10 (24) bytes per unresolved byte.
+//   3. pointer jumping: one word per byte holds either the byte's value (resolved) or the position it copies from; an
+//      unresolved byte reads its source's word and adopts it (the value, or the source's own source: the chain length
+//      halves), twice per round.  Tiles of 1024 bytes that are completely resolved are skipped.
+//      n < 2^32 - 256: 32-bit words, resolved = 0xFFFFFF00 | value; larger n: 64-bit words, bit 63 = resolved.
+//      The word is read and written whole, so "resolved" and the value are seen together.
+// Algorithmic bytes: 2n + z*sizeof(factor); a hop moves one gathered word per unresolved byte, a round
+// reads and writes the byte's own word once.
 #include "common.cuh"
 #include "stages.cuh"
 
@@ -18,6 +20,9 @@ namespace {
 
 constexpr int DT = 1024;                       // bytes per tile of the jumping rounds
 constexpr uint64_t RES64 = 1ull << 63;
+constexpr uint32_t RES32 = 0xFFFFFF00u;         // 32-bit words: values at and above it are resolved bytes
+template <typename P> __device__ __forceinline__ bool is_res(P v) { return sizeof(P) == 4 ? (uint32_t)v >= RES32 : ((uint64_t)v & RES64) != 0; }
+template <typename P> __device__ __forceinline__ P res_word(uint64_t byte) { return sizeof(P) == 4 ? (P)(RES32 | (uint32_t)(byte & 0xFF)) : (P)(RES64 | (byte & 0xFF)); }
 
 // ---- 64-bit exclusive scan of max(1, len) -----------------------------------------------------------------------------
 constexpr int SC_NT = 256, SC_IPT = 8, SC_TILE = SC_NT * SC_IPT;
@@ -105,8 +110,7 @@ __global__ void __launch_bounds__(SC_NT) flen_apply_kernel(const uint64_t* __res
 template <typename P>
 __global__ void __launch_bounds__(256) decode_init_kernel(const uint64_t* __restrict__ src, const uint64_t* __restrict__ len,
                                                           const P* __restrict__ start, uint64_t z, uint64_t n,
-                                                          P* __restrict__ ptr, uint16_t* __restrict__ res,
-                                                          int* __restrict__ err) {
+                                                          P* __restrict__ ptr, int* __restrict__ err) {
     const uint64_t k = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned lane = threadIdx.x & 31;
     if (k >= z) return;
@@ -114,8 +118,7 @@ __global__ void __launch_bounds__(256) decode_init_kernel(const uint64_t* __rest
     if (l == 0) {
         if (lane == 0) {
             if (st >= n) *err = 2;
-            else if (sizeof(P) == 4) res[st] = (uint16_t)(0x100u | (uint32_t)(s & 0xFF));
-            else ptr[st] = (P)(RES64 | (s & 0xFF));
+            else ptr[st] = res_word<P>(s);
         }
         return;
     }
@@ -125,43 +128,36 @@ __global__ void __launch_bounds__(256) decode_init_kernel(const uint64_t* __rest
     }
     const uint64_t d = st - s;                    // a self-overlapping factor repeats T[s .. st) with period d
     if (l <= d) {
-        for (uint64_t i = lane; i < l; i += 32) {
-            ptr[st + i] = (P)(s + i);
-            if (sizeof(P) == 4) res[st + i] = 0;
-        }
+        for (uint64_t i = lane; i < l; i += 32) ptr[st + i] = (P)(s + i);
     } else {
-        for (uint64_t i = lane; i < l; i += 32) {
-            ptr[st + i] = (P)(s + i % d);
-            if (sizeof(P) == 4) res[st + i] = 0;
-        }
+        for (uint64_t i = lane; i < l; i += 32) ptr[st + i] = (P)(s + i % d);
     }
 }
 
 template <typename P>
-__global__ void __launch_bounds__(256) decode_round_kernel(uint64_t n, P* __restrict__ ptr, uint16_t* __restrict__ res,
-                                                           uint8_t* __restrict__ tile_done,
+__global__ void __launch_bounds__(256) decode_round_kernel(uint64_t n, P* __restrict__ ptr, uint8_t* __restrict__ tile_done,
                                                            unsigned long long* __restrict__ unresolved) {
     if (tile_done[blockIdx.x]) return;
     const uint64_t x0 = (uint64_t)blockIdx.x * DT;
+    P v[DT / 256];
     int pending = 0;
+#pragma unroll
+    for (int k = 0; k < DT / 256; k++) {          // own words, then the first hops, all in flight together
+        const uint64_t x = x0 + (uint64_t)k * 256 + threadIdx.x;
+        v[k] = x < n ? ptr[x] : res_word<P>(0);
+    }
+    P w[DT / 256];
+#pragma unroll
+    for (int k = 0; k < DT / 256; k++) w[k] = is_res<P>(v[k]) ? v[k] : *((volatile P*)&ptr[v[k]]);
+#pragma unroll
+    for (int k = 0; k < DT / 256; k++)            // second hops
+        if (!is_res<P>(w[k])) w[k] = *((volatile P*)&ptr[w[k]]);
 #pragma unroll
     for (int k = 0; k < DT / 256; k++) {
         const uint64_t x = x0 + (uint64_t)k * 256 + threadIdx.x;
-        if (x >= n) continue;
-        if (sizeof(P) == 4) {
-            if (res[x] == 0) {
-                const P y = ptr[x];
-                const uint16_t ry = *((volatile uint16_t*)&res[y]);
-                if (ry) res[x] = ry;
-                else { ptr[x] = *((volatile P*)&ptr[y]); pending++; }
-            }
-        } else {
-            const uint64_t v = ptr[x];
-            if (!(v & RES64)) {
-                const uint64_t vy = *((volatile P*)&ptr[v]);      // resolved: the value; else: the next hop
-                ptr[x] = (P)vy;
-                if (!(vy & RES64)) pending++;
-            }
+        if (x < n && !is_res<P>(v[k])) {
+            ptr[x] = w[k];
+            if (!is_res<P>(w[k])) pending++;
         }
     }
     const int any = __syncthreads_count(pending);
@@ -172,10 +168,15 @@ __global__ void __launch_bounds__(256) decode_round_kernel(uint64_t n, P* __rest
 }
 
 template <typename P>
-__global__ void decode_pack_kernel(const P* __restrict__ ptr, const uint16_t* __restrict__ res, uint64_t n,
-                                   uint8_t* __restrict__ out) {
-    const uint64_t x = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (x < n) out[x] = sizeof(P) == 4 ? (uint8_t)(res[x] & 0xFF) : (uint8_t)(ptr[x] & 0xFF);
+__global__ void decode_pack_kernel(const P* __restrict__ ptr, uint64_t n, uint8_t* __restrict__ out) {
+    const uint64_t x = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (x + 3 < n) {
+        uchar4 o;
+        o.x = (uint8_t)(ptr[x] & 0xFF); o.y = (uint8_t)(ptr[x + 1] & 0xFF); o.z = (uint8_t)(ptr[x + 2] & 0xFF); o.w = (uint8_t)(ptr[x + 3] & 0xFF);
+        *reinterpret_cast<uchar4*>(out + x) = o;
+    } else {
+        for (uint64_t k = x; k < n; k++) out[k] = (uint8_t)(ptr[k] & 0xFF);
+    }
 }
 
 __global__ void __launch_bounds__(256) bytes_differ_kernel(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b,
@@ -194,13 +195,11 @@ int decode_impl(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uint8_
     const uint64_t ntile = (n + DT - 1) / DT;
     sc.start.reserve((z + 1) * sizeof(P));
     sc.ptr.reserve(n * sizeof(P));
-    if (sizeof(P) == 4) sc.res.reserve(n);
     sc.tsum.reserve(nt + 2);
     sc.tile_done.reserve(ntile + 1);
     sc.cnt.reserve(2);
     P* start = reinterpret_cast<P*>(sc.start.get());
     P* ptr = reinterpret_cast<P*>(sc.ptr.get());
-    uint16_t* res = sc.res.get();
     int* err = reinterpret_cast<int*>(sc.cnt.get() + 1);
     CUDA_CHECK(cudaMemsetAsync(sc.cnt.get(), 0, 16, st));
     CUDA_CHECK(cudaMemsetAsync(sc.tile_done.get(), 0, ntile, st));
@@ -214,7 +213,7 @@ int decode_impl(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uint8_
     CUDA_CHECK(cudaMemcpyAsync(&h_total, sc.tsum.get() + nt, 8, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
     if (h_total != n) return -1;   // factor lengths do not add up to n
-    decode_init_kernel<P><<<ceil_div_u(z * 32, 256), 256, 0, st>>>(d_src, d_len, start, z, n, ptr, res, err);
+    decode_init_kernel<P><<<ceil_div_u(z * 32, 256), 256, 0, st>>>(d_src, d_len, start, z, n, ptr, err);
     KERNEL_CHECK();
     int h_err = 0;
     CUDA_CHECK(cudaMemcpyAsync(&h_err, err, 4, cudaMemcpyDeviceToHost, st));
@@ -224,7 +223,7 @@ int decode_impl(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uint8_
     bool done = false;
     for (int r = 0; r < 72 && !done; r++) {
         CUDA_CHECK(cudaMemsetAsync(sc.cnt.get(), 0, 8, st));
-        decode_round_kernel<P><<<(unsigned)ntile, 256, 0, st>>>(n, ptr, res, sc.tile_done, sc.cnt);
+        decode_round_kernel<P><<<(unsigned)ntile, 256, 0, st>>>(n, ptr, sc.tile_done, sc.cnt);
         KERNEL_CHECK();
         unsigned long long h_cnt = 0;
         CUDA_CHECK(cudaMemcpyAsync(&h_cnt, sc.cnt.get(), 8, cudaMemcpyDeviceToHost, st));
@@ -233,7 +232,7 @@ int decode_impl(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uint8_
         done = h_cnt == 0;
     }
     if (!done) return -4;          // did not converge: never emit unresolved bytes as zeros
-    decode_pack_kernel<P><<<ceil_div_u(n, 256), 256, 0, st>>>(ptr, res, n, d_out);
+    decode_pack_kernel<P><<<ceil_div_u((n + 3) / 4, 256), 256, 0, st>>>(ptr, n, d_out);
     KERNEL_CHECK();
     return 0;
 }
@@ -258,7 +257,7 @@ int decode_factors(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uin
     if (rounds) *rounds = 0;
     if (n == 0) return 0;
     static const bool force64 = getenv("LZ77SSS_FORCE_POS64") && getenv("LZ77SSS_FORCE_POS64")[0] == '1';
-    if (n < 0xFFFFFFF0ull && !force64) return decode_impl<uint32_t>(d_src, d_len, z, d_out, n, st, rounds, sc);
+    if (n < (uint64_t)RES32 && !force64) return decode_impl<uint32_t>(d_src, d_len, z, d_out, n, st, rounds, sc);
     return decode_impl<uint64_t>(d_src, d_len, z, d_out, n, st, rounds, sc);
 }
 

@@ -435,6 +435,7 @@ struct parse_ctx {
     uint64_t* tr_src;
     uint64_t* tr_len;
     uint32_t* changed;
+    uint32_t dbg;              // count link lookups and chain hops in changed[8..11]
 };
 
 __device__ __forceinline__ bool not_inserted(const uint32_t* __restrict__ bm, uint32_t rel) {
@@ -545,16 +546,20 @@ __device__ __forceinline__ void probe(const parse_ctx& C, const lce_view<pos_t>&
         if (e1 == NOLINK) {
             e1 = raw_pred(C, e, b, hint);
             C.prev[e] = e1;
+            if (C.dbg) atomicAdd(C.changed + 8, 1u);
         }
+        if (C.dbg) atomicAdd(C.changed + 11, 1u);
         bool found = false;
         while (e1 != NOENT) {
             const uint32_t q = e1 / 5u;
             if (q == rel) { occ = i; found = true; break; }        // an earlier pattern of this position wrote the bucket
             uint32_t nxt = C.prev[e1];                // next link, in flight together with the bitmap word
             if (!not_inserted(C.notins, q)) { occ = C.a0 + q; found = true; break; }
+            if (C.dbg) atomicAdd(C.changed + 10, 1u);
             if (nxt == NOLINK) {
-                nxt = raw_pred(C, e1, b, nullptr);
+                nxt = raw_pred(C, e1, b, hint);
                 C.prev[e1] = nxt;
+                if (C.dbg) atomicAdd(C.changed + 9, 1u);
             }
             e1 = nxt;
         }
@@ -1255,7 +1260,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         CUDA_CHECK(cudaMemcpyAsync(sc.Hc.get(), range->d_table_in, table_entries * 8, cudaMemcpyDeviceToDevice, st));
     else
         CUDA_CHECK(cudaMemsetAsync(sc.Hc.get(), 0, table_entries * 8, st));
-    sc.changed.reserve(8);
+    sc.changed.reserve(16);       // [8..11]: debug counters of the probes (LZ77SSS_DEBUG_ROUNDS)
     const bool dbg_rounds = getenv("LZ77SSS_DEBUG_ROUNDS") != nullptr;
     // lanes per parsed block (LZ77SSS_PARSE_GROUP = 8, 16 or 32).  Measured at 1 GiB: 65.9 / 74.5 / 80.2 ms of parse kernel
     // for 32 / 16 / 8 lanes: four times the blocks in flight do not help, a round is as long as its heaviest block
@@ -1542,6 +1547,8 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         C.marked = sc.marked;
         C.tr_cnt = sc.tr_cnt; C.tr_pos = sc.tr_pos; C.tr_src = sc.tr_src; C.tr_len = sc.tr_len;
         C.changed = sc.changed;
+        C.dbg = dbg_rounds ? 1u : 0u;
+        if (dbg_rounds) CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 8, 0, 16, st));
         block_state* d_exit = reinterpret_cast<block_state*>(sc.slice_exit.get());
         const unsigned gw = ceil_div_u((uint64_t)nb * 32, 128);
         auto launch_parse = [&](const parse_ctx& CC) {
@@ -1745,8 +1752,12 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 if (dbg_rounds) {
                     uint32_t d[2];
                     CUDA_CHECK(cudaMemcpy(d, sc.changed.get() + 3, 8, cudaMemcpyDeviceToHost));
-                    fprintf(stderr, "slice %llu round %llu: %u of %u blocks changed, first %u\n", (unsigned long long)a0,
-                            (unsigned long long)round, d[0], nb, d[1]);
+                    uint32_t c4[4];
+                    CUDA_CHECK(cudaMemcpy(c4, sc.changed.get() + 8, 16, cudaMemcpyDeviceToHost));
+                    CUDA_CHECK(cudaMemset(sc.changed.get() + 8, 0, 16));
+                    fprintf(stderr, "slice %llu round %llu: %u of %u blocks changed, first %u; lane probes %u, links looked up %u, chain hops %u, "
+                            "links looked up on a hop %u (incl. round 0 if this is round 1)\n", (unsigned long long)a0,
+                            (unsigned long long)round, d[0], nb, d[1], c4[3], c4[0], c4[2], c4[1]);
                 }
                 CUDA_CHECK(cudaMemcpyAsync(sc.notins_prev.get(), sc.notins.get(), nwords * 4, cudaMemcpyDeviceToDevice, st));
                 uint32_t d[2] = {0, 0};                 // blocks whose trace or exit changed, the first of them

@@ -219,7 +219,6 @@ void rks_fps(const uint8_t* d_text, const rks_state& R, uint64_t s, uint64_t cnt
 // returns 0, -1 (lengths do not add up to n), -2 (a source is not earlier text), -4 (no convergence)
 struct decode_scratch {
     dbuf<uint8_t> start, ptr, tile_done;   // start / ptr hold 32- or 64-bit words depending on n
-    dbuf<uint16_t> res;
     dbuf<uint64_t> tsum;
     dbuf<unsigned long long> cnt;
 };

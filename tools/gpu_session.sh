@@ -45,10 +45,14 @@ if has ncu_list; then
   gzip -f $O/${TAG}_launches.csv
 fi
 if has ncu_full; then
-  for k in parse_kernel gap_entries_kernel rs_scatter_kernel sss_cell_kernel dirty_from_bitmap_kernel decode_round_kernel; do
-    timeout 900 ncu --set full --clock-control none --import-source on -k regex:$k -c 3 -o $O/${TAG}_full_$k -f python tools/run_stats.py 256 dna 16 decode > $O/${TAG}_ncu_full_$k.log 2>&1
-    ncu -i $O/${TAG}_full_$k.ncu-rep --page raw --csv > $O/${TAG}_full_$k.csv 2>/dev/null
-    rm -f $O/${TAG}_full_$k.ncu-rep
+  # one ncu --set full capture per hot kernel (3 launches each) of a 256 MiB run; the raw pages as csv, the reports dropped
+  for spec in "parse:parse_kernel" "entries:gap_entries_sparse_kernel" "scatter32:rs_scatter_kernel<unsigned int, 512" "sss:sss_cell_kernel" \
+              "dirty:dirty_from_bitmap_kernel" "decode:decode_round_kernel" "splice:splice_repair_kernel" "repair:repair_entries_kernel"; do
+    tag=${spec%%:*}; k=${spec#*:}
+    timeout 600 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k "regex:$k" -c 3 \
+      -o $O/${TAG}_full_$tag -f python tools/run_stats.py 256 dna 16 decode > $O/${TAG}_ncu_full_$tag.log 2>&1
+    ncu -i $O/${TAG}_full_$tag.ncu-rep --page raw --csv > $O/${TAG}_full_$tag.csv 2>/dev/null
+    rm -f $O/${TAG}_full_$tag.ncu-rep
   done
   ls -la $O | tail -12
 fi

@@ -9,7 +9,10 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "launch__occupancy_limit_registers", "launch__grid_size"]
 rep = sys.argv[1]
 extra = sys.argv[2:]
-rows = list(csv.reader(subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout.splitlines()))
+if rep.endswith(".csv"):      # the raw page saved as csv on the GPU box
+    rows = list(csv.reader([l for l in open(rep) if not l.startswith("==")]))
+else:
+    rows = list(csv.reader(subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout.splitlines()))
 h = rows[0]
 for v in rows[2:]:
     print("==", v[h.index("Kernel Name")][:80])
