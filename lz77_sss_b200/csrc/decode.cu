@@ -7,7 +7,7 @@
 //      source (period d = start - src < len) points every byte into the period in front of it, so a run costs one hop,
 //   3. pointer jumping: one word per byte holds either the byte's value (resolved) or the position it copies from; an
 //      unresolved byte reads its source's word and adopts it (the value, or the source's own source: the chain length
-//      halves), twice per round.  Tiles of 1024 bytes that are completely resolved are skipped.
+//      halves every round).  Tiles of 1024 bytes that are completely resolved are skipped.
 //      n < 2^32 - 256: 32-bit words, resolved = 0xFFFFFF00 | value; larger n: 64-bit words, bit 63 = resolved.
 //      The word is read and written whole, so "resolved" and the value are seen together.
 // Algorithmic bytes: 2n + z*sizeof(factor); a hop moves one gathered word per unresolved byte, a round
@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(256) decode_init_kernel(const uint64_t* __rest
     }
 }
 
-template <typename P>
+template <typename P, int HOPS>
 __global__ void __launch_bounds__(256) decode_round_kernel(uint64_t n, P* __restrict__ ptr, uint8_t* __restrict__ tile_done,
                                                            unsigned long long* __restrict__ unresolved) {
     if (tile_done[blockIdx.x]) return;
@@ -149,9 +149,11 @@ __global__ void __launch_bounds__(256) decode_round_kernel(uint64_t n, P* __rest
     P w[DT / 256];
 #pragma unroll
     for (int k = 0; k < DT / 256; k++) w[k] = is_res<P>(v[k]) ? v[k] : *((volatile P*)&ptr[v[k]]);
+    if (HOPS > 1) {
 #pragma unroll
-    for (int k = 0; k < DT / 256; k++)            // second hops
-        if (!is_res<P>(w[k])) w[k] = *((volatile P*)&ptr[w[k]]);
+        for (int k = 0; k < DT / 256; k++)        // second hops
+            if (!is_res<P>(w[k])) w[k] = *((volatile P*)&ptr[w[k]]);
+    }
 #pragma unroll
     for (int k = 0; k < DT / 256; k++) {
         const uint64_t x = x0 + (uint64_t)k * 256 + threadIdx.x;
@@ -220,10 +222,13 @@ int decode_impl(const uint64_t* d_src, const uint64_t* d_len, uint64_t z, uint8_
     CUDA_CHECK(cudaStreamSynchronize(st));
     if (h_err) return -2;
     // the longest chain has fewer than n hops and halves every round
+    // (two hops per round, LZ77SSS_DECODE_HOPS=2, save a round but gather more words in total: measured slower)
+    static const bool two_hops = getenv("LZ77SSS_DECODE_HOPS") && getenv("LZ77SSS_DECODE_HOPS")[0] == '2';
     bool done = false;
     for (int r = 0; r < 72 && !done; r++) {
         CUDA_CHECK(cudaMemsetAsync(sc.cnt.get(), 0, 8, st));
-        decode_round_kernel<P><<<(unsigned)ntile, 256, 0, st>>>(n, ptr, sc.tile_done, sc.cnt);
+        if (two_hops) decode_round_kernel<P, 2><<<(unsigned)ntile, 256, 0, st>>>(n, ptr, sc.tile_done, sc.cnt);
+        else decode_round_kernel<P, 1><<<(unsigned)ntile, 256, 0, st>>>(n, ptr, sc.tile_done, sc.cnt);
         KERNEL_CHECK();
         unsigned long long h_cnt = 0;
         CUDA_CHECK(cudaMemcpyAsync(&h_cnt, sc.cnt.get(), 8, cudaMemcpyDeviceToHost, st));

@@ -194,6 +194,9 @@ __global__ void __launch_bounds__(160) gap_entries_sparse_kernel(const uint8_t* 
     __shared__ uint32_t sNeed[SP_WORDS], sRank[SP_WORDS + 1];
     __shared__ uint16_t sAct[SP_SEGS];
     __shared__ uint32_t s_nact;
+    // bucket ids of the 32 segments of one iteration, [segment][5 * position + entry slot] (pitch 321: no bank conflicts):
+    // the five pattern warps fill it, then all threads write a segment's entries as consecutive words
+    __shared__ uint32_t sK[32][5 * GE_SEG + 1];
     const int tid = threadIdx.x, lane = tid & 31, x = tid >> 5;
     const uint64_t t0 = (uint64_t)blockIdx.x * SP_TILE;                   // tile start, slice-relative
     const uint32_t in_tile = cnt - t0 < (uint64_t)SP_TILE ? (uint32_t)(cnt - t0) : (uint32_t)SP_TILE;
@@ -231,7 +234,9 @@ __global__ void __launch_bounds__(160) gap_entries_sparse_kernel(const uint8_t* 
     const uint64_t L = hp.L[x], base = hp.base[x];
     const m107* __restrict__ nbt = hp.nbtab + x * 256;
     const uint64_t c0 = 5ull * first, e0 = 5 * t0;
-    for (uint32_t ai = lane; ai < nact; ai += 32) {
+    for (uint32_t abase = 0; abase < nact; abase += 32) {
+      const uint32_t ai = abase + lane;
+      if (ai < nact) {
         const int sg = sAct[ai];
         const uint64_t need = (uint64_t)sNeed[2 * sg] | ((uint64_t)sNeed[2 * sg + 1] << 32);
         const int lo = __ffsll((long long)need) - 1, hi = 63 - __clzll((long long)need);
@@ -240,7 +245,6 @@ __global__ void __launch_bounds__(160) gap_entries_sparse_kernel(const uint8_t* 
         m107 fp;
         fp.lo = fp.hi = 0;
         bool live = false;                                                // fp holds the window at the current position
-        uint32_t rank = sRank[2 * sg];
         for (int j = lo; j <= hi; j++) {
             const uint64_t pos = pos0 + j;
             const bool fits = pos + L < n;
@@ -253,15 +257,7 @@ __global__ void __launch_bounds__(160) gap_entries_sparse_kernel(const uint8_t* 
                 }
                 live = true;
             }
-            if ((need >> j) & 1ull) {
-                const uint32_t key = fits ? (uint32_t)(fp.lo & hp.mask) : hp.invalid_key;
-                const uint64_t o = 5ull * (uint64_t)(sg * GE_SEG + j) + (4 - x);
-                keys[c0 + 5ull * rank + (4 - x)] = key;
-                vals[c0 + 5ull * rank + (4 - x)] = (uint32_t)(e0 + o);
-                tkeys[e0 + o] = key;
-                prevs[e0 + o] = NOLINK;
-                rank++;
-            }
+            if ((need >> j) & 1ull) sK[lane][5 * j + (4 - x)] = fits ? (uint32_t)(fp.lo & hp.mask) : hp.invalid_key;
             if (fits && j < hi) {
                 if (!((need >> (j + 1)) & 1ull) && __popcll(need >> (j + 1)) && __ffsll((long long)(need >> (j + 1))) - 1 > (int)L) {
                     live = false;                                         // a long stretch without needed positions: start over
@@ -276,6 +272,28 @@ __global__ void __launch_bounds__(160) gap_entries_sparse_kernel(const uint8_t* 
                 fp = muladd107(fp, base, infl);
             }
         }
+      }
+      __syncthreads();
+      // write-out, segment by segment: thread t takes the slots t, t + 160 of the segment's 5 x 64; the entries of a run of
+      // needed positions are consecutive words in all four arrays
+      const uint32_t nseg = nact - abase < 32u ? nact - abase : 32u;
+      for (uint32_t sl = 0; sl < nseg; sl++) {
+          const int sg = sAct[abase + sl];
+          const uint64_t need = (uint64_t)sNeed[2 * sg] | ((uint64_t)sNeed[2 * sg + 1] << 32);
+          const uint32_t rank0 = sRank[2 * sg];
+          for (int o = tid; o < 5 * GE_SEG; o += 160) {
+              const int j = o / 5, y = o - 5 * j;
+              if (!((need >> j) & 1ull)) continue;
+              const uint32_t r = rank0 + (uint32_t)__popcll(need & ((1ull << j) - 1ull));
+              const uint32_t key = sK[sl][o];
+              const uint64_t od = 5ull * (uint64_t)(sg * GE_SEG) + (uint64_t)o;
+              keys[c0 + 5ull * r + y] = key;
+              vals[c0 + 5ull * r + y] = (uint32_t)(e0 + od);
+              tkeys[e0 + od] = key;
+              prevs[e0 + od] = NOLINK;
+          }
+      }
+      __syncthreads();
     }
 }
 
