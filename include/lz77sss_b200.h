@@ -128,6 +128,10 @@ int lz77sss_factorize_approximate_device(lz77sss_handle* h, const uint8_t* d_tex
 int lz77sss_shard_prepare(lz77sss_handle* h, const uint8_t* d_text, const uint8_t* host_text, uint64_t n);
 int lz77sss_shard_table_entries(lz77sss_handle* h, uint64_t* entries);
 int lz77sss_shard_entry_guess(lz77sss_handle* h, uint64_t pos, uint64_t state[4]);
+/* ranges of about equal work for `parts` ranks: bounds[0] = 0 <= bounds[1] <= ... <= bounds[parts] = n, multiples of `align`.
+ * The work of a range is dominated by its gap bytes (the bytes outside the phrases of build_LPF_*), so equal byte counts are
+ * not equal work: the first copy of a repeated sequence is one long gap. */
+int lz77sss_shard_split(lz77sss_handle* h, uint32_t parts, uint64_t align, uint64_t* bounds);
 /* optional, before the first lz77sss_shard_parse of a range: hash and sort its gap-index entries (kept for the parses) and
  * write a GUESS of the range's table (last position per bucket among the positions the phrase list alone says are
  * inserted); exchanged once, it gives the later ranges a nearly right table for their first parse */

@@ -25,7 +25,7 @@ EXPORTS = [
     "lz77sss_device_text_free", "lz77sss_factorize_approximate_device", "lz77sss_decode", "lz77sss_build_sss",
     "lz77sss_time_sss_kernel", "lz77sss_get_stats", "lz77sss_get_sss", "lz77sss_get_sa_s", "lz77sss_get_lcp_s",
     "lz77sss_get_lpf", "lz77sss_lce_batch", "lz77sss_sink_emit",
-    "lz77sss_shard_prepare", "lz77sss_shard_table_entries", "lz77sss_shard_entry_guess", "lz77sss_shard_parse",
+    "lz77sss_shard_prepare", "lz77sss_shard_table_entries", "lz77sss_shard_entry_guess", "lz77sss_shard_split", "lz77sss_shard_parse",
     "lz77sss_shard_factors", "lz77sss_shard_finish", "lz77sss_shard_index",
     "lz77sss_rks_create", "lz77sss_rks_destroy", "lz77sss_rks_table", "lz77sss_rks_fps", "lz77sss_rks_substring",
     "lz77sss_rks_time_build", "lz77sss_time_decode", "lz77sss_kernel_profile", "lz77sss_kernel_profile_get",
@@ -98,6 +98,7 @@ def lib():
         L.lz77sss_shard_prepare.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
         L.lz77sss_shard_table_entries.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
         L.lz77sss_shard_entry_guess.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_shard_split.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.POINTER(C.c_uint64)]
         L.lz77sss_shard_parse.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p,
                                           C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.lz77sss_shard_index.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
@@ -313,6 +314,12 @@ class Factorizer:
         e = C.c_uint64(0)
         _check(lib().lz77sss_shard_table_entries(self._h, C.byref(e)))
         return int(e.value)
+
+    def shard_split(self, parts, align=2048):
+        """Ranges of about equal work (gap bytes weigh 16x phrase bytes): [(beg, end)] * parts."""
+        b = (C.c_uint64 * (parts + 1))()
+        _check(lib().lz77sss_shard_split(self._h, parts, align, b))
+        return [(int(b[r]), int(b[r + 1])) for r in range(parts)]
 
     def shard_entry_guess(self, pos):
         st = (C.c_uint64 * 4)()

@@ -1451,6 +1451,45 @@ int lz77sss_shard_entry_guess(lz77sss_handle* h, uint64_t pos, uint64_t state[4]
     return LZ77SSS_OK;
 }
 
+int lz77sss_shard_split(lz77sss_handle* h, uint32_t parts, uint64_t align, uint64_t* bounds) {
+    NEED_PREPARED();
+    if (!bounds || !parts || !align) return fail(LZ77SSS_E_ARG, "bad argument");
+    // The work of a range is its gap bytes (hashed, sorted, probed); the inside of a phrase costs a bitmap bit.  Cut where
+    // the running weight (16 per gap byte, 1 per phrase byte) passes k / parts of the total, rounded to `align`.
+    const phrase_list ML{h->ml_buf.p, h->ml_count};
+    const uint64_t n = h->n, m = ML.size() - 1;        // (the last entry is the sentinel)
+    auto weight_to = [&](uint64_t k, uint64_t& gaps, uint64_t& phr, uint64_t& at) {   // after phrase k: totals up to its end
+        gaps += ML[k].beg > at ? ML[k].beg - at : 0;
+        phr += ML[k].end - std::max(ML[k].beg, at);
+        at = std::max(at, (uint64_t)ML[k].end);
+    };
+    uint64_t gaps = 0, phr = 0, at = 0;
+    for (uint64_t k = 0; k < m; k++) weight_to(k, gaps, phr, at);
+    gaps += n > at ? n - at : 0;
+    const long double total = 16.0L * gaps + phr;
+    bounds[0] = 0;
+    uint64_t g2 = 0, p2 = 0, at2 = 0, k = 0;
+    for (uint32_t r = 1; r < parts; r++) {
+        const long double want = total * r / parts;
+        while (k < m) {
+            uint64_t g3 = g2, p3 = p2, a3 = at2;
+            weight_to(k, g3, p3, a3);
+            if (16.0L * g3 + p3 > want) break;
+            g2 = g3; p2 = p3; at2 = a3; k++;
+        }
+        // inside the gap in front of phrase k, or inside phrase k: interpolate
+        uint64_t cut = at2;
+        const long double have = 16.0L * g2 + p2;
+        const uint64_t gap_len = k < m && ML[k].beg > at2 ? ML[k].beg - at2 : (k == m ? n - at2 : 0);
+        if (have + 16.0L * gap_len >= want) cut = at2 + (uint64_t)((want - have) / 16.0L);
+        else cut = at2 + gap_len + (uint64_t)(want - have - 16.0L * gap_len);
+        cut = std::min(n, (cut + align / 2) / align * align);
+        bounds[r] = std::max(cut, bounds[r - 1]);
+    }
+    bounds[parts] = n;
+    return LZ77SSS_OK;
+}
+
 int lz77sss_shard_parse(lz77sss_handle* h, uint64_t beg, uint64_t end, const uint64_t entry[4], const uint64_t* d_table_in,
                         uint64_t* d_table_out, uint64_t exit_state[4], uint64_t* num_factors) {
     NEED_PREPARED();

@@ -87,6 +87,9 @@ class CudaBackend:
     def entry_guess(self, pos):
         return self.F.shard_entry_guess(pos)
 
+    def split(self, world):
+        return self.F.shard_split(world)
+
     def index(self, beg, end, table_guess):
         torch.cuda.synchronize(self.device)
         self.F.shard_index(beg, end, table_guess.data_ptr())
@@ -147,11 +150,25 @@ class ThreadComm:
         return any(int(g.item()) for g in got)
 
 
+_PINNED = {}
+
+
+def _pinned(key, numel):
+    """Grow-only pinned int64 staging buffers (allocating pinned memory costs milliseconds per call)."""
+    t = _PINNED.get(key)
+    if t is None or t.numel() < numel:
+        t = torch.empty(max(int(numel * 1.25), 1024), dtype=torch.int64, pin_memory=True)
+        _PINNED[key] = t
+    return t
+
+
 def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int, device, group=None, max_passes=None,
                       log=None, comm=None):
     """Steps 3 and 4 of the module docstring.  Returns (src, len, passes) on rank 0 and (None, None, passes) elsewhere."""
     comm = comm or TorchComm(rank, world, device, group)
-    ranges = split_ranges(n, world)
+    # ranges of equal work where the backend can tell (gap bytes are the work: equal byte counts leave the rank that holds
+    # the first copy of a repeated sequence as the straggler), else of equal length
+    ranges = backend.split(world) if world > 1 and hasattr(backend, "split") else split_ranges(n, world)
     beg, end = ranges[rank]
     first_entry = (0, 0, 0, 1)
     entry = first_entry if rank == 0 or beg >= n else backend.entry_guess(beg)
@@ -160,17 +177,21 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
     local = backend.new_table(table_entries)
     # pass 0 (backends that can): index the own range and exchange guessed tables, so that the first parse of the
     # later ranges already sees nearly the table it will end up with
+    import time
+    t_i = time.perf_counter()
     if world > 1 and hasattr(backend, "index"):
         if beg < end:
             backend.index(beg, end, local)
+        t_j = time.perf_counter()
         guesses = comm.all_gather(local)
         for r in range(rank):
             torch.maximum(table_in, guesses[r], out=table_in)
+        if log is not None:
+            log.append({"index_ms": round((t_j - t_i) * 1e3, 2), "guess_exchange_ms": round((time.perf_counter() - t_j) * 1e3, 2)})
     exit_state = entry
     passes = 0
     need_parse = True
     limit = max_passes if max_passes is not None else world + 2
-    import time
     while True:
         t_a = time.perf_counter()
         if need_parse:
@@ -204,6 +225,7 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
             entry = tuple(new_entry)
             table_in.copy_(new_in)
     # step 4: factors of the own range (+ the tail on the last non-empty range), gathered on rank 0
+    t_c = time.perf_counter()
     if beg < end:
         src, ln = backend.factors()
     else:
@@ -216,13 +238,34 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
         return src, ln, passes
     counts = [int(c.item()) for c in comm.all_gather(torch.tensor([src.size], dtype=torch.int64, device=device))]
     zmax = max(max(counts), 1)
-    mine = torch.zeros(2 * zmax, dtype=torch.int64, device=device)
+    cuda = torch.device(device).type == "cuda"
+    mine = torch.empty(2 * zmax, dtype=torch.int64, device=device)
     if src.size:
-        mine[:src.size] = torch.from_numpy(src.astype(np.int64)).to(device)
-        mine[zmax:zmax + src.size] = torch.from_numpy(ln.astype(np.int64)).to(device)
+        # (uint64 -> int64 is a view; on a GPU the arrays go through a pinned staging buffer that is kept between calls)
+        for k, a in enumerate((src, ln)):
+            h = torch.from_numpy(a.view(np.int64))
+            if cuda:
+                stage = _pinned(("up", k), a.size)
+                stage[:a.size].copy_(h)
+                h = stage[:a.size]
+            mine[k * zmax:k * zmax + a.size].copy_(h, non_blocking=cuda)
     parts = comm.all_gather(mine)
     if rank != 0:
+        if log is not None:
+            log.append({"gather_ms": round((time.perf_counter() - t_c) * 1e3, 2)})
         return None, None, passes
-    srcs = [parts[r][:counts[r]].cpu().numpy().astype(np.uint64) for r in range(world)]
-    lens = [parts[r][zmax:zmax + counts[r]].cpu().numpy().astype(np.uint64) for r in range(world)]
-    return np.concatenate(srcs), np.concatenate(lens), passes
+    total = sum(counts)
+    if cuda:   # one pinned buffer per output array, kept between calls: the returned arrays are views of it
+        outs = [_pinned(("down", k), total) for k in range(2)]
+    else:
+        outs = [torch.empty(max(total, 1), dtype=torch.int64) for _ in range(2)]
+    at = 0
+    for r in range(world):
+        for k in range(2):
+            outs[k][at:at + counts[r]].copy_(parts[r][k * zmax:k * zmax + counts[r]], non_blocking=cuda)
+        at += counts[r]
+    if cuda:
+        torch.cuda.synchronize(device)
+    if log is not None:
+        log.append({"gather_ms": round((time.perf_counter() - t_c) * 1e3, 2)})
+    return outs[0][:total].numpy().view(np.uint64), outs[1][:total].numpy().view(np.uint64), passes
