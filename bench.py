@@ -248,6 +248,7 @@ def run_sharded(args, world, rank, local, barrier):
         stats["d2h"] = st["d2h_bytes"]
         if rank == 0:
             stats["z"] = int(src.size)
+            stats["hash"] = None if not stats.get("want_hash") else stream_hash(src, ln)
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -272,6 +273,20 @@ def run_sharded(args, world, rank, local, barrier):
     dist.all_reduce(lt)
     ms_e2e = timed(lambda: step(True), args.steps, max(1, args.warmup - 2))
     clocks = sampler.stop()
+    # outside the timed region: the sharded factor stream against the single-GPU path on rank 0's GPU (same text and parameters)
+    stats["want_hash"] = True
+    step(False)
+    sharded_ok = None
+    if rank == 0:
+        with capi.Factorizer(tau=args.tau, num_threads=args.threads, gap_bases=capi.DEFAULT_GAP_BASES, device=local) as G:
+            s1, l1 = G.factorize(text)
+        sharded_ok = bool(int(s1.size) == stats["z"] and stream_hash(s1, l1) == stats["hash"])
+        if not sharded_ok:
+            print(f"sharded stream: {stats['z']} factors, single GPU: {int(s1.size)}", file=sys.stderr, flush=True)
+        del s1, l1
+    barrier()
+    if rank == 0 and not sharded_ok:
+        raise RuntimeError("the sharded factor stream differs from the single-GPU path: no number is reported")
     st = F.stats()
     k_ms, s_size = F.time_sss_kernel(C.c_void_p(d_ptr), n, iters=10)
     hb = torch.tensor([stats["h2d"], stats["d2h"]], device="cuda", dtype=torch.int64)
@@ -294,6 +309,8 @@ def run_sharded(args, world, rank, local, barrier):
                            f"front, gap index + greedy emission split by text range, tables and exit states "
                            f"all-gathered between passes ({stats['passes']} passes); every rank also holds the whole text in host memory",
             "factors": stats["z"], "size_sss": int(st["size_sss"]),
+            "parity_checked": sharded_ok, "parity": {"against": "the single-GPU path on rank 0 (itself compared with oracle/_ref at N = 1)",
+                                                     "sha256_equal": sharded_ok},
             "cpu_baseline": None, "cpu_baseline_note": "timed at N = 1 only (bench.py --gpus 1 and --impl reference)",
             "e2e": {"value": (n / MIB) / (ms_e2e / 1e3), "unit": "MiB/s", "h2d_bytes_per_step": int(hb[0].item()),
                     "d2h_bytes_per_step": int(hb[1].item()), "ms_per_step": ms_e2e},

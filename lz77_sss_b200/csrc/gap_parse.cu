@@ -1446,6 +1446,10 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
         if (have_sorted) {
             if (sparse) E = K->E;                     // a retained sparse slice: its skip bitmap, index and repair lists stand
             vals = K->vals_in_v0 ? sc.v0.get() : sc.v1.get();
+            // an index that an index-only pass built (sharded runs) did not know the entry state of this slice: the
+            // positions a gap factor reaching into it has inserted get their entries in front of the first parse
+            // (a slice that was parsed before asks for them where it resumes, below)
+            if (sparse && !have_parse) head_pending = sparse_head;
         } else {
             built_index bi;
             if (pf_valid && pf_a0 == a0 && attempt == pf_attempt) {

@@ -154,7 +154,8 @@ _PINNED = {}
 
 
 def _pinned(key, numel):
-    """Grow-only pinned int64 staging buffers (allocating pinned memory costs milliseconds per call)."""
+    """Grow-only pinned int64 staging buffers (allocating pinned memory costs milliseconds per call); keyed by rank because
+    the tests run virtual ranks as threads of one process."""
     t = _PINNED.get(key)
     if t is None or t.numel() < numel:
         t = torch.empty(max(int(numel * 1.25), 1024), dtype=torch.int64, pin_memory=True)
@@ -245,7 +246,7 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
         for k, a in enumerate((src, ln)):
             h = torch.from_numpy(a.view(np.int64))
             if cuda:
-                stage = _pinned(("up", k), a.size)
+                stage = _pinned((rank, "up", k), a.size)
                 stage[:a.size].copy_(h)
                 h = stage[:a.size]
             mine[k * zmax:k * zmax + a.size].copy_(h, non_blocking=cuda)
@@ -256,7 +257,7 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
         return None, None, passes
     total = sum(counts)
     if cuda:   # one pinned buffer per output array, kept between calls: the returned arrays are views of it
-        outs = [_pinned(("down", k), total) for k in range(2)]
+        outs = [_pinned((rank, "down", k), total) for k in range(2)]
     else:
         outs = [torch.empty(max(total, 1), dtype=torch.int64) for _ in range(2)]
     at = 0

@@ -264,6 +264,22 @@ def test_sharded_greedy_naive_and_small_slices(capi, oracle, monkeypatch):
             assert _eq(src, rs) and _eq(ln, rl), (name, fm)
 
 
+@pytest.mark.parametrize("slice_len", [4096, 7777, 12345, 20011])
+def test_sharded_gap_factor_into_a_slice_indexed_ahead(capi, oracle, monkeypatch, slice_len):
+    """A sharded run indexes its slices before it knows their entry states (index-only pass).  A gap factor that reaches
+    into such a slice inserts positions the sparse index has no entries for: they are added in front of the slice's first
+    parse.  (At 1 GiB with ranges of equal work, a later factor copied from an older occurrence without this.)"""
+    monkeypatch.setenv("LZ77SSS_SLICE_LEN", str(slice_len))
+    tau = 64
+    _need_ref(oracle, tau)
+    for name in ("rep", "dna"):
+        text = _texts()[name]
+        rs, rl, bases, _ = oracle.ref_factorize(text, tau, p=1)
+        for world in (2, 3):
+            src, ln, _ = _sharded_virtual(capi, text, world, tau, bases)
+            assert _eq(src, rs) and _eq(ln, rl), (name, world, slice_len)
+
+
 def test_lnf_regression_dna52(capi, oracle):
     """The input on which a fused two-sided candidate kernel faulted (see lpf.cu, all_candidates_kernel)."""
     tau = 64
