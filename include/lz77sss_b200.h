@@ -158,6 +158,17 @@ int lz77sss_rks_table(lz77sss_rks* r, uint32_t* out, uint64_t cap, uint64_t* cou
 int lz77sss_rks_fps(lz77sss_rks* r, uint64_t s, uint32_t* out, uint64_t cap, uint64_t* count);
 /* batched rabin_karp_substring::substring(pos, len) (:223-239) */
 int lz77sss_rks_substring(lz77sss_rks* r, const uint64_t* pos, const uint64_t* len, uint64_t nq, uint32_t* out);
+/* The table of lz77sss_rks_table WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * d_text: DEVICE pointer to T[0..n), 16-byte aligned, zero bytes behind the text up to the next multiple of 16;
+ * d_table: DEVICE array of ceil(n / 16) u32, 16-byte aligned; stream: a cudaStream_t (NULL = the default stream) of the
+ * CURRENT device.  The call needs no handle, enqueues a memset and one kernel on `stream` and returns without waiting;
+ * it calls no cudaMalloc / cudaFree.  The kernel's look-back scratch is a static device array of
+ * LZ77SSS_RKS_NOALLOC_MAX_BYTES / 16384 words of 8 bytes (512 KiB, held by every GPU that loads the library until the
+ * process ends): n > LZ77SSS_RKS_NOALLOC_MAX_BYTES is rejected with LZ77SSS_E_UNSUPPORTED.  All calls share that array
+ * (cleared in front of every launch): calls that overlap on one GPU (two streams without ordering) race on it. */
+#define LZ77SSS_RKS_NOALLOC_MAX_BYTES (1ull << 30)
+int lz77sss_rks_table_noalloc(const uint8_t* d_text, uint64_t n, uint64_t base, uint32_t* d_table, void* stream);
 /* re-run the build `iters` times on the resident text; mean time (CUDA events on the library's stream) */
 int lz77sss_rks_time_build(lz77sss_rks* r, int iters, double* ms_out, uint64_t* launches_out);
 

@@ -27,7 +27,7 @@ EXPORTS = [
     "lz77sss_get_lpf", "lz77sss_lce_batch", "lz77sss_sink_emit",
     "lz77sss_shard_prepare", "lz77sss_shard_table_entries", "lz77sss_shard_entry_guess", "lz77sss_shard_split", "lz77sss_shard_parse",
     "lz77sss_shard_factors", "lz77sss_shard_finish", "lz77sss_shard_index",
-    "lz77sss_rks_create", "lz77sss_rks_destroy", "lz77sss_rks_table", "lz77sss_rks_fps", "lz77sss_rks_substring",
+    "lz77sss_rks_create", "lz77sss_rks_destroy", "lz77sss_rks_table", "lz77sss_rks_table_noalloc", "lz77sss_rks_fps", "lz77sss_rks_substring",
     "lz77sss_rks_time_build", "lz77sss_time_decode", "lz77sss_kernel_profile", "lz77sss_kernel_profile_get",
 ]
 
@@ -108,6 +108,7 @@ def lib():
         L.lz77sss_rks_destroy.argtypes = [C.c_void_p]
         L.lz77sss_rks_destroy.restype = None
         L.lz77sss_rks_table.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_rks_table_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
         L.lz77sss_rks_fps.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.lz77sss_rks_substring.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.lz77sss_rks_time_build.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]

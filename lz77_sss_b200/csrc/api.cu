@@ -1565,6 +1565,20 @@ int lz77sss_rks_create(lz77sss_handle* h, const uint8_t* text, uint64_t n, uint6
     });
 }
 
+int lz77sss_rks_table_noalloc(const uint8_t* d_text, uint64_t n, uint64_t base, uint32_t* d_table, void* stream) {
+    if ((!d_text || !d_table) && n) return fail(LZ77SSS_E_ARG, "null argument");
+    if (base < 257 || base > 0x7FFFFFFEull) return fail(LZ77SSS_E_ARG, "base must lie in [257, 2^31 - 2] (rabin_karp_substring.hpp:92-96)");
+    if (n > RKS_NOALLOC_MAX_BYTES)
+        return fail(LZ77SSS_E_UNSUPPORTED, "lz77sss_rks_table_noalloc: n exceeds LZ77SSS_RKS_NOALLOC_MAX_BYTES (2^30): the scratch is a "
+                                            "static device array; use lz77sss_rks_create for longer texts");
+    if ((reinterpret_cast<uintptr_t>(d_text) & 15) || (reinterpret_cast<uintptr_t>(d_table) & 15))
+        return fail(LZ77SSS_E_ARG, "lz77sss_rks_table_noalloc: d_text and d_table must be 16-byte aligned");
+    return guarded([&]() {
+        rks_build_noalloc(d_text, n, (uint32_t)base, d_table, static_cast<cudaStream_t>(stream));   // (no allocation, no synchronisation)
+        return LZ77SSS_OK;
+    });
+}
+
 void lz77sss_rks_destroy(lz77sss_rks* r) {
     if (!r) return;
     cudaSetDevice(r->h->cfg.device);

@@ -13,6 +13,8 @@
 // to the reference's for the same base.  The table has one entry per 16 bytes whatever sampling rate the caller names;
 // the reference's `fps` vector for a rate s is derived from it (rks_fps_kernel) for the parity tests.
 // HBM bytes of the build: n read + 4 * n / 16 written = the algorithmic bytes.
+#include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -290,6 +292,72 @@ void rks_build(const uint8_t* d_text, uint64_t n, uint32_t base, rks_state& R, c
     if (per_sm > RK_CTAS_PER_SM) per_sm = RK_CTAS_PER_SM;
     const uint32_t grid = std::min<uint64_t>(ntiles, (uint64_t)sms * per_sm);
     rks_build_kernel<<<grid, RK_NW * 32, 0, st>>>(d_text, R.ngran, ntiles, c, R.pf, R.status.get());
+    KERNEL_CHECK();
+}
+
+// ---- the build without any allocation (lz77sss_rks_table_noalloc) ---------------------------------------------------------
+// The look-back states of the tiles live in a file-scope device array instead of a cudaMalloc'ed buffer: every GPU that loads
+// the library holds these RKS_NOALLOC_MAX_TILES * 8 bytes (512 KiB) until the process ends.  All calls share the array and it
+// keeps the last call's contents: it is cleared on the caller's stream in front of every launch, and two calls that overlap
+// on the GPU (different streams, no ordering between them) race on it.
+static __device__ __align__(256) unsigned long long g_rks_noalloc_status[RKS_NOALLOC_MAX_BYTES / RK_TILE];
+
+void rks_build_noalloc(const uint8_t* d_text, uint64_t n, uint32_t base, uint32_t* d_out, cudaStream_t st) {
+    if (n > RKS_NOALLOC_MAX_BYTES)
+        throw std::invalid_argument("rks_build_noalloc: n exceeds the static scratch (RKS_NOALLOC_MAX_BYTES = 2^30 bytes of text)");
+    const uint64_t ngran = (n + RK_G - 1) / RK_G;
+    if (ngran == 0) return;
+    const uint32_t ntiles = ceil_div_u(ngran, RK_TILE_G);
+    // In host code the array's name is only a stand-in: its device address is asked for once per device, with that device
+    // current, and kept.
+    constexpr int MAX_DEV = 64;
+    static unsigned long long* addr[MAX_DEV] = {};
+    static int sms_of[MAX_DEV] = {};
+    static int per_sm_of[MAX_DEV] = {};
+    static std::mutex mu;
+    int dev = 0;
+    CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEV) throw std::invalid_argument("rks_build_noalloc: device ordinal out of range");
+    unsigned long long* status = nullptr;
+    int sms = 0, per_sm = 0;
+    {
+        std::lock_guard<std::mutex> g(mu);
+        if (!addr[dev]) {
+            void* p = nullptr;
+            CUDA_CHECK(cudaGetSymbolAddress(&p, g_rks_noalloc_status));
+            CUDA_CHECK(cudaDeviceGetAttribute(&sms_of[dev], cudaDevAttrMultiProcessorCount, dev));
+            CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_of[dev], rks_build_kernel, RK_NW * 32, 0));
+            addr[dev] = static_cast<unsigned long long*>(p);
+        }
+        status = addr[dev];
+        sms = sms_of[dev];
+        per_sm = per_sm_of[dev];
+    }
+    if (per_sm < 1) throw std::runtime_error("rks_build_noalloc: kernel does not fit an SM");
+    if (per_sm > RK_CTAS_PER_SM) per_sm = RK_CTAS_PER_SM;
+    CUDA_CHECK(cudaMemsetAsync(status, 0, (uint64_t)ntiles * 8, st));
+    rk_consts c;
+    uint32_t bp[16];
+    bp[0] = 1;
+    for (int k = 1; k < 16; k++) bp[k] = mulmod31(bp[k - 1], base);
+    for (int m = 0; m < 4; m++)
+        for (int q = 0; q < 4; q++) {
+            c.wv[m][q] = 0;
+            for (int j = 0; j < 4; j++) c.wv[m][q] |= ((bp[15 - 4 * q - j] >> (8 * m)) & 0xFFu) << (8 * j);
+        }
+    c.b16 = h_pow(base, 16);
+    c.b64 = h_pow(base, 64);
+    for (int k = 0; k < 5; k++) c.scan_w[k] = h_pow(base, 64ull << k);
+    c.warp_w = h_pow(base, 2048);
+    for (int l = 0; l < 32; l++) c.lane_w[l] = h_pow(base, 64ull * l);
+    for (int g = 0; g < 4; g++) c.gran_w[g] = h_pow(base, 16ull * (g + 1));
+    for (int w = 0; w < RK_NW; w++) c.warp_pow[w] = h_pow(base, 2048ull * w);
+    const uint32_t W = h_pow(base, RK_TILE);
+    c.tile_pow[0] = 1;
+    for (int l = 1; l < 64; l++) c.tile_pow[l] = mulmod31(c.tile_pow[l - 1], W);
+    c.tile_w64 = mulmod31(c.tile_pow[63], W);
+    const uint32_t grid = std::min<uint64_t>(ntiles, (uint64_t)sms * per_sm);
+    rks_build_kernel<<<grid, RK_NW * 32, 0, st>>>(d_text, ngran, ntiles, c, d_out, status);
     KERNEL_CHECK();
 }
 

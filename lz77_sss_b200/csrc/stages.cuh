@@ -210,6 +210,10 @@ struct rks_state {
     uint32_t base = 0;
 };
 void rks_build(const uint8_t* d_text, uint64_t n, uint32_t base, rks_state& R, cudaStream_t st);
+// the same table (pf[g] for g < ceil(n / 16)) into the caller's d_out, look-back states in a static device array: no allocation.
+// n <= RKS_NOALLOC_MAX_BYTES; d_text and d_out 16-byte aligned, zero bytes behind the text up to the next multiple of 16.
+constexpr uint64_t RKS_NOALLOC_MAX_BYTES = 1ull << 30;
+void rks_build_noalloc(const uint8_t* d_text, uint64_t n, uint32_t base, uint32_t* d_out, cudaStream_t st);
 void rks_substring_batch(const uint8_t* d_text, const rks_state& R, const uint64_t* d_pos, const uint64_t* d_len, uint64_t nq,
                          uint32_t* d_out, cudaStream_t st);
 void rks_fps(const uint8_t* d_text, const rks_state& R, uint64_t s, uint64_t cnt, uint32_t* d_out, cudaStream_t st);
