@@ -140,6 +140,9 @@ int lz77sss_shard_parse(lz77sss_handle* h, uint64_t beg, uint64_t end, const uin
                         uint64_t* d_table_out, uint64_t exit_state[4], uint64_t* num_factors);
 /* factors of the last lz77sss_shard_parse on this handle (HOST arrays) */
 int lz77sss_shard_factors(lz77sss_handle* h, uint64_t* src, uint64_t* len, uint64_t cap, uint64_t* count);
+/* the same factors without a copy: pointers to the library's PINNED host arrays (valid until the next call on the handle),
+ * so that a host layer can send them to a device or a peer at link speed */
+int lz77sss_shard_factors_view(lz77sss_handle* h, const uint64_t** src, const uint64_t** len, uint64_t* count);
 /* the last 65 positions of the text (end-of-text rules of the gap index), on the rank that parsed the last range,
  * right after its final lz77sss_shard_parse: emits the remaining factors from `state` */
 int lz77sss_shard_finish(lz77sss_handle* h, const uint64_t state[4], lz77sss_emit_fn emit, void* ctx);

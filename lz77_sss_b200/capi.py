@@ -25,7 +25,7 @@ EXPORTS = [
     "lz77sss_device_text_free", "lz77sss_factorize_approximate_device", "lz77sss_decode", "lz77sss_build_sss",
     "lz77sss_time_sss_kernel", "lz77sss_get_stats", "lz77sss_get_sss", "lz77sss_get_sa_s", "lz77sss_get_lcp_s",
     "lz77sss_get_lpf", "lz77sss_lce_batch", "lz77sss_sink_emit",
-    "lz77sss_shard_prepare", "lz77sss_shard_table_entries", "lz77sss_shard_entry_guess", "lz77sss_shard_split", "lz77sss_shard_parse",
+    "lz77sss_shard_prepare", "lz77sss_shard_table_entries", "lz77sss_shard_entry_guess", "lz77sss_shard_split", "lz77sss_shard_parse", "lz77sss_shard_factors_view",
     "lz77sss_shard_factors", "lz77sss_shard_finish", "lz77sss_shard_index",
     "lz77sss_rks_create", "lz77sss_rks_destroy", "lz77sss_rks_table", "lz77sss_rks_table_noalloc", "lz77sss_rks_fps", "lz77sss_rks_substring",
     "lz77sss_rks_time_build", "lz77sss_time_decode", "lz77sss_kernel_profile", "lz77sss_kernel_profile_get",
@@ -103,6 +103,7 @@ def lib():
                                           C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.lz77sss_shard_index.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]
         L.lz77sss_shard_factors.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.lz77sss_shard_factors_view.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
         L.lz77sss_shard_finish.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
         L.lz77sss_rks_create.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_void_p)]
         L.lz77sss_rks_destroy.argtypes = [C.c_void_p]
@@ -347,6 +348,16 @@ class Factorizer:
         ln = np.empty(max(1, z), dtype=np.uint64)
         _check(lib().lz77sss_shard_factors(self._h, _ptr(src), _ptr(ln), z, C.byref(cnt)))
         return src[:z], ln[:z]
+
+    def shard_factors_view(self):
+        """The factors of the last shard_parse as views of the library's pinned arrays (no copy; valid until the next call)."""
+        ps, pl, cnt = C.c_void_p(), C.c_void_p(), C.c_uint64(0)
+        _check(lib().lz77sss_shard_factors_view(self._h, C.byref(ps), C.byref(pl), C.byref(cnt)))
+        z = int(cnt.value)
+        if z == 0:
+            return np.empty(0, np.uint64), np.empty(0, np.uint64)
+        return (np.ctypeslib.as_array((C.c_uint64 * z).from_address(ps.value)),
+                np.ctypeslib.as_array((C.c_uint64 * z).from_address(pl.value)))
 
     def shard_finish(self, state, cap=4096):
         src, ln, s = self._sink(cap)

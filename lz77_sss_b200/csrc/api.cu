@@ -1529,6 +1529,15 @@ int lz77sss_shard_factors(lz77sss_handle* h, uint64_t* src, uint64_t* len, uint6
     return LZ77SSS_OK;
 }
 
+int lz77sss_shard_factors_view(lz77sss_handle* h, const uint64_t** src, const uint64_t** len, uint64_t* count) {
+    NEED_PREPARED();
+    if (!src || !len || !count) return fail(LZ77SSS_E_ARG, "null argument");
+    *src = h->f_src.data();
+    *len = h->f_len.data();
+    *count = h->f_src.size();
+    return LZ77SSS_OK;
+}
+
 int lz77sss_shard_finish(lz77sss_handle* h, const uint64_t state[4], lz77sss_emit_fn emit, void* ctx) {
     NEED_PREPARED();
     if (!state || !emit) return fail(LZ77SSS_E_ARG, "null argument");

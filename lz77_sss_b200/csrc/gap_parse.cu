@@ -1720,11 +1720,13 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                     link_phase_kernel<<<gl, 256, 0, st>>>(C, first, sc.J, 0, 3, d_exit);
                     KERNEL_CHECK();
                 }
+                mark("  round: chain linked", a0, st);
                 CUDA_CHECK(cudaMemsetAsync(sc.notins.get(), 0, nwords * 4, st));
                 if (!naive) {
                     notins_kernel<<<gw, 128, 0, st>>>(C, sc.notins, first);
                     KERNEL_CHECK();
                 }
+                mark("  round: bitmap built", a0, st);
                 // A resumed slice (sharded run, later passes) starts from a converged parse: few bits flip, and only
                 // the blocks whose probes can see a flipped bit (or a changed table entry, or a new entry state) are
                 // parsed again.  A fresh slice flips bits everywhere in its first rounds; following them costs more
@@ -1755,6 +1757,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                                                                                             (uint32_t)table_entries);
                     KERNEL_CHECK();
                 }
+                mark("  round: changes marked", a0, st);
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get(), 0, 4, st));
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 3, 0, 4, st));
                 CUDA_CHECK(cudaMemsetAsync(sc.changed.get() + 4, 0xFF, 4, st));
@@ -1767,6 +1770,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                     snprintf(nm, sizeof nm, "parse round %02llu%s", (unsigned long long)round, track ? " (tracking)" : "");
                     prof_end(st, nm, 0);
                 }
+                mark("  round: parsed", a0, st);
                 sc.rounds++;
                 uint32_t chg = 0;
                 CUDA_CHECK(cudaMemcpyAsync(&chg, sc.changed.get(), 4, cudaMemcpyDeviceToHost, st));
@@ -1790,6 +1794,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 if (!track && track_now && C.bmin > 0)      // the blocks in front of the last round's first change were not
                     CUDA_CHECK(cudaMemsetAsync(sc.dirty.get(), 0, C.bmin, st));   // parsed and need not be: drop their flags
                 const bool repaired = sparse && repair();
+                mark("  round: repaired", a0, st);
                 if (give_up_sparse) break;
                 if (!chg && !repaired) { converged = true; break; }
                 if (!track) {
@@ -1807,6 +1812,7 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 have_sorted = have_parse = false;
                 continue;
             }
+            mark("converged", a0, st);
             if (!converged) throw std::runtime_error("gap_parse: the block chain did not reach its fixed point");
             if (K) CUDA_CHECK(cudaMemcpyAsync(sc.Hc_prev.get(), sc.Hc.get(), table_entries * 8, cudaMemcpyDeviceToDevice, st));
             // factors of the blocks on the chain, in order

@@ -138,7 +138,16 @@ __global__ void iota_u32_kernel(uint32_t* d, uint64_t n) {
 // A pass takes a digit of up to 9 bits (NB = 256 or 512 bins): the bits of a sort are split into the fewest passes.
 constexpr int RS_NT = 256;
 constexpr int RS_NW = RS_NT / 32;
-template <typename K> struct rs_cfg { static constexpr int IPT = sizeof(K) == 4 ? 16 : 8; };
+#ifndef RS_IPT32
+#define RS_IPT32 16
+#endif
+#ifndef RS_IPT64
+#define RS_IPT64 8
+#endif
+#ifndef RS_MIN_CTAS
+#define RS_MIN_CTAS 4
+#endif
+template <typename K> struct rs_cfg { static constexpr int IPT = sizeof(K) == 4 ? RS_IPT32 : RS_IPT64; };
 
 template <typename K, int NB>
 __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ keys, uint64_t n, int shift,
@@ -174,7 +183,7 @@ __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ ke
 }
 
 template <typename K, int NB, bool IOTA>
-__global__ void __launch_bounds__(RS_NT, 4) rs_scatter_kernel(const K* __restrict__ keys,
+__global__ void __launch_bounds__(RS_NT, RS_MIN_CTAS) rs_scatter_kernel(const K* __restrict__ keys,
                                                            const uint32_t* __restrict__ vals,
                                                            K* __restrict__ okeys, uint32_t* __restrict__ ovals,
                                                            uint64_t n, int shift, uint32_t mask,

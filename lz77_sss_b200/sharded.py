@@ -99,7 +99,7 @@ class CudaBackend:
         return self.F.shard_parse(beg, end, entry, table_in.data_ptr(), table_out.data_ptr())
 
     def factors(self):
-        return self.F.shard_factors()
+        return self.F.shard_factors_view()
 
     def finish(self, state):
         return self.F.shard_finish(state)
@@ -228,28 +228,28 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
     # step 4: factors of the own range (+ the tail on the last non-empty range), gathered on rank 0
     t_c = time.perf_counter()
     if beg < end:
-        src, ln = backend.factors()
+        src, ln = backend.factors()         # (the CUDA backend hands out views of the library's pinned arrays)
     else:
         src, ln = np.empty(0, np.uint64), np.empty(0, np.uint64)
+    ts, tl = np.empty(0, np.uint64), np.empty(0, np.uint64)
     last_rank = max(r for r in range(world) if ranges[r][0] < ranges[r][1])
     if rank == last_rank and exit_state[0] < n:
         ts, tl = backend.finish(exit_state)
-        src, ln = np.concatenate([src, ts]), np.concatenate([ln, tl])
     if world == 1:
-        return src, ln, passes
-    counts = [int(c.item()) for c in comm.all_gather(torch.tensor([src.size], dtype=torch.int64, device=device))]
+        return np.concatenate([src, ts]), np.concatenate([ln, tl]), passes
+    mine_z = src.size + ts.size
+    counts = [int(c.item()) for c in comm.all_gather(torch.tensor([mine_z], dtype=torch.int64, device=device))]
     zmax = max(max(counts), 1)
     cuda = torch.device(device).type == "cuda"
     mine = torch.empty(2 * zmax, dtype=torch.int64, device=device)
-    if src.size:
-        # (uint64 -> int64 is a view; on a GPU the arrays go through a pinned staging buffer that is kept between calls)
-        for k, a in enumerate((src, ln)):
-            h = torch.from_numpy(a.view(np.int64))
-            if cuda:
-                stage = _pinned((rank, "up", k), a.size)
-                stage[:a.size].copy_(h)
-                h = stage[:a.size]
-            mine[k * zmax:k * zmax + a.size].copy_(h, non_blocking=cuda)
+    # (uint64 -> int64 is a view; pinned sources go to the GPU without staging, the few tail factors are pageable)
+    for k, (a, t) in enumerate(((src, ts), (ln, tl))):
+        if a.size:
+            mine[k * zmax:k * zmax + a.size].copy_(torch.from_numpy(a.view(np.int64)), non_blocking=cuda)
+        if t.size:
+            mine[k * zmax + a.size:k * zmax + mine_z].copy_(torch.from_numpy(np.ascontiguousarray(t).view(np.int64)))
+    if cuda:
+        torch.cuda.synchronize(device)      # the views may be overwritten by the handle's next call
     parts = comm.all_gather(mine)
     if rank != 0:
         if log is not None:

@@ -12,6 +12,7 @@ mib = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 world = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 threads = int(sys.argv[3]) if len(sys.argv) > 3 else 16
 equal = "equal" in sys.argv[4:]
+profile = "profile" in sys.argv[4:]      # per-kernel event times of the LAST rank (all its passes)
 n = mib << 20
 text = synth.dna_collection(n, seed=2, chrom_len=min(16 << 20, max(n // 64, 1 << 16)))
 dev = torch.device("cuda", 0)
@@ -31,7 +32,13 @@ def run(r):
             d_ptr = be.distribute_text(text, n)
             entries = be.prepare(d_ptr, text.ctypes.data, n)
             comm = sharded.ThreadComm(r, world, dev, shared)
+            if profile and r == world - 1:
+                F.kernel_profile(True)
             res[r] = sharded.factorize_sharded(be, n, entries, r, world, dev, comm=comm, log=logs[r])
+            if profile and r == world - 1:
+                F.kernel_profile(False)
+                for row in F.kernel_profile_rows():
+                    print(f"rank {r}: {row['ms']:10.3f} ms {row['launches']:5d}  {row['kernel']}")
             if r == 0:
                 res[r] = (res[r][0].copy(), res[r][1].copy(), res[r][2])
     except Exception as e:  # noqa: BLE001
