@@ -372,43 +372,49 @@ __global__ void __launch_bounds__(256) repair_start_kernel(const uint64_t* __res
 // Splices the sorted repair list L (bucket << 32 | entry id; all of it, the step is idempotent) into the chains.  The chains
 // hold the sorted index and, when L is the small list, the big list (big, rstart).  One thread per entry: its own link, and
 // the link of the entry behind it if no other entry of L lies in between.
+template <typename T>
+__device__ __forceinline__ uint32_t hinted_lower_bound(const T* __restrict__ arr, uint32_t lo, uint32_t hi, T key, uint32_t g);
+constexpr uint32_t SPL = 8;               // consecutive list entries per thread
 __global__ void __launch_bounds__(256) splice_repair_kernel(const uint32_t* __restrict__ sval, const uint32_t* __restrict__ bstart,
                                                             const uint64_t* __restrict__ L, uint32_t cnt,
                                                             const uint64_t* __restrict__ big, const uint32_t* __restrict__ rstart,
                                                             uint32_t* __restrict__ prev) {
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= cnt) return;
-    const uint64_t x = L[k];
-    const uint32_t b = (uint32_t)(x >> 32), e = (uint32_t)x;
-    int64_t pred = -1;
-    uint32_t succ = NOENT;
-    {
-        const uint32_t lo = bstart[b], hi = bstart[b + 1];
-        uint32_t l = lo, h = hi;
-        while (l < h) {
-            const uint32_t mid = (l + h) >> 1;
-            if (sval[mid] < e) l = mid + 1;
-            else h = mid;
+    // a thread takes SPL consecutive entries: entries of one bucket ascend, so the search for the next one starts where the
+    // last one ended (a few loads instead of a bisection of a bucket with millions of entries)
+    const uint32_t k0 = (blockIdx.x * blockDim.x + threadIdx.x) * SPL;
+    if (k0 >= cnt) return;
+    const uint32_t k1 = k0 + SPL < cnt ? k0 + SPL : cnt;
+    uint32_t last_b = NOENT, g0 = NOENT, g1 = NOENT;
+    uint64_t before = k0 > 0 ? L[k0 - 1] : 0;
+    uint64_t x = L[k0];
+    for (uint32_t k = k0; k < k1; k++) {
+        const uint64_t after = k + 1 < cnt ? L[k + 1] : ~0ull;
+        const uint32_t b = (uint32_t)(x >> 32), e = (uint32_t)x;
+        if (b != last_b) { g0 = g1 = NOENT; last_b = b; }
+        int64_t pred = -1;
+        uint32_t succ = NOENT;
+        {
+            const uint32_t lo = bstart[b], hi = bstart[b + 1];
+            const uint32_t l = hinted_lower_bound<uint32_t>(sval, lo, hi, e, g0);
+            g0 = l;
+            if (l > lo) pred = sval[l - 1];
+            if (l < hi) succ = sval[l];
         }
-        if (l > lo) pred = sval[l - 1];
-        if (l < hi) succ = sval[l];
-    }
-    if (big) {
-        const uint32_t lo = rstart[b], hi = rstart[b + 1];
-        uint32_t l = lo, h = hi;
-        while (l < h) {
-            const uint32_t mid = (l + h) >> 1;
-            if (big[mid] < x) l = mid + 1;
-            else h = mid;
+        if (big) {
+            const uint32_t lo = rstart[b], hi = rstart[b + 1];
+            const uint32_t l = hinted_lower_bound<uint64_t>(big, lo, hi, x, g1);
+            g1 = l;
+            if (l > lo) pred = max(pred, (int64_t)(uint32_t)big[l - 1]);
+            if (l < hi) succ = min(succ, (uint32_t)big[l]);
         }
-        if (l > lo) pred = max(pred, (int64_t)(uint32_t)big[l - 1]);
-        if (l < hi) succ = min(succ, (uint32_t)big[l]);
+        if (k > 0 && (uint32_t)(before >> 32) == b) pred = max(pred, (int64_t)(uint32_t)before);
+        uint32_t own_next = NOENT;
+        if (k + 1 < cnt && (uint32_t)(after >> 32) == b) own_next = (uint32_t)after;
+        prev[e] = pred < 0 ? NOENT : (uint32_t)pred;
+        if (succ != NOENT && own_next > succ) prev[succ] = e;
+        before = x;
+        x = after;
     }
-    if (k > 0 && (uint32_t)(L[k - 1] >> 32) == b) pred = max(pred, (int64_t)(uint32_t)L[k - 1]);
-    uint32_t own_next = NOENT;
-    if (k + 1 < cnt && (uint32_t)(L[k + 1] >> 32) == b) own_next = (uint32_t)L[k + 1];
-    prev[e] = pred < 0 ? NOENT : (uint32_t)pred;
-    if (succ != NOENT && own_next > succ) prev[succ] = e;
 }
 
 struct block_state {
@@ -1616,13 +1622,13 @@ void gap_parse_run(const uint8_t* d_text, uint64_t n, uint32_t tau, const pos_t*
                 C.rk = rk_cur;
                 repair_start_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(rk_cur, C.R, (uint32_t)table_entries + 1, sc.rstart);
                 KERNEL_CHECK();
-                splice_repair_kernel<<<ceil_div_u(C.R, 256), 256, 0, st>>>(C.sval, C.bstart, rk_cur, C.R, nullptr, nullptr, sc.prev);
+                splice_repair_kernel<<<ceil_div_u(ceil_div_u(C.R, SPL), 256), 256, 0, st>>>(C.sval, C.bstart, rk_cur, C.R, nullptr, nullptr, sc.prev);
                 KERNEL_CHECK();
             } else if (r2[1] <= rcap2) {
                 C.R2 = r2[1];
                 radix_sort_pairs(rk2_cur, rk2_alt, rv_cur, rv_alt, C.R2, 0, 32 + key_bits, sc.sort, st);   // (payload unused)
                 C.rk2 = rk2_cur;
-                splice_repair_kernel<<<ceil_div_u(C.R2, 256), 256, 0, st>>>(C.sval, C.bstart, rk2_cur, C.R2, C.R ? C.rk : nullptr,
+                splice_repair_kernel<<<ceil_div_u(ceil_div_u(C.R2, SPL), 256), 256, 0, st>>>(C.sval, C.bstart, rk2_cur, C.R2, C.R ? C.rk : nullptr,
                                                                             sc.rstart, sc.prev);
                 KERNEL_CHECK();
             } else {
