@@ -283,7 +283,9 @@ def run_sharded(args, world, rank, local, barrier):
     clocks = sampler.stop()
     # outside the timed region: the sharded factor stream against the single-GPU path on rank 0's GPU (same text and parameters)
     stats["want_hash"] = True
+    keep = (stats["h2d"], stats["d2h"])              # (of the last end-to-end step)
     step(False)
+    stats["h2d"], stats["d2h"] = keep
     sharded_ok = None
     if rank == 0:
         with capi.Factorizer(tau=args.tau, num_threads=args.threads, gap_bases=capi.DEFAULT_GAP_BASES, device=local) as G:
