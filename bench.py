@@ -220,6 +220,8 @@ def run_sharded(args, world, rank, local, barrier):
     import torch.distributed as dist
     from lz77_sss_b200 import capi, sharded
     dev = torch.device("cuda", local)
+    # the ranks of one box share its cores: the host side of a rank (coverage chains, copies) takes its share of them
+    os.environ.setdefault("LZ77SSS_HOST_THREADS", str(max(1, (os.cpu_count() or 1) // world)))
     text = make_text(args, 0)                      # the same text on every rank; a rank only uploads its shard
     n = text.size
     sh_ranges = sharded.split_ranges(n, world, 1 << 16)

@@ -141,6 +141,7 @@ struct lz77sss_handle {
     exact_scratch ex;
     dbuf<uint64_t> dec_src, dec_len;
     dbuf<uint8_t> dec_out;
+    pinned_vec<uint8_t> d2h_stage[2];      // decode output on its way to pageable caller memory
     pinned_vec<uint64_t> f_src, f_len;  // factors of the device emission (pinned: they arrive by D2H copies)
     uint64_t slice_len = 1ull << 28;
     uint32_t block_len = 1024;        // positions per parse block (measured at 1 GiB: 2048 / 1024 / 512 -> 65.9 / 50.5 / 50.6 ms of parse)
@@ -199,7 +200,9 @@ template <> pipeline<uint64_t>& pipe<uint64_t>(lz77sss_handle* h) { return h->p6
 // runs f(0) .. f(p-1) on up to hardware_concurrency host threads; the first exception is rethrown
 template <typename F>
 void run_blocks(uint32_t p, F f) {
-    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    if (const char* e = getenv("LZ77SSS_HOST_THREADS"))      // several ranks on one box share its cores (bench.py sets cores / ranks)
+        hw = std::max(1u, (unsigned)atoi(e));
     const unsigned nt = std::min<unsigned>(p, hw);
     if (nt <= 1) {
         for (uint32_t i = 0; i < p; i++) f(i);
@@ -1664,6 +1667,45 @@ int lz77sss_rks_time_build(lz77sss_rks* r, int iters, double* ms_out, uint64_t* 
     });
 }
 
+namespace {
+// Device -> host memory of the caller.  Pinned memory takes one copy at link speed.  Pageable memory would be staged by the
+// driver at a fraction of it: chunks go through two pinned buffers instead, and several host threads copy chunk k - 1 out
+// (first touch of the caller's pages included) while chunk k is on the link.
+void copy_to_host(lz77sss_handle* h, uint8_t* out, const uint8_t* d, uint64_t n) {
+    cudaPointerAttributes attr;
+    const bool pinned = cudaPointerGetAttributes(&attr, out) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();                             // (an unregistered pointer may leave an error behind on old drivers)
+    constexpr uint64_t CH = 64ull << 20;
+    if (pinned || n <= CH / 4) {
+        CUDA_CHECK(cudaMemcpyAsync(out, d, n, cudaMemcpyDeviceToHost, h->st));
+        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        return;
+    }
+    cudaEvent_t ev[2];
+    for (auto& e : ev) CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    struct drop { cudaEvent_t* e; ~drop() { cudaEventDestroy(e[0]); cudaEventDestroy(e[1]); } } guard{ev};
+    for (auto& b : h->d2h_stage) b.resize(CH);
+    const uint64_t chunks = (n + CH - 1) / CH;
+    auto drain = [&](uint64_t k) {                  // chunk k has arrived in its buffer: out to the caller's memory
+        CUDA_CHECK(cudaEventSynchronize(ev[k & 1]));
+        const uint64_t off = k * CH, len = std::min(CH, n - off);
+        const uint8_t* from = h->d2h_stage[k & 1].data();
+        const uint32_t parts = 8;
+        run_blocks(parts, [&](uint32_t t) {
+            const uint64_t b = len * t / parts, e = len * (t + 1) / parts;
+            std::memcpy(out + off + b, from + b, e - b);
+        });
+    };
+    for (uint64_t k = 0; k < chunks; k++) {
+        const uint64_t off = k * CH, len = std::min(CH, n - off);
+        CUDA_CHECK(cudaMemcpyAsync(h->d2h_stage[k & 1].data(), d + off, len, cudaMemcpyDeviceToHost, h->st));
+        CUDA_CHECK(cudaEventRecord(ev[k & 1], h->st));
+        if (k > 0) drain(k - 1);
+    }
+    drain(chunks - 1);
+}
+}  // namespace
+
 int lz77sss_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, uint64_t z, uint8_t* out, uint64_t n) {
     if (!h || !src || !len || (!out && n)) return fail(LZ77SSS_E_ARG, "null argument");
     return guarded([&]() {
@@ -1677,8 +1719,7 @@ int lz77sss_decode(lz77sss_handle* h, const uint64_t* src, const uint64_t* len, 
         int rc = decode_factors(h->dec_src, h->dec_len, z, h->dec_out, n, h->st, &rounds, h->dec);
         if (rc == -4) return fail(LZ77SSS_E_INTERNAL, "decode: the copy chains did not resolve");
         if (rc) return fail(LZ77SSS_E_ARG, "decode: malformed factor stream (lengths do not add up to n or a source is not earlier text)");
-        CUDA_CHECK(cudaMemcpyAsync(out, h->dec_out.get(), n, cudaMemcpyDeviceToHost, h->st));
-        CUDA_CHECK(cudaStreamSynchronize(h->st));
+        copy_to_host(h, out, h->dec_out.get(), n);
         return LZ77SSS_OK;
     });
 }

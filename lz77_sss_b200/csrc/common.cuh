@@ -124,6 +124,8 @@ struct sort_scratch {
 void radix_sort_pairs(uint64_t*& keys, uint64_t*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
                       int bit_hi, sort_scratch& s, cudaStream_t st);
 
+void radix_sort_keys(uint64_t*& keys, uint64_t*& kalt, uint64_t n, int bit_lo, int bit_hi, sort_scratch& s, cudaStream_t st);
+
 // same with 32-bit keys (gap index entries: bucket id -> entry id)
 // vals_are_iota: the values are 0, 1, 2, ... and need not be read (nor written by the caller) before the first pass
 // first_keys: the unsorted keys live in this read-only array (keys is then only a ping-pong buffer)

@@ -147,7 +147,7 @@ struct gap_parse_scratch {
     dbuf<uint64_t> rkb0, rkb1;             // the small second repair list
     dbuf<uint32_t> rstart;                 // bucket starts of the big repair list
     dbuf<uint64_t> newent;                 // the entries a repair step added (for the change tracking)
-    dbuf<uint32_t> rv0, rv1, req;          // (unused payload of that sort), repair requests of a parse round
+    dbuf<uint32_t> req;                    // repair requests of a parse round
     uint64_t repair_entries = 0;           // entries added to repair lists over all slices
     sort_scratch sort;
     scan_scratch scan;

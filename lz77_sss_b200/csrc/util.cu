@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(RS_NT, RS_MIN_CTAS) rs_scatter_kernel(const K*
     }
 #pragma unroll
     for (int k = 0; k < IPT; k++)          // in flight during the scan of the digit totals
-        val[k] = (uint32_t)(k * 32) + lane >= in_warp ? 0u : IOTA ? (uint32_t)(base + (uint64_t)k * 32 + lane) : vals[base + (uint64_t)k * 32 + lane];
+        val[k] = (uint32_t)(k * 32) + lane >= in_warp || !ovals ? 0u : IOTA ? (uint32_t)(base + (uint64_t)k * 32 + lane) : vals[base + (uint64_t)k * 32 + lane];
     __syncthreads();
     {   // thread t, digits DPT*t .. DPT*t+DPT-1: per-warp counts -> exclusive offsets over the warps; digit totals
         uint32_t tot[DPT];
@@ -284,7 +284,7 @@ __global__ void __launch_bounds__(RS_NT, RS_MIN_CTAS) rs_scatter_kernel(const K*
         const uint32_t d = (uint32_t)(kk >> shift) & mask;
         const uint32_t pos = goff[d] + (i - dstart[d]);
         okeys[pos] = kk;
-        ovals[pos] = svals[i];
+        if (ovals) ovals[pos] = svals[i];       // (keys-only sorts pass no payload arrays)
     }
 }
 
@@ -370,14 +370,14 @@ void radix_pass(K* keys, K* kalt, uint32_t* vals, uint32_t* valt, uint64_t n, in
     KERNEL_CHECK();
     // algorithmic bytes: keys and payloads read once and written once (generated payloads are not read)
     PROF_END(st, sizeof(K) == 4 ? "rs_scatter_kernel<u32> (radix pass of the gap index)" : "rs_scatter_kernel<u64> (radix pass of the SSS suffix sort)",
-             n * (2 * sizeof(K) + (iota ? 4 : 8)));
+             n * (2 * sizeof(K) + (!valt ? 0 : iota ? 4 : 8)));
 }
 
 template <typename K>
 void radix_sort_pairs_t(K*& keys, K*& kalt, uint32_t*& vals, uint32_t*& valt, uint64_t n, int bit_lo,
                         int bit_hi, sort_scratch& s, cudaStream_t st, bool iota, const K* first_keys = nullptr) {
     if (n <= 1 || bit_hi <= bit_lo) {
-        if (iota) iota_u32(vals, n, st);
+        if (iota && vals) iota_u32(vals, n, st);
         if (first_keys && n) CUDA_CHECK(cudaMemcpyAsync(keys, first_keys, n * sizeof(K), cudaMemcpyDeviceToDevice, st));
         return;
     }
@@ -418,4 +418,12 @@ void iota_u32(uint32_t* d, uint64_t n, cudaStream_t st) {
     KERNEL_CHECK();
 }
 
+}  // namespace lz77sss
+
+namespace lz77sss {
+// keys only (the repair lists of the gap index: the entry id is part of the key)
+void radix_sort_keys(uint64_t*& keys, uint64_t*& kalt, uint64_t n, int bit_lo, int bit_hi, sort_scratch& s, cudaStream_t st) {
+    uint32_t *v = nullptr, *va = nullptr;
+    radix_sort_pairs_t<uint64_t>(keys, kalt, v, va, n, bit_lo, bit_hi, s, st, false);
+}
 }  // namespace lz77sss

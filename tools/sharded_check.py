@@ -1,6 +1,6 @@
 """Sharded emission against the single-GPU path at bench sizes, on ONE GPU: `world` virtual ranks (threads, one handle each).
   python tools/sharded_check.py <MiB> <world> [num_threads] [equal]
-equal: ranges of equal length instead of equal work.  Prints where the streams first differ (exit 1) or "equal" (exit 0)."""
+equal: ranges of equal length instead of equal work; genomes: the 4 GiB configuration's text generator (64-bit positions above 4 GiB).  Prints where the streams first differ (exit 1) or "equal" (exit 0)."""
 import os, sys, threading
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -14,7 +14,8 @@ threads = int(sys.argv[3]) if len(sys.argv) > 3 else 16
 equal = "equal" in sys.argv[4:]
 profile = "profile" in sys.argv[4:]      # per-kernel event times of the LAST rank (all its passes)
 n = mib << 20
-text = synth.dna_collection(n, seed=2, chrom_len=min(16 << 20, max(n // 64, 1 << 16)))
+text = (synth.genome_collection(n, seed=3) if "genomes" in sys.argv[4:] else
+        synth.dna_collection(n, seed=2, chrom_len=min(16 << 20, max(n // 64, 1 << 16))))
 dev = torch.device("cuda", 0)
 shared = sharded.ThreadComm.make_shared(world)
 res, err, logs = [None] * world, [], [[] for _ in range(world)]

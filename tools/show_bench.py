@@ -3,7 +3,7 @@ import json, sys
 d = json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
 if len(sys.argv) > 2:
     print(d["config"]["tau"], "MiB/s", round(d["value"]), "e2e", round(d["e2e"]["value"]), "parity", d.get("parity_checked"), "|S|", d.get("size_sss"),
-          "z", d.get("factors"), "sss frac", round(d["roofline"]["frac"], 3), "cpu", round(d.get("cpu_baseline", {}).get("value", 0), 1),
+          "z", d.get("factors"), "sss frac", round(d.get("roofline_k1k2", d["roofline"])["frac"], 3), "cpu", round((d.get("cpu_baseline") or {}).get("value", 0), 1),
           "fallbacks", d.get("index", {}).get("sparse_fallbacks"))
     sys.exit(0)
 print({k: d.get(k) for k in ("value", "ms_per_step", "parity_checked", "gpu_launches", "index")})
