@@ -183,8 +183,9 @@ __global__ void __launch_bounds__(RS_NT) rs_hist_kernel(const K* __restrict__ ke
 }
 
 // (Measured and dropped, profiles/r02_scatter_*_experiment.*: other tile sizes and CTAs per SM, 14.2-16.1 ms per GiB for the gap
-// index; a loop over tiles with the next tile's keys and payloads in flight, 17.6-24 ms: neither residency nor the latency of
-// a tile's own loads is what holds the pass at 0.3 of the HBM peak.)
+// index; a loop over tiles with the next tile's keys and payloads in flight, 17.6-24 ms; all MATCH instructions of a thread issued in
+// front of the counter updates, 15.3 against 15.1 ms: neither residency, nor the latency of a tile's own loads, nor the
+// latency of the matches is what holds the pass at 0.3 of the HBM peak.)
 template <typename K, int NB, bool IOTA>
 __global__ void __launch_bounds__(RS_NT, RS_MIN_CTAS) rs_scatter_kernel(const K* __restrict__ keys,
                                                            const uint32_t* __restrict__ vals,
