@@ -209,6 +209,7 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
     exit_state = entry
     passes = 0
     need_parse = True
+    cache = prev_local = new_in = None          # tables of the ranks in front, own table at the last exchange, their maximum
     limit = max_passes if max_passes is not None else world + 2
     while True:
         t_a = time.perf_counter()
@@ -224,12 +225,43 @@ def factorize_sharded(backend, n: int, table_entries: int, rank: int, world: int
         # exchange: exit states and the per-range tables (last inserted position + 1 per bucket inside the range)
         exits = [tuple(t.tolist()) for t in
                  comm.all_gather(torch.tensor([int(x) for x in exit_state], dtype=torch.int64, device=device))]
-        gathered = comm.all_gather(local)
-        new_in = torch.zeros_like(table_in)
-        for r in range(rank):                      # positions grow with the rank: the maximum is the latest writer
-            torch.maximum(new_in, gathered[r], out=new_in)
+        if cache is None:
+            # first exchange: whole tables (one per rank; a rank keeps those of the ranks in front of it)
+            gathered = comm.all_gather(local)
+            cache = [gathered[r] if r < rank else None for r in range(world)]
+            prev_local = local.clone()
+            new_in = torch.zeros_like(table_in)
+            for r in range(rank):                  # positions grow with the rank: the maximum is the latest writer
+                torch.maximum(new_in, cache[r], out=new_in)
+            table_changed = not torch.equal(new_in, table_in)
+        else:
+            # later exchanges: only the entries that changed since the last one travel (index, value), not 8 bytes per bucket
+            idx = torch.nonzero(local != prev_local).squeeze(1)
+            vals = local[idx]
+            prev_local[idx] = vals
+            counts = [int(c.item()) for c in comm.all_gather(torch.tensor([idx.numel()], dtype=torch.int64, device=device))]
+            cmax = max(counts)
+            table_changed = False
+            if cmax:
+                buf = torch.zeros(2 * cmax, dtype=torch.int64, device=device)
+                buf[:idx.numel()] = idx
+                buf[cmax:cmax + idx.numel()] = vals
+                parts = comm.all_gather(buf)
+                touched = []
+                for r in range(rank):
+                    if counts[r]:
+                        i = parts[r][:counts[r]]
+                        cache[r][i] = parts[r][cmax:cmax + counts[r]]
+                        touched.append(i)
+                if touched:
+                    u = torch.cat(touched)
+                    m = torch.zeros_like(u)
+                    for r in range(rank):
+                        torch.maximum(m, cache[r][u], out=m)
+                    table_changed = not torch.equal(m, table_in[u])
+                    new_in[u] = m
         new_entry = chain_entries(exits, ranges, first_entry)[rank]
-        changed = tuple(new_entry) != tuple(entry) or not torch.equal(new_in, table_in)
+        changed = tuple(new_entry) != tuple(entry) or table_changed
         any_changed = comm.any(changed)
         if log is not None:
             log.append({"pass": passes, "changed_here": bool(changed), "parsed": bool(need_parse), "exit": exit_state,
