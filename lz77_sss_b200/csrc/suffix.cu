@@ -55,7 +55,10 @@ __global__ void group_ids_kernel(const uint32_t* __restrict__ flags, uint32_t* _
     if (flags[k]) gstart[g] = (uint32_t)k;
 }
 
-// One warp per element: LCE of its context with the context of the group's first element (pivot).
+// LCE of every unresolved context with the context of its group's first element (pivot).  A warp takes 32 consecutive
+// elements: the lanes classify their own element (coalesced loads; singletons, finished classes and pivots are done at once),
+// then the warp walks over the elements that need a comparison, one warp-wide LCE each.  (One warp per element spent most of
+// the later rounds, where few elements are unresolved, on launching 4.2 M warps that had nothing to compare.)
 template <typename pos_t>
 __global__ void __launch_bounds__(256) ctx_pivot_kernel(const uint8_t* __restrict__ T, uint64_t n, uint32_t tau,
                                                         const pos_t* __restrict__ S, uint64_t s,
@@ -64,53 +67,66 @@ __global__ void __launch_bounds__(256) ctx_pivot_kernel(const uint8_t* __restric
                                                         const uint32_t* __restrict__ gid,
                                                         const uint32_t* __restrict__ gstart, int first,
                                                         uint64_t* __restrict__ newkeys, uint32_t* __restrict__ counter) {
-    const uint64_t k = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint64_t k0 = (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) << 5;
     const unsigned lane = threadIdx.x & 31;
-    if (k >= s) return;
-    const uint32_t g = gid[k];
-    const uint32_t gs = gstart[g], ge = gstart[g + 1];
-    const uint64_t prev = keys[k];
-    const uint64_t ghi = (uint64_t)g << 32;
-    if (ge - gs == 1) {
-        if (lane == 0) newkeys[k] = ghi;
-        return;
-    }
-    if (!first && ((prev >> 23) & 3) == 1) {      // class of contexts equal to an earlier pivot: final
-        if (lane == 0) newkeys[k] = ghi | (1ull << 23);
-        return;
-    }
-    if (k == gs) {
-        if (lane == 0) {
+    if (k0 >= s) return;
+    const uint64_t k = k0 + lane;
+    bool work = false, counted = false;
+    uint64_t x = 0, p = 0, off = 0, lim = 0, lenx = 0, lenp = 0, ghi = 0;
+    if (k < s) {
+        const uint32_t g = gid[k];
+        const uint32_t gs = gstart[g], ge = gstart[g + 1];
+        const uint64_t prev = keys[k];
+        ghi = (uint64_t)g << 32;
+        if (ge - gs == 1) {
+            newkeys[k] = ghi;
+        } else if (!first && ((prev >> 23) & 3) == 1) {      // class of contexts equal to an earlier pivot: final
             newkeys[k] = ghi | (1ull << 23);
-            atomicAdd(counter, 1u);
+        } else if (k == gs) {
+            newkeys[k] = ghi | (1ull << 23);
+            counted = true;
+        } else {
+            work = true;
+            off = 7;
+            if (!first) {
+                const uint32_t side = (uint32_t)(prev >> 23) & 3, df = (uint32_t)(prev >> 9) & 0x3FFF;
+                off = (side == 0 ? df : MAXD - df) + 1;
+            }
+            x = S[ord[k]];
+            p = S[ord[gs]];
+            lenx = min((uint64_t)3 * tau, n - x);
+            lenp = min((uint64_t)3 * tau, n - p);
+            lim = min(lenx, lenp);
+            if (off > lim) off = lim;
         }
-        return;
     }
-    uint64_t off = 7;
-    if (!first) {
-        uint32_t side = (uint32_t)(prev >> 23) & 3, df = (uint32_t)(prev >> 9) & 0x3FFF;
-        off = (side == 0 ? df : MAXD - df) + 1;
+    unsigned todo = __ballot_sync(0xffffffffu, work);
+    uint64_t d = 0;
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint64_t xs = __shfl_sync(0xffffffffu, x, src), ps = __shfl_sync(0xffffffffu, p, src);
+        const uint64_t os = __shfl_sync(0xffffffffu, off, src), ls = __shfl_sync(0xffffffffu, lim, src);
+        const uint64_t ds = warp_lce(T, xs, ps, os, ls);
+        if ((int)lane == src) d = ds;
     }
-    const uint64_t x = S[ord[k]], p = S[ord[gs]];
-    const uint64_t lenx = min((uint64_t)3 * tau, n - x), lenp = min((uint64_t)3 * tau, n - p);
-    const uint64_t lim = min(lenx, lenp);
-    if (off > lim) off = lim;
-    const uint64_t d = warp_lce(T, x, p, off, lim);
-    if (lane == 0) {
+    if (work) {
         uint32_t side, cf;
         if (d == lim) {
             if (lenx == lenp) { side = 1; cf = 0; }
             else if (lenx < lenp) { side = 0; cf = 0; }                   // proper prefix of the pivot: smaller
             else { side = 2; cf = (uint32_t)T[x + d] + 1; }
         } else {
-            uint32_t cx = T[x + d], cp = T[p + d];
+            const uint32_t cx = T[x + d], cp = T[p + d];
             side = cx < cp ? 0 : 2;
             cf = cx + 1;
         }
-        uint32_t df = side == 1 ? 0 : (side == 0 ? (uint32_t)d : MAXD - (uint32_t)d);
+        const uint32_t df = side == 1 ? 0 : (side == 0 ? (uint32_t)d : MAXD - (uint32_t)d);
         newkeys[k] = ghi | ((uint64_t)side << 23) | ((uint64_t)df << 9) | cf;
-        atomicAdd(counter, 1u);
+        counted = true;
     }
+    const unsigned c = __popc(__ballot_sync(0xffffffffu, counted));
+    if (lane == 0 && c) atomicAdd(counter, c);
 }
 
 __global__ void scatter_rank_kernel(const uint32_t* __restrict__ ord, const uint32_t* __restrict__ gid, uint64_t s,
@@ -267,7 +283,7 @@ void suffix_sort_sync(const uint8_t* T, uint64_t n, uint32_t tau, uint32_t qmax,
     for (int level = 0;; level++) {
         if (ng == s) break;
         CUDA_CHECK(cudaMemsetAsync(ss.counter.get(), 0, 4, st));
-        ctx_pivot_kernel<pos_t><<<nbw, 256, 0, st>>>(T, n, tau, S, s, keys, vals, ss.gid, ss.gstart, level == 0, kalt,
+        ctx_pivot_kernel<pos_t><<<nb, 256, 0, st>>>(T, n, tau, S, s, keys, vals, ss.gid, ss.gstart, level == 0, kalt,
                                                     ss.counter.get());
         KERNEL_CHECK();
         uint32_t active;
