@@ -13,7 +13,7 @@ from lz77_sss_b200 import synth
 pytestmark = pytest.mark.gpu
 
 
-def _noalloc_table(capi, torch, text, base):
+def _noalloc_table(capi, torch, text, base, check_free=False):
     n = text.size
     dev = torch.device("cuda", 0)
     d_text = torch.zeros((n + 15) // 16 * 16 + 16, dtype=torch.uint8, device=dev)       # zero bytes behind the text
@@ -21,9 +21,12 @@ def _noalloc_table(capi, torch, text, base):
     d_out = torch.full(((n + 15) // 16 + 4,), 0xDEAD, dtype=torch.int32, device=dev)
     torch.cuda.synchronize(dev)
     before = torch.cuda.memory_allocated(dev)
+    free_before = torch.cuda.mem_get_info(dev)[0]       # the driver's count: sees a cudaMalloc of the library too
     capi._check(capi.lib().lz77sss_rks_table_noalloc(C.c_void_p(d_text.data_ptr()), n, int(base), C.c_void_p(d_out.data_ptr()), None))
     torch.cuda.synchronize(dev)
     assert torch.cuda.memory_allocated(dev) == before
+    if check_free:      # (not on a first call: loading the kernel's module may take device memory once)
+        assert torch.cuda.mem_get_info(dev)[0] == free_before, "device memory was allocated during the call"
     out = d_out.cpu().numpy().view(np.uint32)
     g = (n + 15) // 16
     assert (out[g:] == 0xDEAD).all(), "wrote behind the table"
@@ -42,7 +45,7 @@ def test_noalloc_table_equals_the_allocating_entry_point_twice(capi):
                 want = R.table()
             got = _noalloc_table(capi, torch, text, base)
             assert got.size == want.size and (got == want).all(), (n, base)
-            again = _noalloc_table(capi, torch, text, base)
+            again = _noalloc_table(capi, torch, text, base, check_free=True)
             assert (again == want).all(), (n, base, "second call")
 
 
