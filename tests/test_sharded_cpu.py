@@ -162,3 +162,24 @@ def test_thread_comm_virtual_ranks():
         t.join(timeout=120)
     src, ln, passes = res[0]
     assert src.tolist() == want_src.tolist() and ln.tolist() == want_len.tolist()
+
+
+def test_weighted_split_covers_the_text_and_gives_the_first_range_more():
+    """CudaBackend.split: pieces of equal work from the library (here: a stand-in with equal lengths) are dealt out so that
+    the first range, which parses once, gets FIRST_RANGE_SHARE of a later range's work."""
+    n = 1_000_003
+
+    class F:
+        def shard_split(self, parts, align=1):
+            cuts = [n * k // parts for k in range(parts + 1)]
+            return [(cuts[k], cuts[k + 1]) for k in range(parts)]
+
+    be = sharded.CudaBackend(F(), torch.device("cpu"))
+    assert be.split(1) == [(0, n)]
+    for world in (2, 3, 4, 8):
+        r = be.split(world)
+        assert len(r) == world and r[0][0] == 0 and r[-1][1] == n
+        assert all(r[k][1] == r[k + 1][0] for k in range(world - 1))
+        assert all(b <= e for b, e in r)
+        first, later = r[0][1] - r[0][0], r[1][1] - r[1][0]
+        assert abs(first / later - sharded.CudaBackend.FIRST_RANGE_SHARE) < 0.1
